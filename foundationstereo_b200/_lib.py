@@ -1,0 +1,107 @@
+"""ctypes binding of libfsb200.so (the C ABI declared in include/fsb200.h).
+
+There is no fallback of any kind: if the shared library is missing the import
+of an op raises, and every compute entry point needs a CUDA device.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_float, c_int, c_size_t, c_uint64, c_void_p
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG, "libfsb200.so")
+
+FSB_F32, FSB_F16, FSB_BF16 = 0, 1, 2
+FSB_PREC_FP32, FSB_PREC_TF32, FSB_PREC_F16, FSB_PREC_BF16 = 0, 1, 2, 3
+FSB_MAX_LEVELS = 6
+FSB_MAX_SRC = 4
+FSB_EPI_BIAS, FSB_EPI_RELU, FSB_EPI_GATE_ZR, FSB_EPI_GATE_Q = 0, 1, 2, 3
+FSB_EPI_GELU, FSB_EPI_SCALE_RES = 4, 5
+
+
+class FsbError(RuntimeError):
+    pass
+
+
+class ConvSrc(ctypes.Structure):
+    _fields_ = [("ptr", c_void_p), ("C", c_int), ("ldc", c_int)]
+
+
+class ConvArgs(ctypes.Structure):
+    _fields_ = [
+        ("src", ConvSrc * FSB_MAX_SRC),
+        ("nsrc", c_int),
+        ("B", c_int), ("H", c_int), ("W", c_int),
+        ("ksize", c_int),
+        ("weight", c_void_p),
+        ("bias", c_void_p),
+        ("Cout", c_int),
+        ("epilogue", c_int),
+        ("out", c_void_p),
+        ("ld_out", c_int),
+        ("h", c_void_p),
+        ("att", c_void_p),
+        ("z_l", c_void_p), ("rh_l", c_void_p), ("z_s", c_void_p), ("rh_s", c_void_p),
+        ("h_out", c_void_p),
+        ("aux", c_void_p),
+        ("ld_aux", c_int),
+        ("out_f32", c_void_p),
+    ]
+
+
+_PROTOS = {
+    "fsb_version": (c_int, []),
+    "fsb_last_error": (c_char_p, []),
+    "fsb_launch_count": (c_uint64, []),
+    "fsb_volume_gwc_concat": (c_int, [c_void_p] * 6 + [c_int] * 8 + [c_void_p]),
+    "fsb_corr_pyramid": (c_int, [c_void_p, c_void_p, POINTER(c_void_p)] + [c_int] * 7 + [c_void_p]),
+    "fsb_geo_pyramid": (c_int, [c_void_p, POINTER(c_void_p)] + [c_int] * 6 + [c_void_p]),
+    "fsb_geo_lookup": (c_int, [POINTER(c_void_p), POINTER(c_void_p), c_void_p, c_void_p, c_void_p]
+                       + [c_int] * 9 + [c_void_p]),
+}
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    """The loaded library; raises FsbError when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FsbError(
+                f"{LIB_PATH} is missing: build it with `python -m foundationstereo_b200.build` "
+                "(there is no CPU or PyTorch fallback for these ops)")
+        L = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in _PROTOS.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def register_proto(name: str, restype, argtypes) -> None:
+    """Used by modules that bind further entry points (update block)."""
+    _PROTOS[name] = (restype, argtypes)
+    if _lib is not None:
+        fn = getattr(_lib, name)
+        fn.restype = restype
+        fn.argtypes = argtypes
+
+
+def check(status: int) -> None:
+    if status != 0:
+        msg = lib().fsb_last_error()
+        raise FsbError(f"libfsb200 status {status}: {msg.decode() if msg else '?'}")
+
+
+def launch_count() -> int:
+    return int(lib().fsb_launch_count())
+
+
+def level_array(tensors):
+    arr = (c_void_p * len(tensors))()
+    for i, t in enumerate(tensors):
+        arr[i] = t.data_ptr()
+    return arr

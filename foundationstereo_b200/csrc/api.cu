@@ -1,0 +1,21 @@
+// Library-wide entry points: version, thread-local error text, launch counter.
+#include "common.cuh"
+
+namespace fsb {
+static thread_local char g_err[512] = "";
+static thread_local uint64_t g_launches = 0;
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+void count_launch(int n) { g_launches += (uint64_t)n; }
+}  // namespace fsb
+
+extern "C" {
+int fsb_version(void) { return FSB_VERSION; }
+const char* fsb_last_error(void) { return fsb::g_err; }
+uint64_t fsb_launch_count(void) { return fsb::g_launches; }
+}

@@ -1,0 +1,384 @@
+// Geometry-encoding volume: init correlation + pyramid (kernel 2, fp32 parity path),
+// geometry-volume transpose + pyramid (kernel 2b) and the per-iteration lookup (kernel 3).
+//
+// Replaces Combined_Geo_Encoding_Volume (core/geometry.py:17-77) and the H == 1 use of
+// bilinear_sampler (core/utils/utils.py:44-55) of the reference.
+#include "common.cuh"
+
+namespace fsb {
+
+// =====================================================================================
+// Kernel 2 (FSB_PREC_FP32): corr[b,h,w1,w2] = <f1hat(:,w1), f2hat(:,w2)>, fp32 FFMA.
+// One CTA = 64 (w1) x 128 (w2) outputs of one image row; the (C,W) planes are already
+// "K-major with W contiguous", so the smem tiles are filled with coalesced loads.  The
+// L2 norms are accumulated from the same tiles and applied in the epilogue; the
+// epilogue also emits every pooled pyramid level from registers (a thread owns 8
+// consecutive w2), so the W x W tensor is never re-read.
+// =====================================================================================
+constexpr int kCorrKC = 16;
+
+template <bool VEC>
+__device__ __forceinline__ void store_run4(float* row, int col, int len, const float* v) {
+  if (VEC) {
+    if (col < len) *reinterpret_cast<float4*>(row + col) = make_float4(v[0], v[1], v[2], v[3]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (col + i < len) row[col + i] = v[i];
+  }
+}
+
+__global__ void __launch_bounds__(256)
+corr_fp32_kernel(const float* __restrict__ f1, const float* __restrict__ f2, LevelPtrs lv, int C, int H,
+                 int W1, int W2, int L) {
+  __shared__ __align__(16) float As[kCorrKC][64];
+  __shared__ __align__(16) float Bs[kCorrKC][128];
+  __shared__ float invA[64], invB[128];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int bh = blockIdx.z, b = bh / H, h = bh - b * H;
+  const int w1_0 = blockIdx.y * 64, w2_0 = blockIdx.x * 128;
+  const size_t HW1 = (size_t)H * W1, HW2 = (size_t)H * W2;
+  const float* a_base = f1 + (size_t)b * C * HW1 + (size_t)h * W1;
+  const float* b_base = f2 + (size_t)b * C * HW2 + (size_t)h * W2;
+
+  float acc[4][8];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+  float ss = 0.f;  // thread t<64: column t of A; 64<=t<192: column t-64 of B
+
+  for (int c0 = 0; c0 < C; c0 += kCorrKC) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int idx = tid + i * 256, k = idx >> 6, w = idx & 63;
+      As[k][w] = (c0 + k < C && w1_0 + w < W1) ? a_base[(size_t)(c0 + k) * HW1 + w1_0 + w] : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int idx = tid + i * 256, k = idx >> 7, w = idx & 127;
+      Bs[k][w] = (c0 + k < C && w2_0 + w < W2) ? b_base[(size_t)(c0 + k) * HW2 + w2_0 + w] : 0.f;
+    }
+    __syncthreads();
+    if (tid < 64) {
+#pragma unroll
+      for (int k = 0; k < kCorrKC; ++k) ss = fmaf(As[k][tid], As[k][tid], ss);
+    } else if (tid < 192) {
+#pragma unroll
+      for (int k = 0; k < kCorrKC; ++k) ss = fmaf(Bs[k][tid - 64], Bs[k][tid - 64], ss);
+    }
+#pragma unroll
+    for (int k = 0; k < kCorrKC; ++k) {
+      const float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[k][tx * 8]);
+      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[k][tx * 8 + 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w};
+      const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+  // F.normalize denominators: max(||x||, 1e-12)
+  if (tid < 64) invA[tid] = fmaxf(sqrtf(ss), 1e-12f);
+  else if (tid < 192) invB[tid - 64] = fmaxf(sqrtf(ss), 1e-12f);
+  __syncthreads();
+
+  const bool vec0 = (W2 & 3) == 0;
+  const int c2 = w2_0 + tx * 8;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int w1 = w1_0 + ty * 4 + i;
+    if (w1 >= W1) continue;
+    const size_t p = (size_t)bh * W1 + w1;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[j] = __fdiv_rn(__fdiv_rn(acc[i][j], invA[ty * 4 + i]), invB[tx * 8 + j]);
+    float* row = lv.p[0] + p * W2;
+    if (vec0) { store_run4<true>(row, c2, W2, v); store_run4<true>(row, c2 + 4, W2, v + 4); }
+    else      { store_run4<false>(row, c2, W2, v); store_run4<false>(row, c2 + 4, W2, v + 4); }
+    // pooled levels: mean of adjacent pairs of the previous level (floor length)
+    int n = 8, len = W2, col = c2;
+    for (int l = 1; l < L; ++l) {
+      n >>= 1; len >>= 1; col >>= 1;
+      if (n == 0) break;  // host guarantees L <= 4
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (j < n) v[j] = (v[2 * j] + v[2 * j + 1]) * 0.5f;
+      float* r = lv.p[l] + p * len;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (j < n && col + j < len) r[col + j] = v[j];
+    }
+  }
+}
+
+// =====================================================================================
+// Kernel 2b: (B,Cg,D,H,W) -> level l (B*H*W, D>>l, Cg).  Tile = 32 w x 8 d x all Cg.
+// Reads are 128-byte runs along W, writes are runs of (8>>l)*Cg floats per pixel.
+// =====================================================================================
+constexpr int kGeoTW = 32, kGeoTD = 8;
+
+template <int LVL>
+__device__ __forceinline__ float pooled(const float* t, int Cg, int jj, int c, int w) {
+  if constexpr (LVL == 0) {
+    return t[(jj * Cg + c) * (kGeoTW + 1) + w];
+  } else {
+    return (pooled<LVL - 1>(t, Cg, 2 * jj, c, w) + pooled<LVL - 1>(t, Cg, 2 * jj + 1, c, w)) * 0.5f;
+  }
+}
+
+template <int LVL>
+__device__ __forceinline__ void write_level(const float* t, float* out, int Cg, int D, int d0, size_t p0,
+                                            int wvalid, int tid) {
+  const int Dl = D >> LVL;
+  const int rows = kGeoTD >> LVL;  // pooled rows in this tile
+  const int run = rows * Cg;
+  const int dl0 = d0 >> LVL;
+  for (int i = tid; i < kGeoTW * run; i += 256) {
+    const int w = i / run, j = i - w * run;
+    const int jj = j / Cg, c = j - jj * Cg;
+    if (w < wvalid && dl0 + jj < Dl) out[((p0 + w) * Dl + dl0 + jj) * Cg + c] = pooled<LVL>(t, Cg, jj, c, w);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+geo_pyramid_kernel(const float* __restrict__ vol, LevelPtrs lv, int Cg, int D, int H, int W, int L) {
+  extern __shared__ float t[];  // [kGeoTD*Cg][kGeoTW+1], row index = dd*Cg + c
+  const int tid = threadIdx.x;
+  const int w0 = blockIdx.x * kGeoTW, d0 = blockIdx.y * kGeoTD;
+  const int bh = blockIdx.z, b = bh / H, h = bh - b * H;
+  const size_t HW = (size_t)H * W;
+  const float* src = vol + (size_t)b * Cg * D * HW + (size_t)h * W + w0;
+  const int n = Cg * kGeoTD * kGeoTW;
+  for (int i = tid; i < n; i += 256) {
+    const int w = i & (kGeoTW - 1);
+    const int r = i >> 5;  // = c*kGeoTD + dd
+    const int c = r >> 3, dd = r & 7;
+    float v = 0.f;
+    if (d0 + dd < D && w0 + w < W) v = src[((size_t)c * D + d0 + dd) * HW + w];
+    t[(dd * Cg + c) * (kGeoTW + 1) + w] = v;
+  }
+  __syncthreads();
+  const size_t p0 = (size_t)bh * W + w0;
+  const int wvalid = min(kGeoTW, W - w0);
+  write_level<0>(t, lv.p[0], Cg, D, d0, p0, wvalid, tid);
+  if (L > 1) write_level<1>(t, lv.p[1], Cg, D, d0, p0, wvalid, tid);
+  if (L > 2) write_level<2>(t, lv.p[2], Cg, D, d0, p0, wvalid, tid);
+  if (L > 3) write_level<3>(t, lv.p[3], Cg, D, d0, p0, wvalid, tid);
+}
+
+// =====================================================================================
+// Kernel 3: lookup.  One CTA = 32 consecutive pixels of one image row, all levels.
+//   phase 0: per (pixel, level): sampling positions exactly as the reference computes
+//            them (x -> 2x/(n-1)-1 -> ((.+1)/2)*(n-1), fp32, no FMA contraction), window
+//            base = floor of the first tap, per-tap fraction relative to base+k.
+//   phase 1: the (K+1) x Cg window of each pixel is ONE contiguous run in the
+//            (BHW, D_l, Cg) layout: coalesced loads into smem (row stride odd).
+//   phase 2: lane = pixel, warps stride over channels: 10 conflict-free smem reads ->
+//            9 outputs, stored straight to NCHW (128-byte coalesced along W).
+// =====================================================================================
+constexpr int kLkPix = 32;
+constexpr int kLkThreads = 256;
+constexpr int kLkKMax = 9;  // radius <= 4
+
+__device__ __forceinline__ float ref_unnormalised(float x, int n) {
+  // bilinear_sampler: xgrid = 2*x/(n-1) - 1 ; grid_sample(align_corners=True): ((g+1)/2)*(n-1)
+  const float nm1 = (float)(n - 1);
+  const float g = __fsub_rn(__fdiv_rn(__fmul_rn(2.f, x), nm1), 1.f);
+  return __fmul_rn(__fmul_rn(__fadd_rn(g, 1.f), 0.5f), nm1);
+}
+
+__global__ void __launch_bounds__(kLkThreads)
+lookup_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp, const float* __restrict__ coords,
+              float* __restrict__ out, int Cg, int D, int H, int W, int W2, int L, int r) {
+  extern __shared__ float sm[];
+  const int K = 2 * r + 1;
+  const int run = (K + 1) * Cg;      // floats per pixel window
+  const int PS = run | 1;            // odd pixel stride -> lane==pixel reads are conflict free
+  float* win = sm;                   // [32][PS]
+  float* cwin = win + kLkPix * PS;   // [32][K+2]
+  float* gfr = cwin + kLkPix * (K + 2);       // [32][kLkKMax] geo fractions
+  float* cfr = gfr + kLkPix * kLkKMax;        // [32][kLkKMax] corr fractions
+  int* gbase = reinterpret_cast<int*>(cfr + kLkPix * kLkKMax);  // [32]
+  int* cbase = gbase + kLkPix;                                   // [32]
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int w0 = blockIdx.x * kLkPix;
+  const int bh = blockIdx.y, b = bh / H, h = bh - b * H;
+  const size_t p0 = (size_t)bh * W + w0;
+  const int npix = min(kLkPix, W - w0);
+  const int CH = L * K * (Cg + 1);
+  const size_t HW = (size_t)H * W;
+  float* obase = out + ((size_t)b * CH * H + h) * W + w0;
+
+  for (int l = 0; l < L; ++l) {
+    const int Dl = D >> l, Wl = W2 >> l;
+    const float inv = 1.f / (float)(1 << l);
+    // ---- phase 0
+    if (tid < 2 * kLkPix) {
+      const int pix = tid & 31;
+      const bool is_cor = tid >= kLkPix;
+      if (pix < npix) {
+        const float d = disp[p0 + pix] * inv;  // exact: power-of-two scale
+        const float xc = is_cor ? __fsub_rn(coords[p0 + pix] * inv, d) : d;
+        const int n = is_cor ? Wl : Dl;
+        float* fr = (is_cor ? cfr : gfr) + pix * kLkKMax;
+        int base = 0;
+        for (int k = 0; k < K; ++k) {
+          const float ix = ref_unnormalised(__fadd_rn(xc, (float)(k - r)), n);
+          if (k == 0) {
+            // clamp so that int conversion is safe for wild disparities; any base outside
+            // [-(K+1), n] gives an all-zero window, exactly like the reference's padding
+            base = (int)fminf(fmaxf(floorf(ix), -1.0e6f), 1.0e6f);
+          }
+          fr[k] = ix - (float)(base + k);
+        }
+        (is_cor ? cbase : gbase)[pix] = base;
+      }
+    }
+    __syncthreads();
+    // ---- phase 1: windows -> smem (zero outside [0, n-1])
+    {
+      const float* g = geo.p[l];
+      for (int i = tid; i < kLkPix * run; i += kLkThreads) {
+        const int pix = i / run, j = i - pix * run;
+        float v = 0.f;
+        if (pix < npix) {
+          const int row = j / Cg;
+          const int dd = gbase[pix] + row;
+          if (dd >= 0 && dd < Dl) v = g[((p0 + pix) * Dl + dd) * Cg + (j - row * Cg)];
+        }
+        win[pix * PS + j] = v;
+      }
+      const float* cr = cor.p[l];
+      for (int i = tid; i < kLkPix * (K + 1); i += kLkThreads) {
+        const int pix = i / (K + 1), j = i - pix * (K + 1);
+        float v = 0.f;
+        if (pix < npix) {
+          const int x = cbase[pix] + j;
+          if (x >= 0 && x < Wl) v = cr[(p0 + pix) * Wl + x];
+        }
+        cwin[pix * (K + 2) + j] = v;
+      }
+    }
+    __syncthreads();
+    // ---- phase 2
+    if (lane < npix) {
+      float fg[kLkKMax], fc[kLkKMax];
+#pragma unroll
+      for (int k = 0; k < kLkKMax; ++k) {
+        fg[k] = (k < K) ? gfr[lane * kLkKMax + k] : 0.f;
+        fc[k] = (k < K) ? cfr[lane * kLkKMax + k] : 0.f;
+      }
+      float* ol = obase + (size_t)l * K * (Cg + 1) * HW + lane;
+      for (int c = warp; c <= Cg; c += kLkThreads / 32) {
+        const bool is_cor = (c == Cg);
+        const float* src = is_cor ? (cwin + lane * (K + 2)) : (win + lane * PS + c);
+        const int st = is_cor ? 1 : Cg;
+        float* o = ol + (size_t)c * K * HW;
+        float lo = src[0];
+#pragma unroll
+        for (int k = 0; k < kLkKMax; ++k) {
+          if (k < K) {
+            const float hi = src[(k + 1) * st];
+            const float f = is_cor ? fc[k] : fg[k];
+            o[(size_t)k * HW] = lo * (1.f - f) + hi * f;
+            lo = hi;
+          }
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
+
+static size_t lookup_smem_bytes(int Cg, int r) {
+  const int K = 2 * r + 1;
+  const int PS = ((K + 1) * Cg) | 1;
+  return (size_t)(kLkPix * PS + kLkPix * (K + 2) + 2 * kLkPix * kLkKMax + 2 * kLkPix) * sizeof(float);
+}
+
+}  // namespace fsb
+
+// -------------------------------------------------------------------------------------
+extern "C" int fsb_corr_pyramid(const float* f1, const float* f2, float* const* corr_levels, int B, int C,
+                                int H, int W1, int W2, int L, int precision, fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(f1 && f2 && corr_levels, FSB_ERR_ARG, "fsb_corr_pyramid: NULL pointer");
+  FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W1 > 0 && W2 > 0, FSB_ERR_ARG, "fsb_corr_pyramid: non-positive size");
+  FSB_REQUIRE(L >= 1 && L <= 4, FSB_ERR_SHAPE, "fsb_corr_pyramid: num_levels=%d outside [1,4]", L);
+  FSB_REQUIRE((W2 >> (L - 1)) >= 1, FSB_ERR_SHAPE, "fsb_corr_pyramid: W2=%d too small for %d levels", W2, L);
+  FSB_REQUIRE(precision == FSB_PREC_FP32, FSB_ERR_ARG,
+              "fsb_corr_pyramid: precision %d not available (only FSB_PREC_FP32)", precision);
+  FSB_REQUIRE((long long)B * H < 65536, FSB_ERR_SHAPE, "fsb_corr_pyramid: B*H=%lld >= 65536", (long long)B * H);
+  LevelPtrs lv{};
+  for (int l = 0; l < L; ++l) {
+    FSB_REQUIRE(corr_levels[l], FSB_ERR_ARG, "fsb_corr_pyramid: level %d pointer is NULL", l);
+    FSB_REQUIRE(aligned16(corr_levels[l]), FSB_ERR_ALIGN, "fsb_corr_pyramid: level %d not 16-byte aligned", l);
+    lv.p[l] = corr_levels[l];
+  }
+  dim3 grid(ceil_div(W2, 128), ceil_div(W1, 64), B * H);
+  corr_fp32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(f1, f2, lv, C, H, W1, W2, L);
+  FSB_CHECK_LAUNCH("fsb_corr_pyramid");
+  return FSB_OK;
+}
+
+extern "C" int fsb_geo_pyramid(const float* vol, float* const* geo_levels, int B, int Cg, int D, int H, int W,
+                               int L, fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(vol && geo_levels, FSB_ERR_ARG, "fsb_geo_pyramid: NULL pointer");
+  FSB_REQUIRE(B > 0 && Cg > 0 && D > 0 && H > 0 && W > 0, FSB_ERR_ARG, "fsb_geo_pyramid: non-positive size");
+  FSB_REQUIRE(L >= 1 && L <= 4, FSB_ERR_SHAPE, "fsb_geo_pyramid: num_levels=%d outside [1,4]", L);
+  FSB_REQUIRE((D >> (L - 1)) >= 1, FSB_ERR_SHAPE, "fsb_geo_pyramid: D=%d too small for %d levels", D, L);
+  FSB_REQUIRE((long long)B * H < 65536 && ceil_div(D, kGeoTD) < 65536, FSB_ERR_SHAPE, "fsb_geo_pyramid: grid too large");
+  LevelPtrs lv{};
+  for (int l = 0; l < L; ++l) {
+    FSB_REQUIRE(geo_levels[l], FSB_ERR_ARG, "fsb_geo_pyramid: level %d pointer is NULL", l);
+    lv.p[l] = geo_levels[l];
+  }
+  const size_t smem = (size_t)kGeoTD * Cg * (kGeoTW + 1) * sizeof(float);
+  FSB_REQUIRE(smem <= 227 * 1024, FSB_ERR_SHAPE, "fsb_geo_pyramid: Cg=%d needs %zu B shared memory", Cg, smem);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(geo_pyramid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_pyramid: cudaFuncSetAttribute");
+  }
+  dim3 grid(ceil_div(W, kGeoTW), ceil_div(D, kGeoTD), B * H);
+  geo_pyramid_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(vol, lv, Cg, D, H, W, L);
+  FSB_CHECK_LAUNCH("fsb_geo_pyramid");
+  return FSB_OK;
+}
+
+extern "C" int fsb_geo_lookup(float* const* geo_levels, float* const* corr_levels, const float* disp,
+                              const float* coords, void* out, int B, int Cg, int D, int H, int W, int W2, int L,
+                              int r, int out_layout, fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(geo_levels && corr_levels && disp && coords && out, FSB_ERR_ARG, "fsb_geo_lookup: NULL pointer");
+  FSB_REQUIRE(B > 0 && Cg > 0 && D > 0 && H > 0 && W > 0 && W2 > 0, FSB_ERR_ARG, "fsb_geo_lookup: non-positive size");
+  FSB_REQUIRE(L >= 1 && L <= 4, FSB_ERR_SHAPE, "fsb_geo_lookup: num_levels=%d outside [1,4]", L);
+  FSB_REQUIRE(r >= 1 && 2 * r + 1 <= kLkKMax, FSB_ERR_SHAPE, "fsb_geo_lookup: radius=%d outside [1,4]", r);
+  // a level of length 1 divides by zero in the reference's coordinate normalisation
+  FSB_REQUIRE((D >> (L - 1)) >= 2 && (W2 >> (L - 1)) >= 2, FSB_ERR_SHAPE,
+              "fsb_geo_lookup: coarsest level shorter than 2 (D=%d, W2=%d, L=%d)", D, W2, L);
+  FSB_REQUIRE(out_layout == 0, FSB_ERR_ARG, "fsb_geo_lookup: out_layout %d not available", out_layout);
+  FSB_REQUIRE((long long)B * H < 65536, FSB_ERR_SHAPE, "fsb_geo_lookup: B*H too large");
+  LevelPtrs g{}, c{};
+  for (int l = 0; l < L; ++l) {
+    FSB_REQUIRE(geo_levels[l] && corr_levels[l], FSB_ERR_ARG, "fsb_geo_lookup: level %d pointer is NULL", l);
+    g.p[l] = geo_levels[l];
+    c.p[l] = corr_levels[l];
+  }
+  const size_t smem = lookup_smem_bytes(Cg, r);
+  FSB_REQUIRE(smem <= 227 * 1024, FSB_ERR_SHAPE, "fsb_geo_lookup: Cg=%d r=%d needs %zu B shared memory", Cg, r, smem);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(lookup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_lookup: cudaFuncSetAttribute");
+  }
+  dim3 grid(ceil_div(W, kLkPix), B * H);
+  lookup_kernel<<<grid, kLkThreads, smem, (cudaStream_t)stream>>>(g, c, disp, coords, (float*)out, Cg, D, H, W,
+                                                                  W2, L, r);
+  FSB_CHECK_LAUNCH("fsb_geo_lookup");
+  return FSB_OK;
+}

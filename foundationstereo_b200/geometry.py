@@ -1,0 +1,66 @@
+"""Drop-in replacement for core/geometry.py's Combined_Geo_Encoding_Volume.
+
+Constructor and call signatures, attribute names and results follow
+core/geometry.py:17-77.  Construction runs kernel 2 (init correlation + pooled
+levels) and kernel 2b (volume transpose + pooled levels); each call runs kernel 3
+(all levels, both volumes, NCHW output) -- one launch and no host sync instead of
+the reference's ~70 launches and 2*L ``torch.unique`` syncs per iteration
+(core/utils/utils.py:49).
+"""
+from __future__ import annotations
+
+from typing import List, Optional
+
+import torch
+
+from . import _lib, ops
+
+
+class Combined_Geo_Encoding_Volume:
+    def __init__(self, init_fmap1: torch.Tensor, init_fmap2: torch.Tensor, geo_volume: torch.Tensor,
+                 num_levels: int = 2, dx: Optional[torch.Tensor] = None, precision: int = _lib.FSB_PREC_FP32):
+        if dx is None:
+            raise ValueError("dx (the (1,1,2r+1,1) offsets, core/foundation_stereo.py:177-179) is required")
+        K = dx.numel()
+        r = (K - 1) // 2
+        if K != 2 * r + 1 or r < 1:
+            raise ValueError(f"dx must hold the 2r+1 integer offsets -r..r, got {K} values")
+        if not dx.is_cuda:  # CPU tensor in the reference model: checking costs no device sync
+            want = torch.linspace(-r, r, K)
+            if not torch.equal(dx.reshape(-1).float().cpu(), want):
+                raise ValueError("dx must be linspace(-r, r, 2r+1): the kernel samples integer offsets")
+        self.num_levels = int(num_levels)
+        self.radius = r
+        self.dx = dx
+        self.precision = precision
+        B, Cg, D, H, W = geo_volume.shape
+        assert init_fmap1.shape[0] == B and init_fmap1.shape[2] == H and init_fmap1.shape[3] == W
+        self._shape = (B, Cg, D, H, W)
+        self._w2 = init_fmap2.shape[3]
+        # lookup layout: geo level l is (BHW, D>>l, Cg), corr level l is (BHW, W2>>l)
+        self.corr_levels: List[torch.Tensor] = list(ops.corr_pyramid(init_fmap1, init_fmap2, self.num_levels, precision))
+        self.geo_levels: List[torch.Tensor] = list(ops.geo_pyramid(geo_volume, self.num_levels))
+
+    # -- the reference's attribute names, as views in the reference's shapes -------------
+    @property
+    def geo_volume_pyramid(self) -> List[torch.Tensor]:
+        """[(BHW, Cg, 1, D_l)] like core/geometry.py:32-36 (non-contiguous views)."""
+        return [g.permute(0, 2, 1).unsqueeze(2) for g in self.geo_levels]
+
+    @property
+    def init_corr_pyramid(self) -> List[torch.Tensor]:
+        """[(BHW, 1, 1, W2_l)] like core/geometry.py:31-40."""
+        return [c[:, None, None, :] for c in self.corr_levels]
+
+    def __call__(self, disp: torch.Tensor, coords: torch.Tensor, low_memory: bool = False) -> torch.Tensor:
+        """(B,1,H,W) disparity, (B,H,W,1) x coordinates -> (B, L*K*(Cg+1), H, W) fp32.
+        ``low_memory`` is accepted and ignored like the reference (core/utils/utils.py:44)."""
+        return ops.geo_lookup(self.geo_levels, self.corr_levels, disp, coords, self.radius)
+
+    @staticmethod
+    def corr(fmap1: torch.Tensor, fmap2: torch.Tensor) -> torch.Tensor:
+        """(B,C,H,W1),(B,C,H,W2) -> (B,H,W1,1,W2) fp32 (core/geometry.py:68-77)."""
+        B, _, H, W1 = fmap1.shape
+        W2 = fmap2.shape[3]
+        (c,) = ops.corr_pyramid(fmap1, fmap2, 1, _lib.FSB_PREC_FP32)
+        return c.reshape(B, H, W1, 1, W2)

@@ -1,0 +1,56 @@
+"""The hot path end to end, as core/foundation_stereo.py:207-242 strings it together:
+volumes -> geometry-encoding volume -> `iters` x (lookup + update block).  This is the
+call `bench.py` times and the shape of what `patch.install` makes the reference model do.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Sequence, Tuple
+
+import torch
+
+from .geometry import Combined_Geo_Encoding_Volume
+from .submodule import build_combined_volume
+from .update import SelectiveUpdateBlock
+
+Tensor = torch.Tensor
+
+
+class StereoHotPath:
+    """Owns the update-block weights; `run` processes one batch of pairs.
+
+    Inputs are what the out-of-scope networks of the reference hand to the path:
+      fl, fr   (B,C,H,W)    1/4-res features            (core/foundation_stereo.py:201-204)
+      pl, pr   (B,12,H,W)   proj_cmb outputs            (:208-209)
+      volume   (B,28,D,H,W) filtered cost volume        (:213-215)
+      disp     (B,1,H,W)    initial disparity           (:218-220)
+      net, inp, att         hidden / context / attention lists at 1/4, 1/8, 1/16 (:222-227)
+    """
+
+    def __init__(self, state_dict: Dict[str, Tensor], max_disp: int, corr_levels: int = 2, corr_radius: int = 4,
+                 num_groups: int = 8, device: str | torch.device = "cuda"):
+        self.device = torch.device(device)
+        self.D = max_disp // 4
+        self.L = corr_levels
+        self.r = corr_radius
+        self.G = num_groups
+        self.update_block = SelectiveUpdateBlock(state_dict, self.device)
+        self.dx = torch.linspace(-corr_radius, corr_radius, 2 * corr_radius + 1).reshape(1, 1, -1, 1)
+
+    @torch.no_grad()
+    def run(self, fl: Tensor, fr: Tensor, pl: Tensor, pr: Tensor, volume: Tensor, disp: Tensor,
+            net: Sequence[Tensor], inp: Sequence[Tensor], att: Sequence[Tensor], iters: int
+            ) -> Tuple[Tensor, Tensor, Tensor]:
+        """-> (final 1/4-res disparity (B,1,H,W) fp32, mask features of the last step,
+        the (B,32,D,H,W) gwc+concat volume)."""
+        B, _, H, W = fl.shape
+        comb = build_combined_volume(fl, fr, pl, pr, self.D, self.G)
+        geo = Combined_Geo_Encoding_Volume(fl.float(), fr.float(), volume, num_levels=self.L, dx=self.dx)
+        coords = torch.arange(W, dtype=torch.float32, device=fl.device).reshape(1, 1, W, 1).repeat(B, H, 1, 1)
+        disp = disp.float()
+        net = [t for t in net]
+        mask = None
+        for _ in range(iters):
+            feat = geo(disp, coords)
+            net, mask, delta = self.update_block(net, inp, feat, disp, att)
+            disp = disp + delta.float()
+        return disp, mask, comb

@@ -1,0 +1,169 @@
+"""torch.library ops over the C ABI of libfsb200.so (kernels 1, 2, 2b, 3).
+
+Each op checks device / dtype / contiguity, allocates its outputs with PyTorch
+(so the caching allocator and stream semantics stay intact), and launches the
+kernel on torch's current CUDA stream through ctypes.  The ops are CUDA-only and
+inference-only: no autograd formula is registered, so differentiating through
+them raises instead of silently returning zeros.
+"""
+from __future__ import annotations
+
+from typing import List
+
+import torch
+
+from . import _lib
+from ._lib import check, level_array, lib
+
+_DTYPE = {torch.float32: _lib.FSB_F32, torch.float16: _lib.FSB_F16, torch.bfloat16: _lib.FSB_BF16}
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _need_cuda(*ts: torch.Tensor) -> None:
+    for t in ts:
+        if not t.is_cuda:
+            raise _lib.FsbError("foundationstereo_b200 ops run on CUDA tensors only (no CPU path)")
+
+
+# ----------------------------------------------------------------------------------------
+# kernel 1
+# ----------------------------------------------------------------------------------------
+@torch.library.custom_op("fsb200::gwc_volume", mutates_args=(), device_types="cuda")
+def gwc_volume(fl: torch.Tensor, fr: torch.Tensor, maxdisp: int, num_groups: int) -> torch.Tensor:
+    _need_cuda(fl, fr)
+    assert fl.shape == fr.shape and fl.dtype == fr.dtype and fl.dim() == 4
+    fl, fr = fl.contiguous(), fr.contiguous()
+    B, C, H, W = fl.shape
+    out = torch.empty((B, num_groups, maxdisp, H, W), dtype=fl.dtype, device=fl.device)
+    check(lib().fsb_volume_gwc_concat(fl.data_ptr(), fr.data_ptr(), None, None, out.data_ptr(), None,
+                                      B, C, 0, num_groups, H, W, maxdisp, _DTYPE[fl.dtype], _stream()))
+    return out
+
+
+@gwc_volume.register_fake
+def _(fl, fr, maxdisp, num_groups):
+    B, C, H, W = fl.shape
+    return fl.new_empty((B, num_groups, maxdisp, H, W))
+
+
+@torch.library.custom_op("fsb200::concat_volume", mutates_args=(), device_types="cuda")
+def concat_volume(pl: torch.Tensor, pr: torch.Tensor, maxdisp: int) -> torch.Tensor:
+    _need_cuda(pl, pr)
+    assert pl.shape == pr.shape and pl.dtype == pr.dtype and pl.dim() == 4
+    pl, pr = pl.contiguous(), pr.contiguous()
+    B, Cp, H, W = pl.shape
+    out = torch.empty((B, 2 * Cp, maxdisp, H, W), dtype=pl.dtype, device=pl.device)
+    check(lib().fsb_volume_gwc_concat(None, None, pl.data_ptr(), pr.data_ptr(), None, out.data_ptr(),
+                                      B, 0, Cp, 0, H, W, maxdisp, _DTYPE[pl.dtype], _stream()))
+    return out
+
+
+@concat_volume.register_fake
+def _(pl, pr, maxdisp):
+    B, Cp, H, W = pl.shape
+    return pl.new_empty((B, 2 * Cp, maxdisp, H, W))
+
+
+@torch.library.custom_op("fsb200::combined_volume", mutates_args=(), device_types="cuda")
+def combined_volume(fl: torch.Tensor, fr: torch.Tensor, pl: torch.Tensor, pr: torch.Tensor,
+                    maxdisp: int, num_groups: int) -> torch.Tensor:
+    """gwc and concat volumes written by ONE launch into one (B, G+2Cp, D, H, W) tensor --
+    what core/foundation_stereo.py:207-212 builds with two loops and a torch.cat."""
+    _need_cuda(fl, fr, pl, pr)
+    assert fl.dtype == fr.dtype == pl.dtype == pr.dtype
+    fl, fr, pl, pr = fl.contiguous(), fr.contiguous(), pl.contiguous(), pr.contiguous()
+    B, C, H, W = fl.shape
+    Cp = pl.shape[1]
+    if B != 1:
+        # the two halves are separate (B,*,D,H,W) tensors in the ABI; with B > 1 a shared
+        # allocation would interleave them per batch item, so build per item
+        return torch.cat([combined_volume(fl[b:b + 1], fr[b:b + 1], pl[b:b + 1], pr[b:b + 1], maxdisp, num_groups)
+                          for b in range(B)], 0)
+    out = torch.empty((1, num_groups + 2 * Cp, maxdisp, H, W), dtype=fl.dtype, device=fl.device)
+    gwc = out[:, :num_groups]
+    cat = out[:, num_groups:]
+    check(lib().fsb_volume_gwc_concat(fl.data_ptr(), fr.data_ptr(), pl.data_ptr(), pr.data_ptr(),
+                                      gwc.data_ptr(), cat.data_ptr(), 1, C, Cp, num_groups, H, W, maxdisp,
+                                      _DTYPE[fl.dtype], _stream()))
+    return out
+
+
+@combined_volume.register_fake
+def _(fl, fr, pl, pr, maxdisp, num_groups):
+    B, C, H, W = fl.shape
+    return fl.new_empty((B, num_groups + 2 * pl.shape[1], maxdisp, H, W))
+
+
+# ----------------------------------------------------------------------------------------
+# kernels 2 / 2b
+# ----------------------------------------------------------------------------------------
+@torch.library.custom_op("fsb200::corr_pyramid", mutates_args=(), device_types="cuda")
+def corr_pyramid(f1: torch.Tensor, f2: torch.Tensor, num_levels: int, precision: int) -> List[torch.Tensor]:
+    """levels l = 0..L-1 of the init correlation, each (B*H*W1, W2 >> l) fp32."""
+    _need_cuda(f1, f2)
+    f1 = f1.float().contiguous()
+    f2 = f2.float().contiguous()
+    B, C, H, W1 = f1.shape
+    W2 = f2.shape[3]
+    assert f2.shape[:3] == (B, C, H)
+    levels = [torch.empty((B * H * W1, W2 >> l), dtype=torch.float32, device=f1.device) for l in range(num_levels)]
+    check(lib().fsb_corr_pyramid(f1.data_ptr(), f2.data_ptr(), level_array(levels), B, C, H, W1, W2,
+                                 num_levels, precision, _stream()))
+    return levels
+
+
+@corr_pyramid.register_fake
+def _(f1, f2, num_levels, precision):
+    B, C, H, W1 = f1.shape
+    W2 = f2.shape[3]
+    return [f1.new_empty((B * H * W1, W2 >> l), dtype=torch.float32) for l in range(num_levels)]
+
+
+@torch.library.custom_op("fsb200::geo_pyramid", mutates_args=(), device_types="cuda")
+def geo_pyramid(volume: torch.Tensor, num_levels: int) -> List[torch.Tensor]:
+    """levels of the geometry volume in the lookup layout (B*H*W, D >> l, Cg) fp32."""
+    _need_cuda(volume)
+    volume = volume.float().contiguous()
+    B, Cg, D, H, W = volume.shape
+    levels = [torch.empty((B * H * W, D >> l, Cg), dtype=torch.float32, device=volume.device)
+              for l in range(num_levels)]
+    check(lib().fsb_geo_pyramid(volume.data_ptr(), level_array(levels), B, Cg, D, H, W, num_levels, _stream()))
+    return levels
+
+
+@geo_pyramid.register_fake
+def _(volume, num_levels):
+    B, Cg, D, H, W = volume.shape
+    return [volume.new_empty((B * H * W, D >> l, Cg), dtype=torch.float32) for l in range(num_levels)]
+
+
+# ----------------------------------------------------------------------------------------
+# kernel 3
+# ----------------------------------------------------------------------------------------
+@torch.library.custom_op("fsb200::geo_lookup", mutates_args=(), device_types="cuda")
+def geo_lookup(geo_levels: List[torch.Tensor], corr_levels: List[torch.Tensor], disp: torch.Tensor,
+               coords: torch.Tensor, radius: int) -> torch.Tensor:
+    _need_cuda(disp, coords)
+    L = len(geo_levels)
+    assert len(corr_levels) == L
+    B, _, H, W = disp.shape
+    disp = disp.float().contiguous()
+    coords = coords.float().contiguous()
+    N, D, Cg = geo_levels[0].shape
+    W2 = corr_levels[0].shape[1]
+    assert N == B * H * W and coords.numel() == N
+    K = 2 * radius + 1
+    out = torch.empty((B, L * K * (Cg + 1), H, W), dtype=torch.float32, device=disp.device)
+    check(lib().fsb_geo_lookup(level_array(geo_levels), level_array(corr_levels), disp.data_ptr(),
+                               coords.data_ptr(), out.data_ptr(), B, Cg, D, H, W, W2, L, radius, 0, _stream()))
+    return out
+
+
+@geo_lookup.register_fake
+def _(geo_levels, corr_levels, disp, coords, radius):
+    B, _, H, W = disp.shape
+    Cg = geo_levels[0].shape[2]
+    return disp.new_empty((B, len(geo_levels) * (2 * radius + 1) * (Cg + 1), H, W), dtype=torch.float32)

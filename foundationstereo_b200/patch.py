@@ -1,0 +1,71 @@
+"""Installs the B200 path into an UNCHANGED copy of the reference.
+
+The reference has no plugin API; its seam is Python name binding:
+  * core/foundation_stereo.py:19 star-imports build_gwc_volume / build_concat_volume,
+    :18 imports Combined_Geo_Encoding_Volume by name -> the names live in that module's
+    globals and are looked up at call time (:207, :210, :229);
+  * the update block is the attribute ``model.update_block`` (:137), called at :240; its
+    parameters must stay where they are so checkpoints load (scripts/run_demo.py:125).
+"""
+from __future__ import annotations
+
+import sys
+import types
+from typing import Optional
+
+from .geometry import Combined_Geo_Encoding_Volume
+from .submodule import build_concat_volume, build_gwc_volume
+from .update import SelectiveUpdateBlock
+
+_SAVED = {}
+
+
+def install(model=None, modules: Optional[list] = None) -> None:
+    """Rebind the three names in every loaded reference module that holds them and, if a
+    FoundationStereo ``model`` is given, route ``model.update_block.forward`` through
+    SelectiveUpdateBlock built from the module's own parameters."""
+    names = {
+        "build_gwc_volume": build_gwc_volume,
+        "build_concat_volume": build_concat_volume,
+        "Combined_Geo_Encoding_Volume": Combined_Geo_Encoding_Volume,
+    }
+    if modules is None:
+        modules = [m for n, m in list(sys.modules.items())
+                   if m is not None and n in ("core.foundation_stereo", "core.submodule", "core.geometry")]
+    for mod in modules:
+        for name, fn in names.items():
+            if hasattr(mod, name):
+                _SAVED.setdefault((mod.__name__, name), getattr(mod, name))
+                setattr(mod, name, fn)
+    if model is not None:
+        install_update_block(model.update_block)
+
+
+def install_update_block(update_block) -> None:
+    """Keep the nn.Module (and its state_dict keys) in place, replace only ``forward``.
+    The engine re-reads the parameters when their version counters change."""
+    state = {"engine": None, "versions": None}
+
+    def fast_forward(self, net, inp, corr, disp, att):
+        versions = tuple(p._version for p in self.parameters())
+        if state["engine"] is None or versions != state["versions"]:
+            dev = next(self.parameters()).device
+            state["engine"] = SelectiveUpdateBlock(self.state_dict(), dev)
+            state["versions"] = versions
+        return state["engine"](net, inp, corr, disp, att)
+
+    _SAVED.setdefault(("update_block", id(update_block)), update_block.forward)
+    update_block.forward = types.MethodType(fast_forward, update_block)
+
+
+def uninstall(model=None) -> None:
+    for (modname, name), fn in list(_SAVED.items()):
+        if modname == "update_block":
+            continue
+        mod = sys.modules.get(modname)
+        if mod is not None:
+            setattr(mod, name, fn)
+    if model is not None:
+        key = ("update_block", id(model.update_block))
+        if key in _SAVED:
+            model.update_block.forward = _SAVED.pop(key)

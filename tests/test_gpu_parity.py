@@ -1,0 +1,237 @@
+"""GPU parity tests: the CUDA path (through the C ABI of libfsb200.so) against
+ (a) the committed golden vectors produced by running the reference (tests/golden),
+ (b) the CPU oracle on seeded inputs at sizes the oracle finishes in seconds,
+ (c) size-independent properties at BASELINE.json's full sizes.
+
+Tolerances (BASELINE.json north_star): cost and geo-encoding volumes <= 1e-4 relative
+in fp32; pure copies bit-exact.  "relative" = max|a-b| / max|b| (conftest.rel_err).
+"""
+import pytest
+import torch
+
+import oracle
+from conftest import load_golden, rel_err
+
+pytestmark = pytest.mark.gpu
+
+TOL_FP32 = 1e-4
+
+
+@pytest.fixture(scope="module")
+def fsb():
+    import foundationstereo_b200 as f
+    assert f.lib().fsb_version() >= 100
+    return f
+
+
+def dev(t):
+    return t.cuda() if isinstance(t, torch.Tensor) else t
+
+
+# ------------------------------------------------------------------------------ kernel 1
+@pytest.mark.parametrize("name", ["volumes_f32", "volumes_f16", "volumes_narrow"])
+def test_volumes_golden(fsb, name):
+    g = load_golden(name)
+    n0 = fsb.launch_count()
+    gwc = fsb.build_gwc_volume(dev(g["fl"]), dev(g["fr"]), g["D"], g["G"])
+    cat = fsb.build_concat_volume(dev(g["pl"]), dev(g["pr"]), g["D"])
+    assert fsb.launch_count() == n0 + 2
+    assert gwc.dtype == g["gwc"].dtype and gwc.shape == g["gwc"].shape and gwc.is_contiguous()
+    assert torch.equal(cat.cpu(), g["cat"])  # pure copy: bit exact
+    tol = TOL_FP32 if gwc.dtype == torch.float32 else 2e-3  # fp16 storage: half an ulp of 1.0 is 4.9e-4
+    assert rel_err(gwc.cpu(), g["gwc"]) <= tol
+    comb = fsb.build_combined_volume(dev(g["fl"]), dev(g["fr"]), dev(g["pl"]), dev(g["pr"]), g["D"], g["G"])
+    assert torch.equal(comb, torch.cat([gwc, cat], 1))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(1, 128, 40, 160, 48), (2, 224, 6, 100, 30), (1, 160, 5, 37, 21)])
+def test_volumes_vs_oracle(fsb, dtype, shape):
+    B, C, H, W, D = shape
+    x = oracle.make_inputs(B=B, C=C, H=H, W=W, D=D, seed=7, with_volume=False)
+    fl, fr, pl, pr = (x[k].to(dtype) for k in ("fl", "fr", "pl", "pr"))
+    want_gwc = oracle.gwc_volume(fl, fr, D, 8)
+    want_cat = oracle.concat_volume(pl, pr, D)
+    gwc = fsb.build_gwc_volume(fl.cuda(), fr.cuda(), D, 8)
+    cat = fsb.build_concat_volume(pl.cuda(), pr.cuda(), D)
+    assert torch.equal(cat.cpu(), want_cat)
+    tol = {torch.float32: TOL_FP32, torch.float16: 2e-3, torch.bfloat16: 1.6e-2}[dtype]
+    assert rel_err(gwc.float().cpu(), want_gwc.float()) <= tol
+
+
+def test_volumes_full_size_properties(fsb):
+    """480x640, max_disp 416 (BASELINE config 2): zero region, d = 0 plane, shift structure."""
+    B, C, H, W, D, G = 1, 128, 120, 160, 104, 8
+    x = oracle.make_inputs(B=B, C=C, H=H, W=W, D=D, seed=1, with_volume=False)
+    fl, fr, pl, pr = (x[k].cuda() for k in ("fl", "fr", "pl", "pr"))
+    gwc = fsb.build_gwc_volume(fl, fr, D, G)
+    cat = fsb.build_concat_volume(pl, pr, D)
+    w = torch.arange(W, device="cuda")
+    d = torch.arange(D, device="cuda")
+    invalid = (w[None, :] < d[:, None])[None, None, :, None, :]
+    assert gwc.masked_select(invalid.expand_as(gwc)).abs().max().item() == 0.0
+    assert cat[:, 12:].masked_select(invalid.expand_as(cat[:, 12:])).abs().max().item() == 0.0
+    assert torch.equal(cat[:, :12], pl[:, :, None].expand(B, 12, D, H, W))
+    for dd in (0, 1, 57, 103):
+        assert torch.equal(cat[:, 12:, dd, :, dd:], pr[..., : W - dd])
+    ln = torch.nn.functional.normalize(fl.reshape(B, G, C // G, H, W), dim=2)
+    rn = torch.nn.functional.normalize(fr.reshape(B, G, C // G, H, W), dim=2)
+    for dd in (0, 33, 103):
+        want = (ln[..., dd:] * rn[..., : W - dd]).sum(2)
+        assert rel_err(gwc[:, :, dd, :, dd:], want) <= TOL_FP32
+    # |cosine| <= 1
+    assert gwc.abs().max().item() <= 1.0 + 1e-5
+
+
+def test_volume_rejects_bad_arguments(fsb):
+    fl = torch.zeros(1, 30, 4, 8, device="cuda")
+    with pytest.raises(Exception):
+        fsb.build_gwc_volume(fl, fl, 4, 8)  # 30 % 8 != 0
+    with pytest.raises(Exception):
+        fsb.build_gwc_volume(torch.zeros(1, 32, 4, 8), torch.zeros(1, 32, 4, 8), 4, 8)  # CPU tensors
+
+
+# ------------------------------------------------------------------------- kernels 2, 2b, 3
+@pytest.mark.parametrize("name", ["geo_odd", "geo_std", "geo_l4"])
+def test_geo_golden(fsb, name):
+    g = load_golden(name)
+    L, r = g["L"], g["r"]
+    dx = torch.linspace(-r, r, 2 * r + 1).reshape(1, 1, -1, 1)
+    n0 = fsb.launch_count()
+    vol = fsb.Combined_Geo_Encoding_Volume(dev(g["f1"]), dev(g["f2"]), dev(g["volume"]), num_levels=L, dx=dx)
+    out = vol(dev(g["disp"]), dev(g["coords"]))
+    assert fsb.launch_count() == n0 + 3  # corr+pyramid, transpose+pyramid, lookup
+    for l in range(L):
+        got_geo = vol.geo_volume_pyramid[l].squeeze(2).cpu()
+        assert got_geo.shape == g[f"geo{l}"].shape
+        assert torch.equal(got_geo, g[f"geo{l}"])  # copy + exact halving
+        got_cor = vol.init_corr_pyramid[l].reshape(g[f"corr{l}"].shape).cpu()
+        assert rel_err(got_cor, g[f"corr{l}"]) <= TOL_FP32
+    assert out.shape == g["lookup"].shape and out.is_contiguous()
+    assert rel_err(out.cpu(), g["lookup"]) <= TOL_FP32
+    c = fsb.Combined_Geo_Encoding_Volume.corr(dev(g["f1"]), dev(g["f2"]))
+    B, _, H, W = g["f1"].shape
+    assert c.shape == (B, H, W, 1, W)
+    assert rel_err(c.reshape(B * H * W, W).cpu(), g["corr0"]) <= TOL_FP32
+
+
+@pytest.mark.parametrize("cfg", [
+    # B, C, H, W, D, Cg, L, r
+    (1, 128, 24, 160, 48, 28, 2, 4),
+    (2, 224, 5, 78, 26, 28, 3, 4),
+    (1, 64, 3, 130, 104, 28, 4, 2),
+    (1, 32, 7, 33, 17, 5, 1, 1),
+])
+def test_geo_vs_oracle(fsb, cfg):
+    B, C, H, W, D, Cg, L, r = cfg
+    x = oracle.make_inputs(B=B, C=C, H=H, W=W, D=D, Cg=Cg, seed=3)
+    want = oracle.GeoEncodingVolume(x["fl"], x["fr"], x["volume"], L, r)
+    dx = torch.linspace(-r, r, 2 * r + 1).reshape(1, 1, -1, 1)
+    vol = fsb.Combined_Geo_Encoding_Volume(x["fl"].cuda(), x["fr"].cuda(), x["volume"].cuda(), num_levels=L, dx=dx)
+    for l in range(L):
+        assert torch.equal(vol.geo_volume_pyramid[l].squeeze(2).cpu(), want.geo_levels[l])
+        assert rel_err(vol.corr_levels[l].cpu(), want.corr_levels[l]) <= TOL_FP32
+    out = vol(x["disp"].cuda(), x["coords"].cuda())
+    ref = want(x["disp"], x["coords"])
+    assert rel_err(out.cpu(), ref) <= TOL_FP32
+
+
+def test_geo_full_size_properties(fsb):
+    """Config 2 sizes.  With integer disparities the lookup is an exact gather, and the
+    pooled levels are exact means, so the checks below are bit-level where they can be."""
+    B, C, H, W, D, Cg, L, r = 1, 128, 120, 160, 104, 28, 2, 4
+    K = 2 * r + 1
+    g = torch.Generator().manual_seed(5)
+    f1 = torch.relu(torch.randn(B, C, H, W, generator=g)).cuda()
+    f2 = torch.relu(torch.randn(B, C, H, W, generator=g)).cuda()
+    volume = torch.randn(B, Cg, D, H, W, generator=g).cuda()
+    dx = torch.linspace(-r, r, K).reshape(1, 1, -1, 1)
+    vol = fsb.Combined_Geo_Encoding_Volume(f1, f2, volume, num_levels=L, dx=dx)
+    # pyramid structure
+    g0 = vol.geo_levels[0]
+    assert torch.equal(g0.reshape(B, H, W, D, Cg).permute(0, 4, 3, 1, 2), volume)
+    assert torch.equal(vol.geo_levels[1], (g0[:, 0::2] + g0[:, 1::2]) * 0.5)
+    c0 = vol.corr_levels[0]
+    assert torch.equal(vol.corr_levels[1], (c0[:, 0::2] + c0[:, 1::2]) * 0.5)
+    # correlation: symmetric inputs give unit diagonal; compare with a torch fp32 einsum
+    a = torch.nn.functional.normalize(f1, dim=1)
+    b = torch.nn.functional.normalize(f2, dim=1)
+    want = torch.einsum("bchw,bchv->bhwv", a, b).reshape(B * H * W, W)
+    assert rel_err(c0, want) <= TOL_FP32
+    # integer, in-range disparity: exact gather of level 0 and exact means of level 1
+    disp = torch.randint(r, D - r - 1, (B, 1, H, W), generator=g).float().cuda()
+    disp = 2 * torch.div(disp, 2, rounding_mode="floor")  # even -> level-1 positions are integers too
+    coords = torch.arange(W, dtype=torch.float32, device="cuda").reshape(1, 1, W, 1).repeat(B, H, 1, 1)
+    out = vol(disp, coords)
+    assert out.shape == (B, L * K * (Cg + 1), H, W)
+    idx = (disp.reshape(-1, 1).long() + torch.arange(-r, r + 1, device="cuda")[None, :])  # (N,K)
+    gat = torch.gather(g0.permute(0, 2, 1), 2, idx[:, None, :].expand(-1, Cg, -1))  # (N,Cg,K)
+    got = out[:, : Cg * K].permute(0, 2, 3, 1).reshape(-1, Cg, K)
+    # the reference's coordinate round trip (2x/(n-1)-1 and back) perturbs integer positions by
+    # ~1e-6, so compare with a tolerance scaled to the data, not bitwise
+    assert rel_err(got, gat) <= TOL_FP32
+    # wildly out-of-range disparities give exact zeros (zeros padding), never NaN
+    wild = torch.full((B, 1, H, W), 1.0e7, device="cuda")
+    z = vol(wild, coords)
+    assert torch.isfinite(z).all() and z[:, : Cg * K].abs().max().item() == 0.0
+    neg = torch.full((B, 1, H, W), -1.0e7, device="cuda")
+    z = vol(neg, coords)
+    assert torch.isfinite(z).all() and z.abs().max().item() == 0.0
+
+
+# -------------------------------------------------------------------------- update block
+TOL_F16 = 2e-2  # fp16 operands / fp32 accumulate against the fp32 oracle (the reference's own
+                # autocast region, core/foundation_stereo.py:239, has the same arithmetic)
+
+
+def test_update_block_golden(fsb):
+    g = load_golden("update_step")
+    p = oracle.make_update_block_params(seed=g["seed_params"], corr_levels=2, corr_radius=4, volume_dim=28)
+    x = oracle.make_inputs(B=1, C=32, H=8, W=12, D=10, Cg=28, seed=g["seed_inputs"])
+    ub = fsb.SelectiveUpdateBlock(p, "cuda")
+    net = [t.cuda() for t in x["net"]]
+    handle = net
+    out_net, mask, delta = ub(net, [t.cuda() for t in x["inp"]], g["corr"].cuda(), x["disp"].cuda(),
+                              [t.cuda() for t in x["att"]])
+    assert out_net is handle  # in-place list contract of core/update.py:143-159
+    for i in range(3):
+        assert rel_err(out_net[i].cpu(), g[f"net{i}"]) <= TOL_F16
+    assert rel_err(mask.cpu(), g["mask"]) <= TOL_F16
+    assert rel_err(delta.cpu(), g["delta"]) <= TOL_F16
+
+
+def test_update_block_vs_oracle_midsize(fsb):
+    H, W = 40, 56
+    p = oracle.make_update_block_params(seed=1)
+    x = oracle.make_inputs(B=2, C=16, H=H, W=W, D=24, Cg=28, seed=9)
+    with torch.no_grad():
+        geo = oracle.GeoEncodingVolume(x["fl"], x["fr"], x["volume"], 2, 4)
+        corr = geo(x["disp"], x["coords"])
+        want_net, want_mask, want_delta = oracle.update_block(p, [t.clone() for t in x["net"]], x["inp"], corr,
+                                                              x["disp"], x["att"])
+    ub = fsb.SelectiveUpdateBlock(p, "cuda")
+    net, mask, delta = ub([t.cuda() for t in x["net"]], [t.cuda() for t in x["inp"]], corr.cuda(), x["disp"].cuda(),
+                          [t.cuda() for t in x["att"]])
+    for i in range(3):
+        assert rel_err(net[i].cpu(), want_net[i]) <= TOL_F16
+    assert rel_err(mask.cpu(), want_mask) <= TOL_F16
+    assert rel_err(delta.cpu(), want_delta) <= TOL_F16
+
+
+def test_hot_path_refinement_loop(fsb):
+    """The whole path, free running: final disparity within 0.05 px mean abs of the fp32 oracle
+    (north_star's end-to-end tolerance).  Random weights are not contractive, so the last
+    disparity-head conv is scaled (oracle.params delta_scale)."""
+    H, W, D, iters = 32, 48, 24, 8
+    p = oracle.make_update_block_params(seed=2, delta_scale=0.25)
+    x = oracle.make_inputs(B=1, C=32, H=H, W=W, D=D, Cg=28, seed=4)
+    with torch.no_grad():
+        geo = oracle.GeoEncodingVolume(x["fl"], x["fr"], x["volume"], 2, 4)
+        want, _, _ = oracle.refine(p, geo, x["net"], x["inp"], x["att"], x["disp"], iters)
+    hp = fsb.StereoHotPath(p, max_disp=4 * D)
+    c = lambda t: t.cuda()
+    got, mask, comb = hp.run(c(x["fl"]), c(x["fr"]), c(x["pl"]), c(x["pr"]), c(x["volume"]), c(x["disp"]),
+                             [c(t) for t in x["net"]], [c(t) for t in x["inp"]], [c(t) for t in x["att"]], iters)
+    assert comb.shape == (1, 32, D, H, W)
+    mad = (got.cpu() - want).abs().mean().item()
+    assert mad <= 0.05, mad
