@@ -25,28 +25,44 @@ class FsbError(RuntimeError):
 
 
 class ConvSrc(ctypes.Structure):
-    _fields_ = [("ptr", c_void_p), ("C", c_int), ("ldc", c_int)]
+    """fsb_conv_src (include/fsb200.h)"""
+    _fields_ = [("ptr", c_void_p), ("C", c_int)]
+
+
+class ConvSeg(ctypes.Structure):
+    """fsb_conv_seg"""
+    _fields_ = [("ksize", c_int), ("nsrc", c_int), ("src", c_int * FSB_MAX_SRC)]
 
 
 class ConvArgs(ctypes.Structure):
+    """fsb_conv_args -- field order and types follow include/fsb200.h exactly"""
     _fields_ = [
         ("src", ConvSrc * FSB_MAX_SRC),
         ("nsrc", c_int),
         ("B", c_int), ("H", c_int), ("W", c_int),
-        ("ksize", c_int),
+        ("seg", ConvSeg * 2),
+        ("nseg", c_int),
         ("weight", c_void_p),
         ("bias", c_void_p),
+        ("rows", c_int),
         ("Cout", c_int),
+        ("block_n", c_int),
+        ("stages", c_int),
         ("epilogue", c_int),
         ("out", c_void_p),
         ("ld_out", c_int),
-        ("h", c_void_p),
-        ("att", c_void_p),
-        ("z_l", c_void_p), ("rh_l", c_void_p), ("z_s", c_void_p), ("rh_s", c_void_p),
-        ("h_out", c_void_p),
-        ("aux", c_void_p),
-        ("ld_aux", c_int),
+        ("ch_off", c_int),
         ("out_f32", c_void_p),
+        ("out_scale", c_float),
+        ("res", c_void_p),
+        ("ld_res", c_int),
+        ("gamma", c_void_p),
+        ("h32", c_void_p),
+        ("att", c_void_p),
+        ("z_l", c_void_p), ("z_s", c_void_p), ("rh_l", c_void_p), ("rh_s", c_void_p),
+        ("h32_out", c_void_p),
+        ("h16_out", c_void_p),
+        ("hidden", c_int),
     ]
 
 
@@ -59,6 +75,15 @@ _PROTOS = {
     "fsb_geo_pyramid": (c_int, [c_void_p, POINTER(c_void_p)] + [c_int] * 6 + [c_void_p]),
     "fsb_geo_lookup": (c_int, [POINTER(c_void_p), POINTER(c_void_p), c_void_p, c_void_p, c_void_p]
                        + [c_int] * 9 + [c_void_p]),
+    "fsb_conv_args_size": (c_size_t, []),
+    "fsb_conv2d_nhwc": (c_int, [POINTER(ConvArgs), c_int, c_void_p]),
+    "fsb_nchw_to_nhwc": (c_int, [c_void_p] * 3 + [c_int] * 6 + [c_void_p]),
+    "fsb_nhwc_to_nchw": (c_int, [c_void_p] * 2 + [c_int] * 4 + [c_void_p]),
+    "fsb_pool2x_nhwc": (c_int, [c_void_p] * 2 + [c_int] * 5 + [c_void_p]),
+    "fsb_resize_nhwc": (c_int, [c_void_p] * 2 + [c_int] * 7 + [c_void_p]),
+    "fsb_conv7x7_c1": (c_int, [c_void_p] * 4 + [c_int] * 2 + [c_void_p] + [c_int] * 6 + [c_void_p]),
+    "fsb_dwconv7x7_nhwc": (c_int, [c_void_p] * 4 + [c_int] * 5 + [c_void_p]),
+    "fsb_axpy_f32": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
 }
 
 _lib = None
@@ -77,6 +102,9 @@ def lib() -> ctypes.CDLL:
             fn = getattr(L, name)
             fn.restype = res
             fn.argtypes = args
+        if L.fsb_conv_args_size() != ctypes.sizeof(ConvArgs):
+            raise FsbError(f"fsb_conv_args is {L.fsb_conv_args_size()} bytes in {LIB_PATH} but "
+                           f"{ctypes.sizeof(ConvArgs)} in the ctypes mirror: rebuild the library")
         _lib = L
     return _lib
 

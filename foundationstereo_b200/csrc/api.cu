@@ -18,4 +18,5 @@ extern "C" {
 int fsb_version(void) { return FSB_VERSION; }
 const char* fsb_last_error(void) { return fsb::g_err; }
 uint64_t fsb_launch_count(void) { return fsb::g_launches; }
+size_t fsb_conv_args_size(void) { return sizeof(fsb_conv_args); }
 }

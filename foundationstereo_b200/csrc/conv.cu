@@ -1,0 +1,619 @@
+// Kernel 4: 3x3 / 1x1 convolution of the update block as a tcgen05 implicit GEMM.
+//
+// Replaces the nn.Conv2d / nn.Linear calls of BasicSelectiveMultiUpdateBlock
+// (core/update.py:20-159, core/submodule.py:565-591) together with the elementwise work
+// that follows them (ReLU, GELU, layer scale + residual, and the sigmoid / tanh / blend of
+// RaftConvGRU + SelectiveConvGRU, core/update.py:90-95,112-119).
+//
+// GEMM view:  D[pixel, cout] = sum_{tap, cin} X[pixel + tap, cin] * W[cout, tap, cin]
+//   M tile  = 128 pixels = a TH x TW patch of one image (TH*TW = 128)
+//   K step  = one tap x 64 input channels: ONE 4-D TMA box (64 ch, TW, TH, 1) of the NHWC
+//             activation tensor at the shifted coordinate (x0+dx, y0+dy).  The box lands in
+//             shared memory as 128 rows x 128 B with the 128-byte swizzle, which is exactly
+//             the K-major operand layout tcgen05.mma wants; out-of-image rows/columns are
+//             zero-filled by the TMA unit, which is the convolution's zero padding.  No
+//             im2col buffer exists anywhere.
+//   N tile  = block_n output channels; weights are pre-packed [rows][Ktot] K-major, one 2-D
+//             TMA box (64, block_n) per K step.
+//   D       = fp32 accumulators in TMEM (up to two: the 3x3 "large" and 1x1 "small" GRU).
+//
+// Warp roles (192 threads): warp 0 = TMA producer (one elected lane), warp 1 = TMEM
+// allocator + MMA issuer (one elected lane), warps 2..5 = epilogue (tcgen05.ld, one pixel
+// per thread, 32 output channels per load).  Stages are handed over with mbarriers:
+// full[s] (TMA -> MMA, transaction bytes), empty[s] (tcgen05.commit -> TMA), accum
+// (last commit -> epilogue).
+#include "common.cuh"
+
+#include <cuda.h>
+
+namespace fsb {
+
+constexpr int kConvThreads = 192;
+constexpr int kMaxSteps = 112;
+constexpr int kBM = 128;
+constexpr int kBK = 64;                      // 16-bit elements per K step (128 B)
+constexpr int kATileBytes = kBM * kBK * 2;   // 16 KB
+
+// K-step word: bits 0-1 source, 2-3 dy+1, 4-5 dx+1, 6 accumulator, 8-15 channel chunk of the source
+__host__ __device__ inline uint32_t make_step(int src, int dy, int dx, int acc, int chunk) {
+  return (uint32_t)src | ((uint32_t)(dy + 1) << 2) | ((uint32_t)(dx + 1) << 4) | ((uint32_t)acc << 6) |
+         ((uint32_t)chunk << 8);
+}
+
+struct alignas(64) ConvParams {
+  CUtensorMap amap[FSB_MAX_SRC];
+  CUtensorMap wmap;
+  uint32_t steps[kMaxSteps];
+  int nsteps;
+  int H, W, tiles_x, tiles_y, tw_log2;
+  int BN, nacc, tmem_cols, stages;
+  uint32_t idesc;
+  int rows, Cout;
+  const float* bias;
+  void* out;
+  int ld_out, ch_off;
+  float* out_f32;
+  float out_scale;
+  const void* res;
+  int ld_res;
+  const float* gamma;
+  const float* h32;
+  const float* att;
+  void* z_l;
+  void* z_s;
+  void* rh_l;
+  void* rh_s;
+  float* h32_out;
+  void* h16_out;
+  int hidden;
+};
+
+// ------------------------------------------------------------------------------------ PTX
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// A wait that cannot hang the GPU: after ~2 s of SM clocks the kernel traps (a pipeline bug
+// then shows up as a launch failure instead of a dead box).
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000ll) __trap();
+  }
+}
+
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
+                                            int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major operand tile, 128-byte swizzle: rows of 128 B, 8-row atoms of 1024 B (SBO), descriptor
+// version 1 (Blackwell), layout type 2 (SWIZZLE_128B).  `addr` must be 1024-byte aligned; stepping
+// 16 elements along K inside the atom adds 32 B to the start address.
+__device__ __forceinline__ uint64_t umma_desc_k128(uint32_t addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr & 0x3FFFFu) >> 4);  // start address, bits [0,14)
+  d |= (uint64_t)1 << 16;                   // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;         // stride byte offset between 8-row atoms
+  d |= (uint64_t)1 << 46;                   // descriptor version
+  d |= (uint64_t)2 << 61;                   // SWIZZLE_128B
+  return d;
+}
+
+// ------------------------------------------------------------------------------- epilogue math
+__device__ __forceinline__ float sigmoid_f(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+__device__ __forceinline__ float tanh_f(float x) {
+  const float e = __expf(2.f * x);  // inf for large x -> 1 - 0; 0 for very negative x -> -1
+  return 1.f - __fdividef(2.f, e + 1.f);
+}
+__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752f)); }
+
+template <typename T> __device__ __forceinline__ uint32_t pack2(float a, float b);
+template <> __device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+template <> __device__ __forceinline__ uint32_t pack2<__nv_bfloat16>(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+template <typename T> __device__ __forceinline__ float2 unpack2(uint32_t v);
+template <> __device__ __forceinline__ float2 unpack2<__half>(uint32_t v) {
+  return __half22float2(*reinterpret_cast<__half2*>(&v));
+}
+template <> __device__ __forceinline__ float2 unpack2<__nv_bfloat16>(uint32_t v) {
+  return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&v));
+}
+
+// 32 consecutive channels of one pixel, 16-bit storage: 64 B = 4 x 16 B
+template <typename T> __device__ __forceinline__ void store32(T* dst, const float (&f)[32]) {
+  uint4* d = reinterpret_cast<uint4*>(dst);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    uint4 u;
+    u.x = pack2<T>(f[8 * q + 0], f[8 * q + 1]);
+    u.y = pack2<T>(f[8 * q + 2], f[8 * q + 3]);
+    u.z = pack2<T>(f[8 * q + 4], f[8 * q + 5]);
+    u.w = pack2<T>(f[8 * q + 6], f[8 * q + 7]);
+    d[q] = u;
+  }
+}
+template <typename T> __device__ __forceinline__ void load32(const T* src, float (&f)[32]) {
+  const uint4* s = reinterpret_cast<const uint4*>(src);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const uint4 u = s[q];
+    float2 a = unpack2<T>(u.x), b = unpack2<T>(u.y), c = unpack2<T>(u.z), d = unpack2<T>(u.w);
+    f[8 * q + 0] = a.x; f[8 * q + 1] = a.y; f[8 * q + 2] = b.x; f[8 * q + 3] = b.y;
+    f[8 * q + 4] = c.x; f[8 * q + 5] = c.y; f[8 * q + 6] = d.x; f[8 * q + 7] = d.y;
+  }
+}
+__device__ __forceinline__ void load32f(const float* src, float (&f)[32]) {
+  const float4* s = reinterpret_cast<const float4*>(src);
+#pragma unroll
+  for (int q = 0; q < 8; ++q) {
+    const float4 u = s[q];
+    f[4 * q + 0] = u.x; f[4 * q + 1] = u.y; f[4 * q + 2] = u.z; f[4 * q + 3] = u.w;
+  }
+}
+__device__ __forceinline__ void store32f(float* dst, const float (&f)[32]) {
+  float4* d = reinterpret_cast<float4*>(dst);
+#pragma unroll
+  for (int q = 0; q < 8; ++q) d[q] = make_float4(f[4 * q + 0], f[4 * q + 1], f[4 * q + 2], f[4 * q + 3]);
+}
+
+// ------------------------------------------------------------------------------------ kernel
+template <typename T, int EPI>
+__global__ void __launch_bounds__(kConvThreads)
+conv_umma_kernel(const __grid_constant__ ConvParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bars[2 * 8 + 1];
+  __shared__ uint32_t tmem_slot;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t stage_bytes = kATileBytes + (uint32_t)p.BN * (kBK * 2);
+  const int S = p.stages;
+  const uint32_t bar_full = smem_u32(&bars[0]);
+  const uint32_t bar_empty = smem_u32(&bars[8]);
+  const uint32_t bar_accum = smem_u32(&bars[16]);
+
+  // tile coordinates
+  int t = blockIdx.x;
+  const int txi = t % p.tiles_x;
+  t /= p.tiles_x;
+  const int tyi = t % p.tiles_y;
+  const int b = t / p.tiles_y;
+  const int TW = 1 << p.tw_log2, TH = kBM >> p.tw_log2;
+  const int x0 = txi * TW, y0 = tyi * TH;
+  const int nt = blockIdx.y;
+  const int n0 = nt * p.BN;
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, 1);
+    }
+    mbar_init(bar_accum, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    tma_prefetch_desc(&p.wmap);
+    tma_prefetch_desc(&p.amap[0]);
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
+                 "r"((uint32_t)p.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer
+    if (lane == 0) {
+      for (int i = 0; i < p.nsteps; ++i) {
+        const int s = i % S;
+        if (i >= S) mbar_wait(bar_empty + 8 * s, ((i / S) - 1) & 1);
+        const uint32_t st = p.steps[i];
+        const int src = st & 3, dy = (int)((st >> 2) & 3) - 1, dx = (int)((st >> 4) & 3) - 1, chunk = (st >> 8) & 0xff;
+        const uint32_t a_dst = smem_base + s * stage_bytes;
+        mbar_expect_tx(bar_full + 8 * s, stage_bytes);
+        tma_load_4d(a_dst, &p.amap[src], bar_full + 8 * s, chunk * kBK, x0 + dx, y0 + dy, b);
+        tma_load_2d(a_dst + kATileBytes, &p.wmap, bar_full + 8 * s, i * kBK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    // ====================================================================== MMA issuer
+    if (lane == 0) {
+      uint32_t started = 0;  // bit a: accumulator a already holds a partial sum
+      for (int i = 0; i < p.nsteps; ++i) {
+        const int s = i % S;
+        mbar_wait(bar_full + 8 * s, (i / S) & 1);
+        tc_fence_after();
+        const int acc = (p.steps[i] >> 6) & 1;
+        const uint32_t a_addr = smem_base + s * stage_bytes;
+        const uint64_t adesc = umma_desc_k128(a_addr);
+        const uint64_t bdesc = umma_desc_k128(a_addr + kATileBytes);
+        const uint32_t d = tmem_base + (uint32_t)(acc * p.BN);
+#pragma unroll
+        for (int k = 0; k < kBK / 16; ++k) {
+          // +32 B along K inside the swizzle atom = +2 in the (addr >> 4) field
+          umma_f16(d, adesc + 2 * k, bdesc + 2 * k, p.idesc, ((started >> acc) & 1) | (k > 0));
+        }
+        started |= 1u << acc;
+        umma_commit(bar_empty + 8 * s);  // frees the stage when these MMAs have read it
+      }
+      umma_commit(bar_accum);  // all MMAs done -> accumulators complete
+    }
+  } else {
+    // ======================================================================== epilogue
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int r = q * 32 + lane;
+    const int ty = r >> p.tw_log2, tx = r & (TW - 1);
+    const int y = y0 + ty, x = x0 + tx;
+    const bool valid = (y < p.H) && (x < p.W);
+    const size_t pix = valid ? ((size_t)b * p.H + y) * p.W + x : 0;
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+
+    mbar_wait(bar_accum, 0);
+    tc_fence_after();
+
+    if constexpr (EPI == FSB_EPI_GATE_ZR) {
+      const int half = p.BN >> 1;
+      for (int a = 0; a < p.nacc; ++a) {
+        T* zb = reinterpret_cast<T*>(a == 0 ? p.z_l : p.z_s);
+        T* rb = reinterpret_cast<T*>(a == 0 ? p.rh_l : p.rh_s);
+        const float* bias = p.bias + (size_t)a * p.rows + n0;
+        for (int c = 0; c < p.BN; c += 32) {
+          uint32_t v[32];
+          tmem_ld32(taddr + a * p.BN + c, v);
+          tmem_ld_wait();
+          if (!valid) continue;
+          float f[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = sigmoid_f(__uint_as_float(v[j]) + __ldg(bias + c + j));
+          if (c < half) {
+            store32<T>(zb + pix * p.hidden + nt * half + c, f);
+          } else {
+            const int ch = nt * half + (c - half);
+            float h[32];
+            load32f(p.h32 + pix * p.hidden + ch, h);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] *= h[j];
+            store32<T>(rb + pix * p.hidden + ch, f);
+          }
+        }
+      }
+    } else if constexpr (EPI == FSB_EPI_GATE_Q) {
+      const float att = valid ? __ldg(p.att + pix) : 0.f;
+      for (int c = 0; c < p.BN; c += 32) {
+        uint32_t v0[32], v1[32];
+        tmem_ld32(taddr + c, v0);
+        tmem_ld32(taddr + p.BN + c, v1);
+        tmem_ld_wait();
+        if (!valid) continue;
+        const int ch = n0 + c;
+        float h[32], zl[32], zs[32];
+        load32f(p.h32 + pix * p.hidden + ch, h);
+        load32<T>(reinterpret_cast<const T*>(p.z_l) + pix * p.hidden + ch, zl);
+        load32<T>(reinterpret_cast<const T*>(p.z_s) + pix * p.hidden + ch, zs);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float ql = tanh_f(__uint_as_float(v0[j]) + __ldg(p.bias + ch + j));
+          const float qs = tanh_f(__uint_as_float(v1[j]) + __ldg(p.bias + p.rows + ch + j));
+          const float hl = (1.f - zl[j]) * h[j] + zl[j] * ql;
+          const float hs = (1.f - zs[j]) * h[j] + zs[j] * qs;
+          h[j] = hs * att + hl * (1.f - att);
+        }
+        store32f(p.h32_out + pix * p.hidden + ch, h);
+        store32<T>(reinterpret_cast<T*>(p.h16_out) + pix * p.hidden + ch, h);
+      }
+    } else {
+      T* out = reinterpret_cast<T*>(p.out);
+      for (int c = 0; c < p.BN; c += 32) {
+        uint32_t v[32];
+        tmem_ld32(taddr + c, v);
+        tmem_ld_wait();
+        const int n = n0 + c;
+        if (!valid || n >= p.Cout) continue;
+        const bool full = (n + 32 <= p.Cout);
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float a = __uint_as_float(v[j]) + ((full || n + j < p.Cout) ? __ldg(p.bias + n + j) : 0.f);
+          if constexpr (EPI == FSB_EPI_RELU) a = fmaxf(a, 0.f);
+          if constexpr (EPI == FSB_EPI_GELU) a = gelu_f(a);
+          f[j] = a;
+        }
+        if constexpr (EPI == FSB_EPI_SCALE_RES) {
+          float rres[32];
+          load32<T>(reinterpret_cast<const T*>(p.res) + pix * p.ld_res + n, rres);  // Cout % 32 == 0 (host check)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = rres[j] + __ldg(p.gamma + n + j) * f[j];
+        }
+        if (out != nullptr) {
+          T* o = out + pix * p.ld_out + p.ch_off + n;
+          if (full) {
+            store32<T>(o, f);
+          } else {
+            for (int j = 0; j < 32 && n + j < p.Cout; ++j) o[j] = from_f32<T>(f[j]);
+          }
+        }
+        if (p.out_f32 != nullptr) {
+          const size_t hw = (size_t)p.H * p.W;
+          float* o = p.out_f32 + ((size_t)b * p.Cout + n) * hw + (size_t)y * p.W + x;
+#pragma unroll 4
+          for (int j = 0; j < 32; ++j)
+            if (full || n + j < p.Cout) o[(size_t)j * hw] = f[j] * p.out_scale;
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncwarp();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.tmem_cols)
+                 : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------------- host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      f = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(f);
+  }();
+  return fn;
+}
+
+static int pick_tile(int H, int W, int* tw_log2) {
+  // TH x TW = 128, both powers of two: fewest tiles, ties -> wider rows (longer contiguous runs)
+  long best = -1;
+  int best_l = 4;
+  for (int l = 7; l >= 2; --l) {
+    const int tw = 1 << l, th = kBM >> l;
+    const long n = (long)ceil_div(W, tw) * ceil_div(H, th);
+    if (best < 0 || n < best) {
+      best = n;
+      best_l = l;
+    }
+  }
+  *tw_log2 = best_l;
+  return (int)best;
+}
+
+template <typename T>
+static auto kernel_for(int epi) -> void (*)(const ConvParams) {
+  switch (epi) {
+    case FSB_EPI_BIAS: return conv_umma_kernel<T, FSB_EPI_BIAS>;
+    case FSB_EPI_RELU: return conv_umma_kernel<T, FSB_EPI_RELU>;
+    case FSB_EPI_GATE_ZR: return conv_umma_kernel<T, FSB_EPI_GATE_ZR>;
+    case FSB_EPI_GATE_Q: return conv_umma_kernel<T, FSB_EPI_GATE_Q>;
+    case FSB_EPI_GELU: return conv_umma_kernel<T, FSB_EPI_GELU>;
+    case FSB_EPI_SCALE_RES: return conv_umma_kernel<T, FSB_EPI_SCALE_RES>;
+    default: return nullptr;
+  }
+}
+
+}  // namespace fsb
+
+extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(a != nullptr, FSB_ERR_ARG, "fsb_conv2d_nhwc: NULL args");
+  FSB_REQUIRE(dtype == FSB_F16 || dtype == FSB_BF16, FSB_ERR_ARG, "fsb_conv2d_nhwc: dtype %d (need f16/bf16)", dtype);
+  FSB_REQUIRE(a->nsrc >= 1 && a->nsrc <= FSB_MAX_SRC, FSB_ERR_ARG, "fsb_conv2d_nhwc: nsrc=%d", a->nsrc);
+  FSB_REQUIRE(a->B > 0 && a->H > 0 && a->W > 0, FSB_ERR_ARG, "fsb_conv2d_nhwc: non-positive size");
+  FSB_REQUIRE(a->nseg == 1 || a->nseg == 2, FSB_ERR_ARG, "fsb_conv2d_nhwc: nseg=%d", a->nseg);
+  FSB_REQUIRE(a->weight && a->bias, FSB_ERR_ARG, "fsb_conv2d_nhwc: NULL weight/bias");
+  const int BN = a->block_n;
+  FSB_REQUIRE(BN == 16 || (BN >= 32 && BN <= 256 && BN % 32 == 0), FSB_ERR_SHAPE,
+              "fsb_conv2d_nhwc: block_n=%d (16 or a multiple of 32 up to 256)", BN);
+  FSB_REQUIRE(a->nseg * BN <= 512, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: %d accumulators of %d columns exceed TMEM", a->nseg, BN);
+  FSB_REQUIRE(a->rows > 0 && a->rows % BN == 0 && a->Cout > 0 && a->Cout <= a->rows, FSB_ERR_SHAPE,
+              "fsb_conv2d_nhwc: rows=%d block_n=%d Cout=%d", a->rows, BN, a->Cout);
+  for (int i = 0; i < a->nsrc; ++i) {
+    FSB_REQUIRE(a->src[i].ptr && a->src[i].C > 0 && a->src[i].C % kBK == 0, FSB_ERR_SHAPE,
+                "fsb_conv2d_nhwc: source %d needs a non-NULL pointer and C %% 64 == 0 (C=%d)", i, a->src[i].C);
+    FSB_REQUIRE(aligned16(a->src[i].ptr), FSB_ERR_ALIGN, "fsb_conv2d_nhwc: source %d not 16-byte aligned", i);
+  }
+  FSB_REQUIRE(aligned16(a->weight), FSB_ERR_ALIGN, "fsb_conv2d_nhwc: weight not 16-byte aligned");
+  const int epi = a->epilogue;
+  if (epi == FSB_EPI_GATE_ZR) {
+    FSB_REQUIRE(a->h32 && a->z_l && a->rh_l && (a->nseg == 1 || (a->z_s && a->rh_s)), FSB_ERR_ARG,
+                "fsb_conv2d_nhwc: GATE_ZR needs h32, z_*, rh_*");
+    FSB_REQUIRE(BN % 64 == 0 && a->hidden > 0 && a->hidden % 32 == 0 && a->rows == 2 * a->hidden, FSB_ERR_SHAPE,
+                "fsb_conv2d_nhwc: GATE_ZR needs block_n %% 64 == 0 and rows == 2*hidden (rows=%d hidden=%d)", a->rows, a->hidden);
+  } else if (epi == FSB_EPI_GATE_Q) {
+    FSB_REQUIRE(a->nseg == 2 && a->h32 && a->att && a->z_l && a->z_s && a->h32_out && a->h16_out, FSB_ERR_ARG,
+                "fsb_conv2d_nhwc: GATE_Q needs two segments, h32, att, z_l, z_s, h32_out, h16_out");
+    FSB_REQUIRE(BN % 32 == 0 && a->rows == a->hidden && a->Cout == a->hidden, FSB_ERR_SHAPE,
+                "fsb_conv2d_nhwc: GATE_Q needs rows == Cout == hidden");
+  } else {
+    FSB_REQUIRE(epi == FSB_EPI_BIAS || epi == FSB_EPI_RELU || epi == FSB_EPI_GELU || epi == FSB_EPI_SCALE_RES,
+                FSB_ERR_ARG, "fsb_conv2d_nhwc: unknown epilogue %d", epi);
+    FSB_REQUIRE(a->nseg == 1, FSB_ERR_ARG, "fsb_conv2d_nhwc: plain epilogues take one segment");
+    FSB_REQUIRE(a->out || a->out_f32, FSB_ERR_ARG, "fsb_conv2d_nhwc: no output");
+    if (a->out) {
+      FSB_REQUIRE(a->ld_out >= a->ch_off + a->Cout && a->ld_out % 8 == 0 && a->ch_off % 8 == 0 && aligned16(a->out),
+                  FSB_ERR_SHAPE, "fsb_conv2d_nhwc: out needs ld_out %% 8 == 0, ch_off %% 8 == 0 (ld_out=%d ch_off=%d Cout=%d)",
+                  a->ld_out, a->ch_off, a->Cout);
+    }
+    if (epi == FSB_EPI_SCALE_RES)
+      FSB_REQUIRE(a->res && a->gamma && a->Cout % 32 == 0 && a->ld_res % 8 == 0, FSB_ERR_ARG,
+                  "fsb_conv2d_nhwc: SCALE_RES needs res, gamma, Cout %% 32 == 0");
+  }
+
+  EncodeTiledFn enc = encode_fn();
+  FSB_REQUIRE(enc != nullptr, FSB_ERR_CUDA, "fsb_conv2d_nhwc: cuTensorMapEncodeTiled not available from the driver");
+
+  ConvParams p;
+  memset(&p, 0, sizeof(p));
+  int tw_log2 = 4;
+  pick_tile(a->H, a->W, &tw_log2);
+  const int TW = 1 << tw_log2, TH = kBM >> tw_log2;
+  p.H = a->H;
+  p.W = a->W;
+  p.tiles_x = ceil_div(a->W, TW);
+  p.tiles_y = ceil_div(a->H, TH);
+  p.tw_log2 = tw_log2;
+  p.BN = BN;
+  p.nacc = a->nseg;
+  int cols = 32;
+  while (cols < a->nseg * BN) cols <<= 1;
+  p.tmem_cols = cols;
+
+  // K-step program + Ktot
+  int n = 0;
+  for (int s = 0; s < a->nseg; ++s) {
+    const fsb_conv_seg& sg = a->seg[s];
+    FSB_REQUIRE(sg.ksize == 1 || sg.ksize == 3, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: segment %d ksize=%d", s, sg.ksize);
+    FSB_REQUIRE(sg.nsrc >= 1 && sg.nsrc <= FSB_MAX_SRC, FSB_ERR_ARG, "fsb_conv2d_nhwc: segment %d nsrc=%d", s, sg.nsrc);
+    const int rad = sg.ksize / 2;
+    for (int dy = -rad; dy <= rad; ++dy)
+      for (int dx = -rad; dx <= rad; ++dx)
+        for (int k = 0; k < sg.nsrc; ++k) {
+          const int si = sg.src[k];
+          FSB_REQUIRE(si >= 0 && si < a->nsrc, FSB_ERR_ARG, "fsb_conv2d_nhwc: segment %d source index %d", s, si);
+          for (int c = 0; c < a->src[si].C / kBK; ++c) {
+            FSB_REQUIRE(n < kMaxSteps, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: more than %d K steps", kMaxSteps);
+            p.steps[n++] = make_step(si, dy, dx, s, c);
+          }
+        }
+  }
+  p.nsteps = n;
+  const int Ktot = n * kBK;
+
+  const size_t stage_bytes = (size_t)kATileBytes + (size_t)BN * kBK * 2;
+  int stages = a->stages;
+  if (stages <= 0) stages = (BN > 128) ? 4 : (BN > 64 ? 3 : 4);
+  if (stages > 8) stages = 8;
+  while (stages > 1 && stages * stage_bytes + 1024 > 220 * 1024) --stages;
+  if (stages > n) stages = n;
+  p.stages = stages;
+  const size_t smem = stages * stage_bytes + 1024;
+
+  const CUtensorMapDataType dt = dtype == FSB_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  for (int i = 0; i < a->nsrc; ++i) {
+    const cuuint64_t C = (cuuint64_t)a->src[i].C;
+    cuuint64_t dims[4] = {C, (cuuint64_t)a->W, (cuuint64_t)a->H, (cuuint64_t)a->B};
+    cuuint64_t strides[3] = {C * 2, C * 2 * a->W, C * 2 * a->W * a->H};
+    cuuint32_t box[4] = {(cuuint32_t)kBK, (cuuint32_t)TW, (cuuint32_t)TH, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(&p.amap[i], dt, 4, const_cast<void*>(a->src[i].ptr), dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    FSB_REQUIRE(r == CUDA_SUCCESS, FSB_ERR_CUDA, "fsb_conv2d_nhwc: cuTensorMapEncodeTiled(source %d) -> %d", i, (int)r);
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)Ktot, (cuuint64_t)a->rows};
+    cuuint64_t strides[1] = {(cuuint64_t)Ktot * 2};
+    cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)BN};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&p.wmap, dt, 2, const_cast<void*>(a->weight), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    FSB_REQUIRE(r == CUDA_SUCCESS, FSB_ERR_CUDA, "fsb_conv2d_nhwc: cuTensorMapEncodeTiled(weight) -> %d", (int)r);
+  }
+  // instruction descriptor, kind::f16: D fp32, A/B f16|bf16, both K-major, M = 128, N = block_n
+  const uint32_t fmt = dtype == FSB_F16 ? 0u : 1u;
+  p.idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+  p.rows = a->rows;
+  p.Cout = a->Cout;
+  p.bias = a->bias;
+  p.out = a->out;
+  p.ld_out = a->ld_out;
+  p.ch_off = a->ch_off;
+  p.out_f32 = a->out_f32;
+  p.out_scale = a->out_scale;
+  p.res = a->res;
+  p.ld_res = a->ld_res;
+  p.gamma = a->gamma;
+  p.h32 = a->h32;
+  p.att = a->att;
+  p.z_l = a->z_l;
+  p.z_s = a->z_s;
+  p.rh_l = a->rh_l;
+  p.rh_s = a->rh_s;
+  p.h32_out = a->h32_out;
+  p.h16_out = a->h16_out;
+  p.hidden = a->hidden;
+
+  auto kern = dtype == FSB_F16 ? kernel_for<__half>(epi) : kernel_for<__nv_bfloat16>(epi);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return cuda_fail(e, "fsb_conv2d_nhwc: cudaFuncSetAttribute");
+  const long long mtiles = (long long)p.tiles_x * p.tiles_y * a->B;
+  FSB_REQUIRE(mtiles < (1ll << 31) && a->rows / BN < 65536, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: grid too large");
+  dim3 grid((unsigned)mtiles, (unsigned)(a->rows / BN));
+  kern<<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(p);
+  FSB_CHECK_LAUNCH("fsb_conv2d_nhwc");
+  return FSB_OK;
+}

@@ -1,0 +1,349 @@
+// Small HBM-bound helpers of the update block (CUDA cores): layout changes between the
+// reference's fp32 NCHW tensors and the 16-bit NHWC activations the tcgen05 convolution
+// reads, pool2x / interp (core/update.py:72-80), the two 7x7 convolutions that are not
+// GEMM-shaped (1 input channel: BasicMotionEncoder.convd1, core/update.py:58; depthwise:
+// EdgeNextConvEncoder.dwconv, core/submodule.py:569) and the disparity update
+// (core/foundation_stereo.py:242).
+#include "common.cuh"
+
+namespace fsb {
+
+// ------------------------------------------------------------------ NCHW <-> NHWC
+// tile = 32 pixels x 32 channels through shared memory; both sides coalesced.
+template <typename T>
+__global__ void __launch_bounds__(256)
+nchw_to_nhwc_kernel(const float* __restrict__ src, T* __restrict__ dst16, float* __restrict__ dst32, int C,
+                    int HW, int Cpad) {
+  __shared__ float t[32][33];
+  const int b = blockIdx.z;
+  const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  const float* s = src + (size_t)b * C * HW;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = c0 + ty + 8 * i, p = p0 + tx;
+    t[ty + 8 * i][tx] = (c < C && p < HW) ? s[(size_t)c * HW + p] : 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int p = p0 + ty + 8 * i, c = c0 + tx;
+    if (p >= HW) continue;
+    const float v = t[tx][ty + 8 * i];
+    if (dst16 != nullptr && c < Cpad) dst16[((size_t)b * HW + p) * Cpad + c] = from_f32<T>(v);
+    if (dst32 != nullptr && c < C) dst32[((size_t)b * HW + p) * C + c] = v;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+nhwc_to_nchw_kernel(const float* __restrict__ src, float* __restrict__ dst, int C, int HW) {
+  __shared__ float t[32][33];
+  const int b = blockIdx.z;
+  const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int p = p0 + ty + 8 * i, c = c0 + tx;
+    t[ty + 8 * i][tx] = (c < C && p < HW) ? src[((size_t)b * HW + p) * C + c] : 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = c0 + ty + 8 * i, p = p0 + tx;
+    if (c < C && p < HW) dst[((size_t)b * C + c) * HW + p] = t[tx][ty + 8 * i];
+  }
+}
+
+// ------------------------------------------------------------------ pool2x / interp
+// one thread = 4 channels of one output pixel (float4 loads, 8-byte store)
+template <typename T>
+__global__ void __launch_bounds__(256)
+pool2x_kernel(const float* __restrict__ src, T* __restrict__ dst, int C4, int H, int W, int Ho, int Wo,
+              size_t total) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int c4 = (int)(i % C4);
+  size_t r = i / C4;
+  const int xo = (int)(r % Wo);
+  r /= Wo;
+  const int yo = (int)(r % Ho);
+  const int b = (int)(r / Ho);
+  const float4* s = reinterpret_cast<const float4*>(src) + (size_t)b * H * W * C4 + c4;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int dy = -1; dy <= 1; ++dy) {
+    const int y = 2 * yo + dy;
+    if (y < 0 || y >= H) continue;
+#pragma unroll
+    for (int dx = -1; dx <= 1; ++dx) {
+      const int x = 2 * xo + dx;
+      if (x < 0 || x >= W) continue;
+      const float4 v = __ldg(s + ((size_t)y * W + x) * C4);
+      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+    }
+  }
+  const float k = 1.f / 9.f;  // count_include_pad=True: the divisor is always 9
+  Quad<T>::store(dst + i * 4, a.x * k, a.y * k, a.z * k, a.w * k);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+resize_kernel(const float* __restrict__ src, T* __restrict__ dst, int C4, int Hs, int Ws, int Hd, int Wd,
+              float sy, float sx, size_t total) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int c4 = (int)(i % C4);
+  size_t r = i / C4;
+  const int xo = (int)(r % Wd);
+  r /= Wd;
+  const int yo = (int)(r % Hd);
+  const int b = (int)(r / Hd);
+  // align_corners=True: src = dst * (in-1)/(out-1)
+  const float fy = sy * (float)yo, fx = sx * (float)xo;
+  const int y0 = min((int)fy, Hs - 1), x0 = min((int)fx, Ws - 1);
+  const int y1 = min(y0 + 1, Hs - 1), x1 = min(x0 + 1, Ws - 1);
+  const float ly = fy - (float)y0, lx = fx - (float)x0;
+  const float4* s = reinterpret_cast<const float4*>(src) + (size_t)b * Hs * Ws * C4 + c4;
+  const float4 v00 = __ldg(s + ((size_t)y0 * Ws + x0) * C4), v01 = __ldg(s + ((size_t)y0 * Ws + x1) * C4);
+  const float4 v10 = __ldg(s + ((size_t)y1 * Ws + x0) * C4), v11 = __ldg(s + ((size_t)y1 * Ws + x1) * C4);
+  const float w00 = (1.f - ly) * (1.f - lx), w01 = (1.f - ly) * lx, w10 = ly * (1.f - lx), w11 = ly * lx;
+  Quad<T>::store(dst + i * 4, w00 * v00.x + w01 * v01.x + w10 * v10.x + w11 * v11.x,
+                 w00 * v00.y + w01 * v01.y + w10 * v10.y + w11 * v11.y,
+                 w00 * v00.z + w01 * v01.z + w10 * v10.z + w11 * v11.z,
+                 w00 * v00.w + w01 * v01.w + w10 * v10.w + w11 * v11.w);
+}
+
+// ------------------------------------------------------------------ 7x7, one input channel
+// CTA = 32 consecutive pixels of one row; thread = (pixel, 8 output channels).
+constexpr int kC1MaxCout = 64;
+template <typename T>
+__global__ void __launch_bounds__(256)
+conv7x7_c1_kernel(const float* __restrict__ disp, const float* __restrict__ weight, const float* __restrict__ bias,
+                  T* __restrict__ out, int ld_out, int Cout, T* __restrict__ disp_out, int ld_disp, int disp_ch,
+                  int H, int W) {
+  __shared__ float wsm[49][kC1MaxCout];
+  __shared__ float patch[7][32 + 6];
+  const int tid = threadIdx.x;
+  const int x0 = blockIdx.x * 32, y = blockIdx.y, b = blockIdx.z;
+  for (int i = tid; i < 49 * Cout; i += 256) {
+    const int co = i / 49, t = i - co * 49;
+    wsm[t][co] = weight[i];
+  }
+  const float* d = disp + (size_t)b * H * W;
+  for (int i = tid; i < 7 * 38; i += 256) {
+    const int ry = i / 38, rx = i - ry * 38;
+    const int yy = y + ry - 3, xx = x0 + rx - 3;
+    patch[ry][rx] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? d[(size_t)yy * W + xx] : 0.f;
+  }
+  __syncthreads();
+  const int px = tid & 31, cg = tid >> 5;  // 8 channel groups
+  const int x = x0 + px;
+  if (x >= W) return;
+  const size_t pix = ((size_t)b * H + y) * W + x;
+  for (int c0 = cg * 8; c0 < Cout; c0 += 64) {
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = (c0 + j < Cout) ? __ldg(bias + c0 + j) : 0.f;
+#pragma unroll
+    for (int ky = 0; ky < 7; ++ky)
+#pragma unroll
+      for (int kx = 0; kx < 7; ++kx) {
+        const float v = patch[ky][px + kx];
+        const float4 w0 = *reinterpret_cast<const float4*>(&wsm[ky * 7 + kx][c0]);
+        const float4 w1 = *reinterpret_cast<const float4*>(&wsm[ky * 7 + kx][c0 + 4]);
+        acc[0] = fmaf(v, w0.x, acc[0]); acc[1] = fmaf(v, w0.y, acc[1]);
+        acc[2] = fmaf(v, w0.z, acc[2]); acc[3] = fmaf(v, w0.w, acc[3]);
+        acc[4] = fmaf(v, w1.x, acc[4]); acc[5] = fmaf(v, w1.y, acc[5]);
+        acc[6] = fmaf(v, w1.z, acc[6]); acc[7] = fmaf(v, w1.w, acc[7]);
+      }
+    T* o = out + pix * ld_out + c0;
+    Quad<T>::store(o, fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f), fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
+    Quad<T>::store(o + 4, fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f), fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
+  }
+  if (disp_out != nullptr && cg == 0) disp_out[pix * ld_disp + disp_ch] = from_f32<T>(patch[3][px + 3]);
+}
+
+// ------------------------------------------------------------------ depthwise 7x7
+// CTA = 8 x 8 output pixels x 64 channels.  The (14 x 14) input patch is staged in
+// shared memory as fp32 (50 KB), the 49 x 64 weights too; thread = (pixel, 16 channels).
+constexpr int kDwT = 8, kDwC = 64, kDwP = kDwT + 6;
+template <typename T>
+__global__ void __launch_bounds__(256)
+dwconv7x7_kernel(const T* __restrict__ x, const float* __restrict__ weight, const float* __restrict__ bias,
+                 T* __restrict__ out, int C, int H, int W) {
+  extern __shared__ float dsm[];
+  float* patch = dsm;                         // [kDwP*kDwP][kDwC + 4]
+  float* wsm = dsm + kDwP * kDwP * (kDwC + 4);  // [49][kDwC]
+  const int tid = threadIdx.x;
+  const int tiles_x = (W + kDwT - 1) / kDwT;
+  const int tx0 = (blockIdx.x % tiles_x) * kDwT, ty0 = (blockIdx.x / tiles_x) * kDwT;
+  const int c0 = blockIdx.y * kDwC, b = blockIdx.z;
+  for (int i = tid; i < 49 * kDwC; i += 256) {
+    const int c = i / 49, t = i - c * 49;
+    wsm[t * kDwC + c] = (c0 + c < C) ? weight[(size_t)(c0 + c) * 49 + t] : 0.f;
+  }
+  // patch: 8 channels (16 bytes) per load
+  for (int i = tid; i < kDwP * kDwP * (kDwC / 8); i += 256) {
+    const int c8 = i % (kDwC / 8), pp = i / (kDwC / 8);
+    const int py = pp / kDwP, px = pp - py * kDwP;
+    const int yy = ty0 + py - 3, xx = tx0 + px - 3;
+    float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+      const uint4 u = *reinterpret_cast<const uint4*>(x + (((size_t)b * H + yy) * W + xx) * C + c0 + c8 * 8);
+      const T* e = reinterpret_cast<const T*>(&u);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] = to_f32<T>(e[j]);
+    }
+    float* d = patch + pp * (kDwC + 4) + c8 * 8;
+    *reinterpret_cast<float4*>(d) = make_float4(f[0], f[1], f[2], f[3]);
+    *reinterpret_cast<float4*>(d + 4) = make_float4(f[4], f[5], f[6], f[7]);
+  }
+  __syncthreads();
+  const int cq = tid & 3, pix = tid >> 2;  // 4 channel quarters of 16 x 64 pixels
+  const int py = pix >> 3, px = pix & 7;
+  const int y = ty0 + py, xo = tx0 + px;
+  if (y >= H || xo >= W) return;
+  float acc[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) acc[j] = __ldg(bias + c0 + cq * 16 + j);
+#pragma unroll 1
+  for (int ky = 0; ky < 7; ++ky)
+#pragma unroll
+    for (int kx = 0; kx < 7; ++kx) {
+      const float* pv = patch + ((py + ky) * kDwP + px + kx) * (kDwC + 4) + cq * 16;
+      const float* wv = wsm + (ky * 7 + kx) * kDwC + cq * 16;
+#pragma unroll
+      for (int j4 = 0; j4 < 4; ++j4) {
+        const float4 v = *reinterpret_cast<const float4*>(pv + 4 * j4);
+        const float4 w = *reinterpret_cast<const float4*>(wv + 4 * j4);
+        acc[4 * j4 + 0] = fmaf(v.x, w.x, acc[4 * j4 + 0]);
+        acc[4 * j4 + 1] = fmaf(v.y, w.y, acc[4 * j4 + 1]);
+        acc[4 * j4 + 2] = fmaf(v.z, w.z, acc[4 * j4 + 2]);
+        acc[4 * j4 + 3] = fmaf(v.w, w.w, acc[4 * j4 + 3]);
+      }
+    }
+  T* o = out + (((size_t)b * H + y) * W + xo) * C + c0 + cq * 16;
+#pragma unroll
+  for (int j4 = 0; j4 < 4; ++j4) Quad<T>::store(o + 4 * j4, acc[4 * j4], acc[4 * j4 + 1], acc[4 * j4 + 2], acc[4 * j4 + 3]);
+}
+
+__global__ void __launch_bounds__(256) axpy_kernel(float* __restrict__ y, const float* __restrict__ x, size_t n) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) y[i] += x[i];
+}
+
+}  // namespace fsb
+
+// -------------------------------------------------------------------------------------
+#define FSB_DISPATCH16(dtype, CALL)                                   \
+  do {                                                                \
+    if ((dtype) == FSB_F16) { using T = __half; CALL; }               \
+    else { using T = __nv_bfloat16; CALL; }                           \
+  } while (0)
+
+static inline bool is16(int dtype) { return dtype == FSB_F16 || dtype == FSB_BF16; }
+
+extern "C" int fsb_nchw_to_nhwc(const float* src, void* dst16, float* dst32, int B, int C, int H, int W, int Cpad,
+                                int dtype, fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(src && (dst16 || dst32), FSB_ERR_ARG, "fsb_nchw_to_nhwc: NULL pointer");
+  FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, FSB_ERR_ARG, "fsb_nchw_to_nhwc: non-positive size");
+  FSB_REQUIRE(!dst16 || (is16(dtype) && Cpad >= C), FSB_ERR_ARG, "fsb_nchw_to_nhwc: dtype=%d Cpad=%d C=%d", dtype, Cpad, C);
+  if (!dst16) Cpad = C;
+  const int HW = H * W;
+  FSB_REQUIRE(B < 65536 && ceil_div(Cpad, 32) < 65536, FSB_ERR_SHAPE, "fsb_nchw_to_nhwc: grid too large");
+  dim3 grid(ceil_div(HW, 32), ceil_div(Cpad, 32), B);
+  FSB_DISPATCH16(dtype, (nchw_to_nhwc_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>(src, (T*)dst16, dst32, C, HW, Cpad)));
+  FSB_CHECK_LAUNCH("fsb_nchw_to_nhwc");
+  return FSB_OK;
+}
+
+extern "C" int fsb_nhwc_to_nchw(const float* src, float* dst, int B, int C, int H, int W, fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(src && dst, FSB_ERR_ARG, "fsb_nhwc_to_nchw: NULL pointer");
+  FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, FSB_ERR_ARG, "fsb_nhwc_to_nchw: non-positive size");
+  FSB_REQUIRE(B < 65536 && ceil_div(C, 32) < 65536, FSB_ERR_SHAPE, "fsb_nhwc_to_nchw: grid too large");
+  dim3 grid(ceil_div(H * W, 32), ceil_div(C, 32), B);
+  nhwc_to_nchw_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, C, H * W);
+  FSB_CHECK_LAUNCH("fsb_nhwc_to_nchw");
+  return FSB_OK;
+}
+
+extern "C" int fsb_pool2x_nhwc(const float* src, void* dst, int B, int C, int H, int W, int dtype,
+                               fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(src && dst, FSB_ERR_ARG, "fsb_pool2x_nhwc: NULL pointer");
+  FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && is16(dtype), FSB_ERR_ARG, "fsb_pool2x_nhwc: bad size or dtype");
+  FSB_REQUIRE(C % 4 == 0 && aligned16(src), FSB_ERR_SHAPE, "fsb_pool2x_nhwc: C=%d must be a multiple of 4", C);
+  const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
+  const size_t total = (size_t)B * Ho * Wo * (C / 4);
+  const unsigned blocks = (unsigned)((total + 255) / 256);
+  FSB_DISPATCH16(dtype, (pool2x_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(src, (T*)dst, C / 4, H, W, Ho, Wo, total)));
+  FSB_CHECK_LAUNCH("fsb_pool2x_nhwc");
+  return FSB_OK;
+}
+
+extern "C" int fsb_resize_nhwc(const float* src, void* dst, int B, int C, int Hs, int Ws, int Hd, int Wd,
+                               int dtype, fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(src && dst, FSB_ERR_ARG, "fsb_resize_nhwc: NULL pointer");
+  FSB_REQUIRE(B > 0 && C > 0 && Hs > 0 && Ws > 0 && Hd > 0 && Wd > 0 && is16(dtype), FSB_ERR_ARG,
+              "fsb_resize_nhwc: bad size or dtype");
+  FSB_REQUIRE(C % 4 == 0 && aligned16(src), FSB_ERR_SHAPE, "fsb_resize_nhwc: C=%d must be a multiple of 4", C);
+  const float sy = Hd > 1 ? (float)(Hs - 1) / (float)(Hd - 1) : 0.f;
+  const float sx = Wd > 1 ? (float)(Ws - 1) / (float)(Wd - 1) : 0.f;
+  const size_t total = (size_t)B * Hd * Wd * (C / 4);
+  const unsigned blocks = (unsigned)((total + 255) / 256);
+  FSB_DISPATCH16(dtype, (resize_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(src, (T*)dst, C / 4, Hs, Ws, Hd, Wd, sy, sx, total)));
+  FSB_CHECK_LAUNCH("fsb_resize_nhwc");
+  return FSB_OK;
+}
+
+extern "C" int fsb_conv7x7_c1(const float* disp, const float* weight, const float* bias, void* out, int ld_out,
+                              int Cout, void* disp_out, int ld_disp, int disp_ch, int B, int H, int W, int dtype,
+                              fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(disp && weight && bias && out, FSB_ERR_ARG, "fsb_conv7x7_c1: NULL pointer");
+  FSB_REQUIRE(B > 0 && H > 0 && W > 0 && is16(dtype), FSB_ERR_ARG, "fsb_conv7x7_c1: bad size or dtype");
+  FSB_REQUIRE(Cout > 0 && Cout <= kC1MaxCout && Cout % 8 == 0 && ld_out % 4 == 0 && ld_out >= Cout, FSB_ERR_SHAPE,
+              "fsb_conv7x7_c1: Cout=%d (multiple of 8, <= %d), ld_out=%d", Cout, kC1MaxCout, ld_out);
+  FSB_REQUIRE(!disp_out || (disp_ch >= 0 && disp_ch < ld_disp), FSB_ERR_ARG, "fsb_conv7x7_c1: disp_ch=%d ld_disp=%d", disp_ch, ld_disp);
+  FSB_REQUIRE(H < 65536 && B < 65536, FSB_ERR_SHAPE, "fsb_conv7x7_c1: grid too large");
+  dim3 grid(ceil_div(W, 32), H, B);
+  FSB_DISPATCH16(dtype, (conv7x7_c1_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>(disp, weight, bias, (T*)out, ld_out, Cout,
+                                                                                       (T*)disp_out, ld_disp, disp_ch, H, W)));
+  FSB_CHECK_LAUNCH("fsb_conv7x7_c1");
+  return FSB_OK;
+}
+
+extern "C" int fsb_dwconv7x7_nhwc(const void* x, const float* weight, const float* bias, void* out, int B, int C,
+                                  int H, int W, int dtype, fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(x && weight && bias && out, FSB_ERR_ARG, "fsb_dwconv7x7_nhwc: NULL pointer");
+  FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && is16(dtype), FSB_ERR_ARG, "fsb_dwconv7x7_nhwc: bad size or dtype");
+  FSB_REQUIRE(C % kDwC == 0 && aligned16(x) && aligned16(out), FSB_ERR_SHAPE, "fsb_dwconv7x7_nhwc: C=%d must be a multiple of %d", C, kDwC);
+  FSB_REQUIRE(B < 65536, FSB_ERR_SHAPE, "fsb_dwconv7x7_nhwc: grid too large");
+  const size_t smem = (size_t)(kDwP * kDwP * (kDwC + 4) + 49 * kDwC) * sizeof(float);
+  dim3 grid(ceil_div(W, kDwT) * ceil_div(H, kDwT), C / kDwC, B);
+  if (dtype == FSB_F16) {
+    cudaError_t e = cudaFuncSetAttribute(dwconv7x7_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return cuda_fail(e, "fsb_dwconv7x7_nhwc: cudaFuncSetAttribute");
+    dwconv7x7_kernel<__half><<<grid, 256, smem, (cudaStream_t)stream>>>((const __half*)x, weight, bias, (__half*)out, C, H, W);
+  } else {
+    cudaError_t e = cudaFuncSetAttribute(dwconv7x7_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return cuda_fail(e, "fsb_dwconv7x7_nhwc: cudaFuncSetAttribute");
+    dwconv7x7_kernel<__nv_bfloat16><<<grid, 256, smem, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, weight, bias,
+                                                                               (__nv_bfloat16*)out, C, H, W);
+  }
+  FSB_CHECK_LAUNCH("fsb_dwconv7x7_nhwc");
+  return FSB_OK;
+}
+
+extern "C" int fsb_axpy_f32(float* y, const float* x, size_t n, fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(y && x, FSB_ERR_ARG, "fsb_axpy_f32: NULL pointer");
+  if (n == 0) return FSB_OK;
+  axpy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(y, x, n);
+  FSB_CHECK_LAUNCH("fsb_axpy_f32");
+  return FSB_OK;
+}

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define FSB_VERSION 100 /* major*100 + minor */
+#define FSB_VERSION 110 /* major*100 + minor */
 #define FSB_MAX_LEVELS 6
 
 typedef void* fsb_stream_t; /* cudaStream_t */
@@ -102,6 +102,120 @@ int fsb_geo_pyramid(const float* vol, float* const* geo_levels, int B, int Cg, i
 int fsb_geo_lookup(float* const* geo_levels, float* const* corr_levels, const float* disp,
                    const float* coords, void* out, int B, int Cg, int D, int H, int W, int W2,
                    int L, int r, int out_layout, fsb_stream_t stream);
+
+/* ---- kernel 4: 3x3 / 1x1 convolution as a tcgen05 implicit GEMM with fused epilogue ----
+ * The convolutions of the update block (core/update.py:20-159): SelectiveConvGRU conv0/conv1,
+ * the RaftConvGRU gate convolutions convz/convr/convq with their sigmoid / tanh / blend
+ * (core/update.py:83-119), BasicMotionEncoder (:51-70), DispHead (:20-32) with the
+ * pointwise layers of EdgeNextConvEncoder (core/submodule.py:565-591) and the mask head
+ * (core/update.py:134-139).
+ *
+ * Activations are NHWC with 16-bit elements (fp16 or bf16), channel count a multiple of 64;
+ * one GEMM row is one pixel.  The input of a convolution is the channel-concatenation of up
+ * to FSB_MAX_SRC tensors ("sources"), which replaces the torch.cat calls of the reference.
+ * A call may hold two "segments": segment 0 (ksize 1 or 3) accumulates into TMEM accumulator
+ * 0, segment 1 (ksize 1) into accumulator 1 -- the large (3x3) and small (1x1) GRU of
+ * SelectiveConvGRU run as ONE launch that shares the activation tiles.
+ *
+ * weight: packed [rows][Ktot] 16-bit, K-major.  The K axis is, in order: for each segment,
+ *   for each tap (ky,kx row-major), for each source of the segment, for each channel of the
+ *   source.  rows = n_tiles * block_n (rows >= Cout; rows beyond Cout are zero).
+ * bias  : fp32 [nseg][rows].
+ *
+ * epilogue (acc_s = accumulator s + bias):
+ *   FSB_EPI_BIAS/RELU/GELU : out[pix, ch_off + n] = act(acc0)            (16-bit NHWC, ld_out)
+ *                            out_f32[b, n, y, x]  = out_scale * act(acc0) (fp32 NCHW, optional)
+ *   FSB_EPI_SCALE_RES      : out = res[pix, n] + gamma[n] * acc0          (EdgeNeXt layer scale)
+ *   FSB_EPI_GATE_ZR        : rows of a tile are [z (block_n/2) | r (block_n/2)] of hidden channels
+ *                            [t*block_n/2, (t+1)*block_n/2); z_l/z_s = sigmoid(acc0/acc1) z part,
+ *                            rh_l/rh_s = sigmoid(acc0/acc1 r part) * h32      (core/update.py:91-93)
+ *   FSB_EPI_GATE_Q         : q_l = tanh(acc0), q_s = tanh(acc1);
+ *                            h' = att*((1-z_s)h + z_s q_s) + (1-att)*((1-z_l)h + z_l q_l)
+ *                            -> h32_out (fp32 NHWC) and h16_out (16-bit NHWC) (core/update.py:94-95,119)
+ */
+#define FSB_MAX_SRC 4
+
+enum fsb_epilogue {
+  FSB_EPI_BIAS = 0,
+  FSB_EPI_RELU = 1,
+  FSB_EPI_GATE_ZR = 2,
+  FSB_EPI_GATE_Q = 3,
+  FSB_EPI_GELU = 4,
+  FSB_EPI_SCALE_RES = 5
+};
+
+typedef struct fsb_conv_src {
+  const void* ptr; /* (B,H,W,C) 16-bit */
+  int C;           /* channels = pixel stride, multiple of 64 */
+} fsb_conv_src;
+
+typedef struct fsb_conv_seg {
+  int ksize;             /* 1 or 3; stride 1, zero padding ksize/2 */
+  int nsrc;              /* sources concatenated along channels, in this order */
+  int src[FSB_MAX_SRC];  /* indices into fsb_conv_args.src */
+} fsb_conv_seg;
+
+typedef struct fsb_conv_args {
+  fsb_conv_src src[FSB_MAX_SRC];
+  int nsrc;
+  int B, H, W;
+  fsb_conv_seg seg[2];
+  int nseg;
+  const void* weight; /* packed, see above */
+  const float* bias;  /* [nseg][rows] */
+  int rows;           /* n_tiles * block_n */
+  int Cout;           /* valid output channels per accumulator */
+  int block_n;        /* 16, 32, 64, 96, 128, 160, 192, 224 or 256; nseg*block_n <= 512 */
+  int stages;         /* smem pipeline depth, 0 = choose */
+  int epilogue;       /* fsb_epilogue */
+  void* out;          /* 16-bit NHWC or NULL */
+  int ld_out;         /* channels per pixel of out */
+  int ch_off;         /* first channel written */
+  float* out_f32;     /* fp32 NCHW (B,Cout,H,W) or NULL */
+  float out_scale;
+  const void* res;    /* SCALE_RES: 16-bit NHWC residual */
+  int ld_res;
+  const float* gamma; /* SCALE_RES: [Cout] */
+  const float* h32;   /* gates: fp32 NHWC (B,H,W,hidden) */
+  const float* att;   /* GATE_Q: fp32 (B,H,W) */
+  void* z_l;          /* gates: 16-bit NHWC (B,H,W,hidden); written by ZR, read by Q */
+  void* z_s;
+  void* rh_l;         /* ZR out: r*h, the first source of the q convolution */
+  void* rh_s;
+  float* h32_out;     /* GATE_Q out (may alias h32) */
+  void* h16_out;      /* GATE_Q out */
+  int hidden;         /* channels of h (128) */
+} fsb_conv_args;
+
+int fsb_conv2d_nhwc(const fsb_conv_args* args, int dtype /* FSB_F16 | FSB_BF16 */, fsb_stream_t stream);
+/* sizeof(fsb_conv_args) as compiled into the library: FFI bindings compare it with their own
+ * mirror of the struct before the first call */
+size_t fsb_conv_args_size(void);
+
+/* ---- small NHWC helpers of the update block (HBM-bound, CUDA cores) ------------------- */
+/* (B,C,H,W) fp32 -> (B,H,W,Cpad) 16-bit (pad channels zero) and, if dst32 != NULL, (B,H,W,C) fp32 */
+int fsb_nchw_to_nhwc(const float* src, void* dst16, float* dst32, int B, int C, int H, int W, int Cpad,
+                     int dtype, fsb_stream_t stream);
+/* (B,H,W,C) fp32 -> (B,C,H,W) fp32 */
+int fsb_nhwc_to_nchw(const float* src, float* dst, int B, int C, int H, int W, fsb_stream_t stream);
+/* pool2x (core/update.py:72-73): 3x3 average, stride 2, pad 1, padded zeros counted.
+ * src fp32 NHWC (B,H,W,C) -> dst 16-bit NHWC (B,Ho,Wo,C), Ho=(H+1)/2 */
+int fsb_pool2x_nhwc(const float* src, void* dst, int B, int C, int H, int W, int dtype, fsb_stream_t stream);
+/* interp (core/update.py:78-80): bilinear, align_corners=True, fp32 NHWC (B,Hs,Ws,C) -> 16-bit (B,Hd,Wd,C) */
+int fsb_resize_nhwc(const float* src, void* dst, int B, int C, int Hs, int Ws, int Hd, int Wd, int dtype,
+                    fsb_stream_t stream);
+/* BasicMotionEncoder.convd1 (core/update.py:58,66): 7x7, 1 -> Cout channels, pad 3, + bias, ReLU.
+ * disp fp32 (B,1,H,W); weight fp32 (Cout,49); out 16-bit NHWC (B,H,W,ld_out) channels [0,Cout).
+ * If disp_out != NULL also writes disp itself as channel disp_ch of disp_out (ld_disp channels/pixel):
+ * the last channel of the motion features (core/update.py:70).                                    */
+int fsb_conv7x7_c1(const float* disp, const float* weight, const float* bias, void* out, int ld_out, int Cout,
+                   void* disp_out, int ld_disp, int disp_ch, int B, int H, int W, int dtype, fsb_stream_t stream);
+/* depthwise 7x7, pad 3, + bias (EdgeNextConvEncoder.dwconv, core/submodule.py:569,581).
+ * x, out 16-bit NHWC (B,H,W,C); weight fp32 (C,49) */
+int fsb_dwconv7x7_nhwc(const void* x, const float* weight, const float* bias, void* out, int B, int C, int H, int W,
+                       int dtype, fsb_stream_t stream);
+/* y += x (fp32, n elements): the disparity update of core/foundation_stereo.py:242 */
+int fsb_axpy_f32(float* y, const float* x, size_t n, fsb_stream_t stream);
 
 #ifdef __cplusplus
 }
