@@ -346,7 +346,7 @@ def run_b200(args):
                        "l2": "inputs+outputs of a step (224 MB filtered volume, 256 MB cost volume, 335 MB geo pyramid) "
                              "exceed the 126 MB L2; per-kernel timings flush L2 with a 512 MiB write before each launch",
                        "parallelism": f"pairs sharded over {world} GPU(s), no collective on the path",
-                       "update_block": "interim torch/cuDNN fp16 convolutions (tcgen05 implicit-GEMM kernel in progress)"},
+                       "update_block": "tcgen05 implicit-GEMM convolutions with fused gate epilogues (csrc/conv.cu), one CUDA graph per step"},
             "us_per_gru_iter": None,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
                     "ms_per_step": ms_e2e / args.steps},
@@ -356,19 +356,59 @@ def run_b200(args):
             "clocks": clocks.summary(tw0, te1),
             "wall_ms_per_step": 1e3 * (tw1 - tw0) / args.steps,
         }
-        # us per GRU iteration: time the loop body alone
+        # us per GRU iteration: the refinement loop alone (one graph replay per iteration)
+        ws = fsb.Combined_Geo_Encoding_Volume.make_workspace(c["B"], c["Cg"], D, c["H"], c["W"], c["W"], L, device)
+        geo_ws = fsb.Combined_Geo_Encoding_Volume(dev["fl"], dev["fr"], dev["volume"], num_levels=L, dx=hp.dx, workspace=ws)
+        ub = hp.update_block
+        for _ in range(2):
+            ub.refine(geo_ws, dev["net"], dev["inp"], dev["att"], dev["disp"], 2)
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        net = [t for t in dev["net"]]
-        disp = dev["disp"].clone()
         torch.cuda.synchronize()
         g0.record()
-        for _ in range(c["iters"]):
-            feat = geo(disp, coords)
-            net, mask, delta = hp.update_block(net, dev["inp"], feat, disp, dev["att"])
-            disp = disp + delta
+        ub.refine(geo_ws, dev["net"], dev["inp"], dev["att"], dev["disp"], c["iters"])
         g1.record()
         torch.cuda.synchronize()
-        line["us_per_gru_iter"] = 1e3 * g0.elapsed_time(g1) / c["iters"]
+        us_iter = 1e3 * g0.elapsed_time(g1) / c["iters"]
+        line["us_per_gru_iter"] = us_iter
+
+        # ---- tensor roofline of the dominant kernel (conv_umma_kernel: every convolution / linear of the
+        # update block).  Per-launch CUDA-event durations of one step issued launch by launch on one
+        # stream; achieved = algorithmic FLOPs (2*px*Cout*Cin*k*k, unpadded) / sum of durations.
+        plan = ub.plan_for(c["B"], c["H"], c["W"])
+        steps = [(n_, f_) for n_, f_ in zip(plan.names, plan.steps) if callable(f_)]
+        reps = 10
+        tot = [0.0] * len(steps)
+        for _ in range(reps):
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(len(steps) + 1)]
+            ev[0].record()
+            for i, (_, fn) in enumerate(steps):
+                fn()
+                ev[i + 1].record()
+            torch.cuda.synchronize()
+            for i in range(len(steps)):
+                tot[i] += ev[i].elapsed_time(ev[i + 1]) / reps
+        conv_ms = sum(t for (n_, f_), t in zip(steps, tot) if hasattr(f_, "flops"))
+        other_ms = sum(t for (n_, f_), t in zip(steps, tot) if not hasattr(f_, "flops"))
+        conv_flops = synthetic.update_block_flops(state, c["B"], c["H"], c["W"])
+        n_conv = sum(1 for n_, f_ in steps if hasattr(f_, "flops"))
+        tf = conv_flops / (conv_ms * 1e-3) / 1e12
+        peak_tf = peaks["bf16_tflops_sustained"]
+        conv_share = (conv_ms * c["iters"]) / (ms_total / args.steps)
+        hbm = line["roofline"]
+        line["roofline"] = {
+            "kernel": "conv_umma_kernel (tcgen05 implicit-GEMM convolution, all %d launches of one update step)" % n_conv,
+            "bound": "tensor", "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
+            "traffic": None,
+            "peak_source": peaks["source"] + " (MEASURED_PEAKS.json bf16_tflops_sustained: the kernel runs inside a long step)",
+            "algorithmic_flops_per_step": conv_flops, "launches_per_step": n_conv * c["iters"],
+            "ms_per_update_step_sum_of_launches": conv_ms, "ms_other_kernels_per_update_step": other_ms,
+            "share_of_step": min(conv_share, 1.0),
+            "whole_iteration_tflops": conv_flops / (us_iter * 1e-6) / 1e12,
+            "hbm_kernels": hbm["kernels"],
+        }
+        if os.path.exists(traffic_file):
+            with open(traffic_file) as fh:
+                line["roofline"]["traffic"] = json.load(fh).get("conv_umma_kernel")
         print(json.dumps(line))
     if world > 1:
         dist.barrier()

@@ -17,18 +17,27 @@
 //             TMA box (64, block_n) per K step.
 //   D       = fp32 accumulators in TMEM (up to two: the 3x3 "large" and 1x1 "small" GRU).
 //
-// Warp roles (192 threads): warp 0 = TMA producer (one elected lane), warp 1 = TMEM
-// allocator + MMA issuer (one elected lane), warps 2..5 = epilogue (tcgen05.ld, one pixel
-// per thread, 32 output channels per load).  Stages are handed over with mbarriers:
-// full[s] (TMA -> MMA, transaction bytes), empty[s] (tcgen05.commit -> TMA), accum
-// (last commit -> epilogue).
+// Warp roles (224 threads): warp 0 = TMA producer of the activation tiles, warp 6 = TMA
+// producer of the weight tiles (one elected lane each), warp 1 = TMEM allocator + MMA issuer
+// (one elected lane), warps 2..5 = epilogue (tcgen05.ld, one pixel per thread, 32 output
+// channels per load).  A pipeline stage holds `kper` K steps (1, 2 or 4).  Stages are handed
+// over with mbarriers: full[s] (both producers -> MMA, transaction bytes), empty[s]
+// (tcgen05.commit -> producers), accum (last commit -> epilogue).
+//
+// Why two producer warps and multi-step stages: measured on B200 (tools/tma_bench2.cu), ONE
+// issuing thread sustains one mbarrier round (try_wait + expect_tx) per ~370 cycles plus ~117
+// cycles per TMA instruction regardless of the bytes moved, while a 128 x 128 x 64 MMA step
+// lasts 256 cycles -- a single producer issuing two loads per 64-wide K step (~600 cycles)
+// starves the tensor pipe.  Independent issuers scale linearly up to the L2 limit (~95
+// B/cycle/SM).  The single-thread loops below are therefore kept free of integer division
+// and parameter-space indexing beyond one word per step.
 #include "common.cuh"
 
 #include <cuda.h>
 
 namespace fsb {
 
-constexpr int kConvThreads = 192;
+constexpr int kConvThreads = 224;
 constexpr int kMaxSteps = 112;
 constexpr int kBM = 128;
 constexpr int kBK = 64;                      // 16-bit elements per K step (128 B)
@@ -46,7 +55,7 @@ struct alignas(64) ConvParams {
   uint32_t steps[kMaxSteps];
   int nsteps;
   int H, W, tiles_x, tiles_y, tw_log2;
-  int BN, nacc, tmem_cols, stages;
+  int BN, nacc, tmem_cols, stages, kper;
   uint32_t idesc;
   int rows, Cout;
   const float* bias;
@@ -93,8 +102,9 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
   const long long t0 = clock64();
+  uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000ll) __trap();
+    if ((++spins & 255u) == 0 && clock64() - t0 > 4000000000ll) __trap();
   }
 }
 
@@ -164,7 +174,19 @@ __device__ __forceinline__ float tanh_f(float x) {
   const float e = __expf(2.f * x);  // inf for large x -> 1 - 0; 0 for very negative x -> -1
   return 1.f - __fdividef(2.f, e + 1.f);
 }
-__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.f + erff(x * 0.70710678118654752f)); }
+// erf by Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7, far below the 16-bit output rounding):
+// a dozen instructions instead of erff's branchy ~30.
+__device__ __forceinline__ float erf_as(float x) {
+  const float ax = fabsf(x);
+  const float t = __fdividef(1.f, fmaf(0.3275911f, ax, 1.f));
+  float p = fmaf(1.061405429f, t, -1.453152027f);
+  p = fmaf(p, t, 1.421413741f);
+  p = fmaf(p, t, -0.284496736f);
+  p = fmaf(p, t, 0.254829592f);
+  const float e = 1.f - p * t * __expf(-ax * ax);
+  return copysignf(e, x);
+}
+__device__ __forceinline__ float gelu_f(float x) { return 0.5f * x * (1.f + erf_as(x * 0.70710678118654752f)); }
 
 template <typename T> __device__ __forceinline__ uint32_t pack2(float a, float b);
 template <> __device__ __forceinline__ uint32_t pack2<__half>(float a, float b) {
@@ -227,10 +249,14 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * 8 + 1];
   __shared__ uint32_t tmem_slot;
+  __shared__ __align__(16) float bias_s[2 * 256];  // [nacc][BN] bias of this CTA's output channels
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t stage_bytes = kATileBytes + (uint32_t)p.BN * (kBK * 2);
+  const int kper = p.kper;
+  const uint32_t b_tile_bytes = (uint32_t)p.BN * (kBK * 2);
+  const uint32_t a_stage_bytes = (uint32_t)kper * kATileBytes;
+  const uint32_t stage_bytes = a_stage_bytes + (uint32_t)kper * b_tile_bytes;
   const int S = p.stages;
   const uint32_t bar_full = smem_u32(&bars[0]);
   const uint32_t bar_empty = smem_u32(&bars[8]);
@@ -249,19 +275,25 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < S; ++s) {
-      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_full + 8 * s, 2);   // one expect_tx arrival from each producer
       mbar_init(bar_empty + 8 * s, 1);
     }
     mbar_init(bar_accum, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    tma_prefetch_desc(&p.wmap);
     tma_prefetch_desc(&p.amap[0]);
   }
+  if (warp == 6 && lane == 0) tma_prefetch_desc(&p.wmap);
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
                  "r"((uint32_t)p.tmem_cols)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (warp >= 2 && warp < 6) {
+    for (int i = threadIdx.x - 64; i < p.nacc * p.BN; i += 128) {
+      const int a = i / p.BN, c = i - a * p.BN;
+      bias_s[i] = __ldg(p.bias + (size_t)a * p.rows + n0 + c);
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -269,43 +301,76 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
   const uint32_t tmem_base = tmem_slot;
 
   if (warp == 0) {
-    // ===================================================================== TMA producer
+    // ================================================== TMA producer: activation tiles
     if (lane == 0) {
-      for (int i = 0; i < p.nsteps; ++i) {
-        const int s = i % S;
-        if (i >= S) mbar_wait(bar_empty + 8 * s, ((i / S) - 1) & 1);
-        const uint32_t st = p.steps[i];
-        const int src = st & 3, dy = (int)((st >> 2) & 3) - 1, dx = (int)((st >> 4) & 3) - 1, chunk = (st >> 8) & 0xff;
-        const uint32_t a_dst = smem_base + s * stage_bytes;
-        mbar_expect_tx(bar_full + 8 * s, stage_bytes);
-        tma_load_4d(a_dst, &p.amap[src], bar_full + 8 * s, chunk * kBK, x0 + dx, y0 + dy, b);
-        tma_load_2d(a_dst + kATileBytes, &p.wmap, bar_full + 8 * s, i * kBK, n0);
+      int s = 0;
+      uint32_t ph = 0;
+      for (int i = 0; i < p.nsteps; i += kper) {
+        const int n = min(kper, p.nsteps - i);
+        if (i >= S * kper) mbar_wait(bar_empty + 8 * s, ph ^ 1);
+        const uint32_t full = bar_full + 8 * s;
+        uint32_t dst = smem_base + s * stage_bytes;
+        mbar_expect_tx(full, (uint32_t)n * kATileBytes);
+        for (int j = 0; j < n; ++j) {
+          const uint32_t st = p.steps[i + j];
+          const int src = st & 3, dy = (int)((st >> 2) & 3) - 1, dx = (int)((st >> 4) & 3) - 1, chunk = (st >> 8) & 0xff;
+          tma_load_4d(dst, &p.amap[src], full, chunk * kBK, x0 + dx, y0 + dy, b);
+          dst += kATileBytes;
+        }
+        if (++s == S) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 6) {
+    // ====================================================== TMA producer: weight tiles
+    if (lane == 0) {
+      int s = 0;
+      uint32_t ph = 0;
+      for (int i = 0; i < p.nsteps; i += kper) {
+        const int n = min(kper, p.nsteps - i);
+        if (i >= S * kper) mbar_wait(bar_empty + 8 * s, ph ^ 1);
+        const uint32_t full = bar_full + 8 * s;
+        uint32_t dst = smem_base + s * stage_bytes + a_stage_bytes;
+        mbar_expect_tx(full, (uint32_t)n * b_tile_bytes);
+        for (int j = 0; j < n; ++j) {
+          tma_load_2d(dst, &p.wmap, full, (i + j) * kBK, n0);
+          dst += b_tile_bytes;
+        }
+        if (++s == S) { s = 0; ph ^= 1; }
       }
     }
   } else if (warp == 1) {
     // ====================================================================== MMA issuer
     if (lane == 0) {
       uint32_t started = 0;  // bit a: accumulator a already holds a partial sum
-      for (int i = 0; i < p.nsteps; ++i) {
-        const int s = i % S;
-        mbar_wait(bar_full + 8 * s, (i / S) & 1);
+      int s = 0;
+      uint32_t ph = 0;
+      const uint32_t idesc = p.idesc;
+      for (int i = 0; i < p.nsteps; i += kper) {
+        const int n = min(kper, p.nsteps - i);
+        mbar_wait(bar_full + 8 * s, ph);
         tc_fence_after();
-        const int acc = (p.steps[i] >> 6) & 1;
         const uint32_t a_addr = smem_base + s * stage_bytes;
-        const uint64_t adesc = umma_desc_k128(a_addr);
-        const uint64_t bdesc = umma_desc_k128(a_addr + kATileBytes);
-        const uint32_t d = tmem_base + (uint32_t)(acc * p.BN);
-#pragma unroll
-        for (int k = 0; k < kBK / 16; ++k) {
+        uint64_t adesc = umma_desc_k128(a_addr);
+        uint64_t bdesc = umma_desc_k128(a_addr + a_stage_bytes);
+        for (int j = 0; j < n; ++j) {
+          const int acc = (p.steps[i + j] >> 6) & 1;
+          const uint32_t d = tmem_base + (uint32_t)(acc * p.BN);
+          const uint32_t first = (started >> acc) & 1;
           // +32 B along K inside the swizzle atom = +2 in the (addr >> 4) field
-          umma_f16(d, adesc + 2 * k, bdesc + 2 * k, p.idesc, ((started >> acc) & 1) | (k > 0));
+          umma_f16(d, adesc, bdesc, idesc, first);
+          umma_f16(d, adesc + 2, bdesc + 2, idesc, 1);
+          umma_f16(d, adesc + 4, bdesc + 4, idesc, 1);
+          umma_f16(d, adesc + 6, bdesc + 6, idesc, 1);
+          started |= 1u << acc;
+          adesc += kATileBytes >> 4;
+          bdesc += b_tile_bytes >> 4;
         }
-        started |= 1u << acc;
         umma_commit(bar_empty + 8 * s);  // frees the stage when these MMAs have read it
+        if (++s == S) { s = 0; ph ^= 1; }
       }
       umma_commit(bar_accum);  // all MMAs done -> accumulators complete
     }
-  } else {
+  } else if (warp < 6) {
     // ======================================================================== epilogue
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     const int r = q * 32 + lane;
@@ -323,7 +388,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
       for (int a = 0; a < p.nacc; ++a) {
         T* zb = reinterpret_cast<T*>(a == 0 ? p.z_l : p.z_s);
         T* rb = reinterpret_cast<T*>(a == 0 ? p.rh_l : p.rh_s);
-        const float* bias = p.bias + (size_t)a * p.rows + n0;
+        const float* bias = bias_s + a * p.BN;
         for (int c = 0; c < p.BN; c += 32) {
           uint32_t v[32];
           tmem_ld32(taddr + a * p.BN + c, v);
@@ -331,7 +396,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
           if (!valid) continue;
           float f[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = sigmoid_f(__uint_as_float(v[j]) + __ldg(bias + c + j));
+          for (int j = 0; j < 32; ++j) f[j] = sigmoid_f(__uint_as_float(v[j]) + bias[c + j]);
           if (c < half) {
             store32<T>(zb + pix * p.hidden + nt * half + c, f);
           } else {
@@ -359,8 +424,8 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
         load32<T>(reinterpret_cast<const T*>(p.z_s) + pix * p.hidden + ch, zs);
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          const float ql = tanh_f(__uint_as_float(v0[j]) + __ldg(p.bias + ch + j));
-          const float qs = tanh_f(__uint_as_float(v1[j]) + __ldg(p.bias + p.rows + ch + j));
+          const float ql = tanh_f(__uint_as_float(v0[j]) + bias_s[c + j]);
+          const float qs = tanh_f(__uint_as_float(v1[j]) + bias_s[p.BN + c + j]);
           const float hl = (1.f - zl[j]) * h[j] + zl[j] * ql;
           const float hs = (1.f - zs[j]) * h[j] + zs[j] * qs;
           h[j] = hs * att + hl * (1.f - att);
@@ -380,7 +445,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) {
-          float a = __uint_as_float(v[j]) + ((full || n + j < p.Cout) ? __ldg(p.bias + n + j) : 0.f);
+          float a = __uint_as_float(v[j]) + bias_s[c + j];  // rows beyond Cout carry zero bias
           if constexpr (EPI == FSB_EPI_RELU) a = fmaxf(a, 0.f);
           if constexpr (EPI == FSB_EPI_GELU) a = gelu_f(a);
           f[j] = a;
@@ -553,14 +618,29 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   p.nsteps = n;
   const int Ktot = n * kBK;
 
-  const size_t stage_bytes = (size_t)kATileBytes + (size_t)BN * kBK * 2;
-  int stages = a->stages;
-  if (stages <= 0) stages = (BN > 128) ? 4 : (BN > 64 ? 3 : 4);
+  // Pipeline shape.  A grid that fits the machine in one wave (<= 148 CTAs) streams its K loop
+  // alone on an SM: it gets stages of 2 (4 for narrow tiles) K steps, as many as shared memory
+  // holds, so each producer pays one mbarrier round per 2-4 loads.  Larger grids keep two CTAs
+  // per SM (<= 108 KB each: one CTA's epilogue overlaps the other's MMAs, and four producer
+  // threads per SM); tiles too big for that (block_n 256) run one CTA per SM.
+  const size_t step_bytes = (size_t)kATileBytes + (size_t)BN * kBK * 2;
+  const long long n_ctas = (long long)ceil_div(a->W, TW) * ceil_div(a->H, TH) * a->B * (a->rows / BN);
+  int kper = 1, stages = a->stages;
+  if (n_ctas <= 148 || 2 * step_bytes + 1024 > 108 * 1024) {
+    kper = (BN <= 64) ? 4 : 2;
+    while (kper > 1 && (kper > n || 2 * kper * step_bytes + 1024 > 220 * 1024)) kper >>= 1;
+    if (stages <= 0) stages = (int)((220 * 1024 - 1024) / (kper * step_bytes));
+  } else if (stages <= 0) {
+    stages = (int)((108 * 1024 - 1024) / step_bytes);
+  }
   if (stages > 8) stages = 8;
-  while (stages > 1 && stages * stage_bytes + 1024 > 220 * 1024) --stages;
-  if (stages > n) stages = n;
+  while (stages > 1 && stages * kper * step_bytes + 1024 > 220 * 1024) --stages;
+  const int nstage_iters = ceil_div(n, kper);
+  if (stages > nstage_iters) stages = nstage_iters;
+  if (stages < 1) stages = 1;
   p.stages = stages;
-  const size_t smem = stages * stage_bytes + 1024;
+  p.kper = kper;
+  const size_t smem = (size_t)stages * kper * step_bytes + 1024;
 
   const CUtensorMapDataType dt = dtype == FSB_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   for (int i = 0; i < a->nsrc; ++i) {

@@ -164,67 +164,85 @@ conv7x7_c1_kernel(const float* __restrict__ disp, const float* __restrict__ weig
 }
 
 // ------------------------------------------------------------------ depthwise 7x7
-// CTA = 8 x 8 output pixels x 64 channels.  The (14 x 14) input patch is staged in
-// shared memory as fp32 (50 KB), the 49 x 64 weights too; thread = (pixel, 16 channels).
-constexpr int kDwT = 8, kDwC = 64, kDwP = kDwT + 6;
+// CTA = 8 (y) x 16 (x) output pixels x 64 channels.  The 14 x 22 input patch is staged in
+// shared memory in its 16-bit storage type (39 KB), the 49 x 64 weights as fp32.
+// thread = (4 channels, strip of 8 consecutive x, one row): per kernel row it reads 14
+// input vectors (8 B) and 7 weight vectors (16 B) for 224 FMAs, so the kernel is FMA-bound
+// instead of shared-memory-bound; a warp = 16 channel quads x 2 strips reads/writes whole
+// 128-byte runs and its shared-memory accesses are conflict free.
+constexpr int kDwTY = 8, kDwTX = 16, kDwC = 64, kDwPY = kDwTY + 6, kDwPX = kDwTX + 6, kDwR = 8;
+
+template <typename T> __device__ __forceinline__ float4 load4_f32(const T* p);
+template <> __device__ __forceinline__ float4 load4_f32<__half>(const __half* p) {
+  const uint2 u = *reinterpret_cast<const uint2*>(p);
+  const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&u.x));
+  const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+template <> __device__ __forceinline__ float4 load4_f32<__nv_bfloat16>(const __nv_bfloat16* p) {
+  const uint2 u = *reinterpret_cast<const uint2*>(p);
+  const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
+  const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 dwconv7x7_kernel(const T* __restrict__ x, const float* __restrict__ weight, const float* __restrict__ bias,
                  T* __restrict__ out, int C, int H, int W) {
-  extern __shared__ float dsm[];
-  float* patch = dsm;                         // [kDwP*kDwP][kDwC + 4]
-  float* wsm = dsm + kDwP * kDwP * (kDwC + 4);  // [49][kDwC]
+  extern __shared__ __align__(16) uint8_t dsm_raw[];
+  float* wsm = reinterpret_cast<float*>(dsm_raw);                      // [49][kDwC]
+  T* patch = reinterpret_cast<T*>(dsm_raw + 49 * kDwC * sizeof(float));  // [kDwPY][kDwPX][kDwC]
   const int tid = threadIdx.x;
-  const int tiles_x = (W + kDwT - 1) / kDwT;
-  const int tx0 = (blockIdx.x % tiles_x) * kDwT, ty0 = (blockIdx.x / tiles_x) * kDwT;
+  const int tiles_x = (W + kDwTX - 1) / kDwTX;
+  const int tx0 = (blockIdx.x % tiles_x) * kDwTX, ty0 = (blockIdx.x / tiles_x) * kDwTY;
   const int c0 = blockIdx.y * kDwC, b = blockIdx.z;
   for (int i = tid; i < 49 * kDwC; i += 256) {
     const int c = i / 49, t = i - c * 49;
-    wsm[t * kDwC + c] = (c0 + c < C) ? weight[(size_t)(c0 + c) * 49 + t] : 0.f;
+    wsm[t * kDwC + c] = weight[(size_t)(c0 + c) * 49 + t];
   }
-  // patch: 8 channels (16 bytes) per load
-  for (int i = tid; i < kDwP * kDwP * (kDwC / 8); i += 256) {
-    const int c8 = i % (kDwC / 8), pp = i / (kDwC / 8);
-    const int py = pp / kDwP, px = pp - py * kDwP;
+  // patch: 8 channels (16 bytes) per load, zero outside the image
+  for (int i = tid; i < kDwPY * kDwPX * (kDwC / 8); i += 256) {
+    const int c8 = i & (kDwC / 8 - 1), pp = i >> 3;
+    const int py = pp / kDwPX, px = pp - py * kDwPX;
     const int yy = ty0 + py - 3, xx = tx0 + px - 3;
-    float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
-      const uint4 u = *reinterpret_cast<const uint4*>(x + (((size_t)b * H + yy) * W + xx) * C + c0 + c8 * 8);
-      const T* e = reinterpret_cast<const T*>(&u);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] = to_f32<T>(e[j]);
-    }
-    float* d = patch + pp * (kDwC + 4) + c8 * 8;
-    *reinterpret_cast<float4*>(d) = make_float4(f[0], f[1], f[2], f[3]);
-    *reinterpret_cast<float4*>(d + 4) = make_float4(f[4], f[5], f[6], f[7]);
+    uint4 u = make_uint4(0u, 0u, 0u, 0u);
+    if (yy >= 0 && yy < H && xx >= 0 && xx < W)
+      u = *reinterpret_cast<const uint4*>(x + (((size_t)b * H + yy) * W + xx) * C + c0 + c8 * 8);
+    *reinterpret_cast<uint4*>(patch + pp * kDwC + c8 * 8) = u;
   }
   __syncthreads();
-  const int cq = tid & 3, pix = tid >> 2;  // 4 channel quarters of 16 x 64 pixels
-  const int py = pix >> 3, px = pix & 7;
-  const int y = ty0 + py, xo = tx0 + px;
-  if (y >= H || xo >= W) return;
-  float acc[16];
+  const int cq = tid & 15, xs = (tid >> 4) & 1, row = tid >> 5;
+  const int y = ty0 + row, xb = tx0 + xs * kDwR;
+  float acc[kDwR][4];
+  {
+    const float4 bv = *reinterpret_cast<const float4*>(bias + c0 + cq * 4);
 #pragma unroll
-  for (int j = 0; j < 16; ++j) acc[j] = __ldg(bias + c0 + cq * 16 + j);
+    for (int j = 0; j < kDwR; ++j) { acc[j][0] = bv.x; acc[j][1] = bv.y; acc[j][2] = bv.z; acc[j][3] = bv.w; }
+  }
 #pragma unroll 1
-  for (int ky = 0; ky < 7; ++ky)
+  for (int ky = 0; ky < 7; ++ky) {
+    float4 in[kDwR + 6];
+    const T* prow = patch + ((row + ky) * kDwPX + xs * kDwR) * kDwC + cq * 4;
+#pragma unroll
+    for (int j = 0; j < kDwR + 6; ++j) in[j] = load4_f32<T>(prow + j * kDwC);
 #pragma unroll
     for (int kx = 0; kx < 7; ++kx) {
-      const float* pv = patch + ((py + ky) * kDwP + px + kx) * (kDwC + 4) + cq * 16;
-      const float* wv = wsm + (ky * 7 + kx) * kDwC + cq * 16;
+      const float4 w = *reinterpret_cast<const float4*>(wsm + (ky * 7 + kx) * kDwC + cq * 4);
 #pragma unroll
-      for (int j4 = 0; j4 < 4; ++j4) {
-        const float4 v = *reinterpret_cast<const float4*>(pv + 4 * j4);
-        const float4 w = *reinterpret_cast<const float4*>(wv + 4 * j4);
-        acc[4 * j4 + 0] = fmaf(v.x, w.x, acc[4 * j4 + 0]);
-        acc[4 * j4 + 1] = fmaf(v.y, w.y, acc[4 * j4 + 1]);
-        acc[4 * j4 + 2] = fmaf(v.z, w.z, acc[4 * j4 + 2]);
-        acc[4 * j4 + 3] = fmaf(v.w, w.w, acc[4 * j4 + 3]);
+      for (int j = 0; j < kDwR; ++j) {
+        acc[j][0] = fmaf(in[j + kx].x, w.x, acc[j][0]);
+        acc[j][1] = fmaf(in[j + kx].y, w.y, acc[j][1]);
+        acc[j][2] = fmaf(in[j + kx].z, w.z, acc[j][2]);
+        acc[j][3] = fmaf(in[j + kx].w, w.w, acc[j][3]);
       }
     }
-  T* o = out + (((size_t)b * H + y) * W + xo) * C + c0 + cq * 16;
+  }
+  if (y >= H) return;
+  T* o = out + (((size_t)b * H + y) * W + xb) * C + c0 + cq * 4;
 #pragma unroll
-  for (int j4 = 0; j4 < 4; ++j4) Quad<T>::store(o + 4 * j4, acc[4 * j4], acc[4 * j4 + 1], acc[4 * j4 + 2], acc[4 * j4 + 3]);
+  for (int j = 0; j < kDwR; ++j)
+    if (xb + j < W) Quad<T>::store(o + (size_t)j * C, acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
 }
 
 __global__ void __launch_bounds__(256) axpy_kernel(float* __restrict__ y, const float* __restrict__ x, size_t n) {
@@ -321,10 +339,10 @@ extern "C" int fsb_dwconv7x7_nhwc(const void* x, const float* weight, const floa
   using namespace fsb;
   FSB_REQUIRE(x && weight && bias && out, FSB_ERR_ARG, "fsb_dwconv7x7_nhwc: NULL pointer");
   FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && is16(dtype), FSB_ERR_ARG, "fsb_dwconv7x7_nhwc: bad size or dtype");
-  FSB_REQUIRE(C % kDwC == 0 && aligned16(x) && aligned16(out), FSB_ERR_SHAPE, "fsb_dwconv7x7_nhwc: C=%d must be a multiple of %d", C, kDwC);
+  FSB_REQUIRE(C % kDwC == 0 && aligned16(x) && aligned16(out) && aligned16(bias), FSB_ERR_SHAPE, "fsb_dwconv7x7_nhwc: C=%d must be a multiple of %d", C, kDwC);
   FSB_REQUIRE(B < 65536, FSB_ERR_SHAPE, "fsb_dwconv7x7_nhwc: grid too large");
-  const size_t smem = (size_t)(kDwP * kDwP * (kDwC + 4) + 49 * kDwC) * sizeof(float);
-  dim3 grid(ceil_div(W, kDwT) * ceil_div(H, kDwT), C / kDwC, B);
+  const size_t smem = (size_t)49 * kDwC * sizeof(float) + (size_t)kDwPY * kDwPX * kDwC * 2;
+  dim3 grid(ceil_div(W, kDwTX) * ceil_div(H, kDwTY), C / kDwC, B);
   if (dtype == FSB_F16) {
     cudaError_t e = cudaFuncSetAttribute(dwconv7x7_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return cuda_fail(e, "fsb_dwconv7x7_nhwc: cudaFuncSetAttribute");

@@ -18,7 +18,14 @@ from . import _lib, ops
 
 class Combined_Geo_Encoding_Volume:
     def __init__(self, init_fmap1: torch.Tensor, init_fmap2: torch.Tensor, geo_volume: torch.Tensor,
-                 num_levels: int = 2, dx: Optional[torch.Tensor] = None, precision: int = _lib.FSB_PREC_FP32):
+                 num_levels: int = 2, dx: Optional[torch.Tensor] = None, precision: int = _lib.FSB_PREC_FP32,
+                 workspace: Optional[dict] = None, nhwc16_out=None):
+        """``workspace``: optional {"corr": [...], "geo": [...]} caller-owned level buffers of the
+        right shapes (stable addresses, so a CUDA graph that holds the lookup can be replayed
+        for every pair).  ``nhwc16_out``: optional callable (B,H,W) -> 16-bit (B,H,W,Cpad)
+        buffer; when given, a call writes the fused 16-bit NHWC layout into that buffer and
+        returns its (B, L*K*(Cg+1), H, W) channels-last view (what SelectiveUpdateBlock
+        consumes in place) instead of the reference's fp32 NCHW tensor."""
         if dx is None:
             raise ValueError("dx (the (1,1,2r+1,1) offsets, core/foundation_stereo.py:177-179) is required")
         K = dx.numel()
@@ -38,8 +45,22 @@ class Combined_Geo_Encoding_Volume:
         self._shape = (B, Cg, D, H, W)
         self._w2 = init_fmap2.shape[3]
         # lookup layout: geo level l is (BHW, D>>l, Cg), corr level l is (BHW, W2>>l)
-        self.corr_levels: List[torch.Tensor] = list(ops.corr_pyramid(init_fmap1, init_fmap2, self.num_levels, precision))
-        self.geo_levels: List[torch.Tensor] = list(ops.geo_pyramid(geo_volume, self.num_levels))
+        self._nhwc16_out = nhwc16_out
+        if workspace is not None:
+            self.corr_levels = list(workspace["corr"])
+            self.geo_levels = list(workspace["geo"])
+            ops.corr_pyramid_into(init_fmap1, init_fmap2, self.corr_levels, precision)
+            ops.geo_pyramid_into(geo_volume, self.geo_levels)
+        else:
+            self.corr_levels: List[torch.Tensor] = list(ops.corr_pyramid(init_fmap1, init_fmap2, self.num_levels, precision))
+            self.geo_levels: List[torch.Tensor] = list(ops.geo_pyramid(geo_volume, self.num_levels))
+
+    @staticmethod
+    def make_workspace(B: int, Cg: int, D: int, H: int, W: int, W2: int, num_levels: int, device) -> dict:
+        """Level buffers in the lookup layout: geo (BHW, D>>l, Cg), corr (BHW, W2>>l), fp32."""
+        n = B * H * W
+        return {"corr": [torch.empty((n, W2 >> l), dtype=torch.float32, device=device) for l in range(num_levels)],
+                "geo": [torch.empty((n, D >> l, Cg), dtype=torch.float32, device=device) for l in range(num_levels)]}
 
     # -- the reference's attribute names, as views in the reference's shapes -------------
     @property
@@ -55,7 +76,18 @@ class Combined_Geo_Encoding_Volume:
     def __call__(self, disp: torch.Tensor, coords: torch.Tensor, low_memory: bool = False) -> torch.Tensor:
         """(B,1,H,W) disparity, (B,H,W,1) x coordinates -> (B, L*K*(Cg+1), H, W) fp32.
         ``low_memory`` is accepted and ignored like the reference (core/utils/utils.py:44)."""
+        if self._nhwc16_out is not None:
+            return self.lookup_nhwc16(disp, coords, self._nhwc16_out(*[disp.shape[i] for i in (0, 2, 3)]))
         return ops.geo_lookup(self.geo_levels, self.corr_levels, disp, coords, self.radius)
+
+    def lookup_nhwc16(self, disp: torch.Tensor, coords: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+        """Fused-output lookup into the 16-bit (B,H,W,Cpad) buffer ``out``; returns the
+        (B, L*K*(Cg+1), H, W) view of it (channels-last strides, pad channels hidden)."""
+        B, H, W, Cpad = out.shape
+        ops.geo_lookup_nhwc16(self.geo_levels, self.corr_levels, disp.float().contiguous(),
+                              coords.float().contiguous(), self.radius, out)
+        planes = self.num_levels * (2 * self.radius + 1) * (self._shape[1] + 1)
+        return torch.as_strided(out, (B, planes, H, W), (H * W * Cpad, 1, W * Cpad, Cpad))
 
     @staticmethod
     def corr(fmap1: torch.Tensor, fmap2: torch.Tensor) -> torch.Tensor:

@@ -35,6 +35,7 @@ class StereoHotPath:
         self.G = num_groups
         self.update_block = SelectiveUpdateBlock(state_dict, self.device)
         self.dx = torch.linspace(-corr_radius, corr_radius, 2 * corr_radius + 1).reshape(1, 1, -1, 1)
+        self._ws = {}
 
     @torch.no_grad()
     def run(self, fl: Tensor, fr: Tensor, pl: Tensor, pr: Tensor, volume: Tensor, disp: Tensor,
@@ -44,13 +45,11 @@ class StereoHotPath:
         the (B,32,D,H,W) gwc+concat volume)."""
         B, _, H, W = fl.shape
         comb = build_combined_volume(fl, fr, pl, pr, self.D, self.G)
-        geo = Combined_Geo_Encoding_Volume(fl.float(), fr.float(), volume, num_levels=self.L, dx=self.dx)
-        coords = torch.arange(W, dtype=torch.float32, device=fl.device).reshape(1, 1, W, 1).repeat(B, H, 1, 1)
-        disp = disp.float()
-        net = [t for t in net]
-        mask = None
-        for _ in range(iters):
-            feat = geo(disp, coords)
-            net, mask, delta = self.update_block(net, inp, feat, disp, att)
-            disp = disp + delta.float()
+        key = (B, volume.shape[1], volume.shape[2], H, W, fr.shape[3])
+        ws = self._ws.get(key)
+        if ws is None:  # level buffers with stable addresses: the per-iteration graph is captured once
+            ws = self._ws[key] = Combined_Geo_Encoding_Volume.make_workspace(B, volume.shape[1], volume.shape[2], H, W,
+                                                                           fr.shape[3], self.L, fl.device)
+        geo = Combined_Geo_Encoding_Volume(fl.float(), fr.float(), volume, num_levels=self.L, dx=self.dx, workspace=ws)
+        disp, mask, _ = self.update_block.refine(geo, net, inp, att, disp, iters)
         return disp, mask, comb

@@ -167,3 +167,49 @@ def _(geo_levels, corr_levels, disp, coords, radius):
     B, _, H, W = disp.shape
     Cg = geo_levels[0].shape[2]
     return disp.new_empty((B, len(geo_levels) * (2 * radius + 1) * (Cg + 1), H, W), dtype=torch.float32)
+
+
+def geo_lookup_nhwc16(geo_levels: List[torch.Tensor], corr_levels: List[torch.Tensor], disp: torch.Tensor,
+                      coords: torch.Tensor, radius: int, out: torch.Tensor) -> torch.Tensor:
+    """Kernel 3 with the fused output layout: writes the samples as the 16-bit NHWC tensor
+    ``out`` (B,H,W,Cpad), Cpad = L*K*(Cg+1) rounded up to 64 with zero pad channels -- the A
+    operand of encoder.convc1.  ``out`` is caller-owned (a static buffer of the update-block
+    plan), so the launch can be captured in a CUDA graph; not a torch.library op because it
+    writes in place into that buffer."""
+    _need_cuda(disp, coords, out)
+    L = len(geo_levels)
+    B, _, H, W = disp.shape
+    N, D, Cg = geo_levels[0].shape
+    W2 = corr_levels[0].shape[1]
+    K = 2 * radius + 1
+    cpad = (L * K * (Cg + 1) + 63) // 64 * 64
+    assert out.shape == (B, H, W, cpad) and out.is_contiguous() and out.dtype in (torch.float16, torch.bfloat16)
+    assert disp.dtype == torch.float32 and disp.is_contiguous() and coords.dtype == torch.float32 \
+        and coords.is_contiguous() and coords.numel() == N == B * H * W
+    layout = 1 if out.dtype == torch.float16 else 2
+    check(lib().fsb_geo_lookup(level_array(geo_levels), level_array(corr_levels), disp.data_ptr(),
+                               coords.data_ptr(), out.data_ptr(), B, Cg, D, H, W, W2, L, radius, layout, _stream()))
+    return out
+
+
+def corr_pyramid_into(f1: torch.Tensor, f2: torch.Tensor, levels: List[torch.Tensor], precision: int) -> None:
+    """fsb_corr_pyramid into caller-owned level buffers (stable addresses for graph capture)."""
+    _need_cuda(f1, f2)
+    f1 = f1.float().contiguous()
+    f2 = f2.float().contiguous()
+    B, C, H, W1 = f1.shape
+    W2 = f2.shape[3]
+    for l, t in enumerate(levels):
+        assert t.shape == (B * H * W1, W2 >> l) and t.dtype == torch.float32 and t.is_contiguous()
+    check(lib().fsb_corr_pyramid(f1.data_ptr(), f2.data_ptr(), level_array(levels), B, C, H, W1, W2,
+                                 len(levels), precision, _stream()))
+
+
+def geo_pyramid_into(volume: torch.Tensor, levels: List[torch.Tensor]) -> None:
+    """fsb_geo_pyramid into caller-owned level buffers."""
+    _need_cuda(volume)
+    volume = volume.float().contiguous()
+    B, Cg, D, H, W = volume.shape
+    for l, t in enumerate(levels):
+        assert t.shape == (B * H * W, D >> l, Cg) and t.dtype == torch.float32 and t.is_contiguous()
+    check(lib().fsb_geo_pyramid(volume.data_ptr(), level_array(levels), B, Cg, D, H, W, len(levels), _stream()))

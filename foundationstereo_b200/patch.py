@@ -20,14 +20,30 @@ from .update import SelectiveUpdateBlock
 _SAVED = {}
 
 
-def install(model=None, modules: Optional[list] = None) -> None:
+def install(model=None, modules: Optional[list] = None, fused_lookup: bool = True) -> None:
     """Rebind the three names in every loaded reference module that holds them and, if a
     FoundationStereo ``model`` is given, route ``model.update_block.forward`` through
-    SelectiveUpdateBlock built from the module's own parameters."""
+    SelectiveUpdateBlock built from the module's own parameters.
+
+    With a model and ``fused_lookup`` (default) ``geo_fn(disp, coords)`` writes its samples
+    straight into the update block's 16-bit NHWC input buffer and returns a channels-last
+    view of it -- the unchanged caller (core/foundation_stereo.py:238-240) only hands that
+    tensor on to ``update_block``.  ``fused_lookup=False`` returns the reference's fp32
+    (B, L*K*(Cg+1), H, W) tensor."""
+    geo_cls = Combined_Geo_Encoding_Volume
+    if model is not None:
+        engine_of = install_update_block(model.update_block)
+        if fused_lookup:
+            class FusedGeoEncodingVolume(Combined_Geo_Encoding_Volume):
+                def __init__(self, init_fmap1, init_fmap2, geo_volume, num_levels=2, dx=None):
+                    super().__init__(init_fmap1, init_fmap2, geo_volume, num_levels=num_levels, dx=dx,
+                                     nhwc16_out=lambda B, H, W: engine_of().corr_buffer(B, H, W))
+            FusedGeoEncodingVolume.__name__ = "Combined_Geo_Encoding_Volume"
+            geo_cls = FusedGeoEncodingVolume
     names = {
         "build_gwc_volume": build_gwc_volume,
         "build_concat_volume": build_concat_volume,
-        "Combined_Geo_Encoding_Volume": Combined_Geo_Encoding_Volume,
+        "Combined_Geo_Encoding_Volume": geo_cls,
     }
     if modules is None:
         modules = [m for n, m in list(sys.modules.items())
@@ -37,25 +53,28 @@ def install(model=None, modules: Optional[list] = None) -> None:
             if hasattr(mod, name):
                 _SAVED.setdefault((mod.__name__, name), getattr(mod, name))
                 setattr(mod, name, fn)
-    if model is not None:
-        install_update_block(model.update_block)
 
 
-def install_update_block(update_block) -> None:
+def install_update_block(update_block):
     """Keep the nn.Module (and its state_dict keys) in place, replace only ``forward``.
-    The engine re-reads the parameters when their version counters change."""
+    The engine re-reads the parameters when their version counters change.  Returns a
+    callable that yields the current engine (built on first use)."""
     state = {"engine": None, "versions": None}
 
-    def fast_forward(self, net, inp, corr, disp, att):
-        versions = tuple(p._version for p in self.parameters())
+    def engine():
+        versions = tuple(p._version for p in update_block.parameters())
         if state["engine"] is None or versions != state["versions"]:
-            dev = next(self.parameters()).device
-            state["engine"] = SelectiveUpdateBlock(self.state_dict(), dev)
+            dev = next(update_block.parameters()).device
+            state["engine"] = SelectiveUpdateBlock(update_block.state_dict(), dev)
             state["versions"] = versions
-        return state["engine"](net, inp, corr, disp, att)
+        return state["engine"]
+
+    def fast_forward(self, net, inp, corr, disp, att):
+        return engine()(net, inp, corr, disp, att)
 
     _SAVED.setdefault(("update_block", id(update_block)), update_block.forward)
     update_block.forward = types.MethodType(fast_forward, update_block)
+    return engine
 
 
 def uninstall(model=None) -> None:

@@ -92,3 +92,18 @@ def random_update_block_state(seed: int = 0, corr_levels: int = 2, corr_radius: 
     out["disp_head.conv.4.weight"] *= delta_scale
     out["disp_head.conv.4.bias"] *= delta_scale
     return out
+
+
+def update_block_flops(state: Dict[str, torch.Tensor], B: int, H: int, W: int) -> float:
+    """Algorithmic FLOPs of one BasicSelectiveMultiUpdateBlock.forward (core/update.py:141-159) on the
+    GEMM-shaped layers (every Conv2d / Linear except the 1-channel and depthwise 7x7 convolutions):
+    2 * pixels * Cout * Cin * k * k, pixels = those of the pyramid level the layer runs on."""
+    px = [B * down2(H, i) * down2(W, i) for i in range(3)]
+    level = {"gru04": 0, "gru08": 1, "gru16": 2}
+    total = 0.0
+    for name, w in state.items():
+        if not name.endswith(".weight") or name.endswith("dwconv.weight") or name == "encoder.convd1.weight":
+            continue
+        n = px[level.get(name.split(".")[0], 0)]
+        total += 2.0 * n * w.numel()
+    return total

@@ -27,6 +27,10 @@ DEFAULT_BLOCK_N = {
     "conv0": 128, "conv1": 128, "zr": 128, "q": 64,
     "convc1": 128, "convc2": 128, "convd2": 64, "enc_conv": 64,
     "head0": 64, "pw1": 128, "pw2": 64, "head4": 16, "mask0": 32, "mask2": 32,
+    # the coarse levels have few pixel tiles (10 at 30x40, 40 at 60x80): narrower N tiles put
+    # more CTAs on the 148 SMs (the K loop of a CTA is serial)
+    "gru16.conv0": 32, "gru16.conv1": 32, "gru16.zr": 64, "gru16.q": 32,
+    "gru08.zr": 64, "gru08.q": 32,
 }
 
 
@@ -34,16 +38,36 @@ def _down(n: int) -> int:
     return (n + 1) // 2
 
 
+FORK, JOIN = "fork", "join"
+
+
 class _Plan:
-    """Static buffers + prepared launches for one (B, H, W)."""
+    """Static buffers + prepared launches for one (B, H, W).
+
+    ``steps`` is the launch list of one refinement step.  Each entry runs on lane 0 (the
+    caller's stream) or lane 1 (a side stream): the motion encoder does not depend on
+    gru16/gru08 (core/update.py:143-151) and the mask head not on the disparity head
+    (:155-158), and the coarse GRU levels have too few pixel tiles to fill 148 SMs, so the
+    two chains run concurrently between FORK / JOIN markers (also inside the CUDA graph)."""
 
     def __init__(self):
         self.steps: List[Callable[[], None]] = []
         self.names: List[str] = []
+        self.lanes: List[int] = []
+        self.lane = 0
         self.graph: Optional[torch.cuda.CUDAGraph] = None
-        self.graph_key = None
+        self.iter_graph: Optional[torch.cuda.CUDAGraph] = None
+        self.iter_key = None
+        self.lookup: Optional[Callable[[], None]] = None
         self.calls = 0
+        self.iter_calls = 0
         self.flops = 0.0
+        self.side = torch.cuda.Stream()
+
+    def add(self, name: str, fn) -> None:
+        self.steps.append(fn)
+        self.names.append(name)
+        self.lanes.append(self.lane)
 
 
 class SelectiveUpdateBlock:
@@ -54,7 +78,7 @@ class SelectiveUpdateBlock:
     place and returned, outputs are fp32 (B,C,H,W) tensors.  The returned tensors are
     channels-last views of the engine's own buffers and stay valid until the next call.
     ``corr`` may be the reference's fp32 (B, L*K*(Cg+1), H, W) tensor or the 16-bit NHWC view
-    produced by Combined_Geo_Encoding_Volume(..., nhwc16=True), which is consumed in place.
+    produced by Combined_Geo_Encoding_Volume(..., nhwc16_out=self.corr_buffer), which is consumed in place.
     """
 
     def __init__(self, state_dict: Dict[str, Tensor], device: torch.device | str = "cuda",
@@ -91,28 +115,31 @@ class SelectiveUpdateBlock:
             b[i, :bi.numel()] = bi
         self.w[name] = (w, b.contiguous(), cout)
 
+    def _bn(self, key: str, g: Optional[str] = None) -> int:
+        return self.bn.get(f"{g}.{key}", self.bn[key]) if g else self.bn[key]
+
     def _pack(self, sd: Dict[str, Tensor]) -> None:
         hd = self.hidden
         bn = self.bn
         for g, cin in (("gru16", 2 * hd), ("gru08", 3 * hd), ("gru04", 3 * hd)):
             nx = cin // hd
             self._put(f"{g}.conv0", [pack_segment(sd[f"{g}.conv0.0.weight"], [(hd, hd)] * nx)],
-                      [sd[f"{g}.conv0.0.bias"]], cin, bn["conv0"])
+                      [sd[f"{g}.conv0.0.bias"]], cin, self._bn("conv0", g))
             self._put(f"{g}.conv1", [pack_segment(sd[f"{g}.conv1.0.weight"], [(cin, cin), (hd, hd)])],
-                      [sd[f"{g}.conv1.0.bias"]], cin + hd, bn["conv1"])
+                      [sd[f"{g}.conv1.0.bias"]], cin + hd, self._bn("conv1", g))
             hx = [(cin + hd, cin + hd)]
             zr_w, zr_b = [], []
             for gru in ("large_gru", "small_gru"):
                 z = pack_segment(sd[f"{g}.{gru}.convz.weight"], hx)
                 r = pack_segment(sd[f"{g}.{gru}.convr.weight"], hx)
-                zr_w.append(interleave_zr(z, r, bn["zr"]))
+                zr_w.append(interleave_zr(z, r, self._bn("zr", g)))
                 zr_b.append(interleave_zr(sd[f"{g}.{gru}.convz.bias"][:, None], sd[f"{g}.{gru}.convr.bias"][:, None],
-                                          bn["zr"]).flatten())
-            self._put(f"{g}.zr", zr_w, zr_b, 2 * hd, bn["zr"])
+                                          self._bn("zr", g)).flatten())
+            self._put(f"{g}.zr", zr_w, zr_b, 2 * hd, self._bn("zr", g))
             rhx = [(hd, hd), (cin, cin)]
             self._put(f"{g}.q", [pack_segment(sd[f"{g}.large_gru.convq.weight"], rhx),
                                  pack_segment(sd[f"{g}.small_gru.convq.weight"], rhx)],
-                      [sd[f"{g}.large_gru.convq.bias"], sd[f"{g}.small_gru.convq.bias"]], hd, bn["q"])
+                      [sd[f"{g}.large_gru.convq.bias"], sd[f"{g}.small_gru.convq.bias"]], hd, self._bn("q", g))
         P, Pp = self.planes, self.planes_pad
         self._put("convc1", [pack_segment(sd["encoder.convc1.weight"], [(P, Pp)])], [sd["encoder.convc1.bias"]], 256,
                   bn["convc1"])
@@ -143,10 +170,9 @@ class SelectiveUpdateBlock:
     # ---- per-shape plan -------------------------------------------------------------------
     def _conv(self, plan: _Plan, name: str, wname: str, srcs, segs, bn_key: str, epilogue: int, **kw) -> None:
         w, b, cout = self.w[wname]
-        launch = ConvLaunch(srcs=srcs, segs=segs, weight=w, bias=b, cout=cout, block_n=self.bn[bn_key],
+        launch = ConvLaunch(srcs=srcs, segs=segs, weight=w, bias=b, cout=cout, block_n=self.bn.get(name, self.bn[bn_key]),
                             epilogue=epilogue, name=name, **kw)
-        plan.steps.append(launch)
-        plan.names.append(name)
+        plan.add(name, launch)
         plan.flops += launch.flops
 
     def _gru(self, plan: _Plan, g: str, lvl: int, xs: Sequence[Tensor]) -> None:
@@ -167,7 +193,7 @@ class SelectiveUpdateBlock:
         self._conv(plan, f"{g}.q", f"{g}.q", [rh_l, rh_s, x16], [(3, [0, 2]), (1, [1, 2])], "q", _lib.FSB_EPI_GATE_Q,
                    h32=h32, att=att, z_l=z_l, z_s=z_s, h32_out=h32, h16_out=h16, hidden=hd)
 
-    def _build_plan(self, B: int, H: int, W: int, corr16: Optional[Tensor]) -> _Plan:
+    def _build_plan(self, B: int, H: int, W: int) -> _Plan:
         hd, dev, dt = self.hidden, self.device, self.dtype
         plan = _Plan()
         plan.shape = [(B, H, W), (B, _down(H), _down(W)), (B, _down(_down(H)), _down(_down(W)))]
@@ -179,14 +205,22 @@ class SelectiveUpdateBlock:
         plan.disp = torch.empty(B, 1, H, W, dtype=torch.float32, device=dev)
         plan.delta = torch.empty(B, 1, H, W, dtype=torch.float32, device=dev)
         plan.mask = torch.empty(B, 32, H, W, dtype=torch.float32, device=dev)
-        plan.own_corr = corr16 is None
-        plan.corr16 = corr16 if corr16 is not None else torch.zeros(B, H, W, self.planes_pad, dtype=dt, device=dev)
+        plan.corr16 = torch.zeros(B, H, W, self.planes_pad, dtype=dt, device=dev)
+        plan.coords = torch.arange(W, dtype=torch.float32, device=dev).reshape(1, 1, W, 1).repeat(B, H, 1, 1)
         plan.src_key = [None] * 3  # (data_ptr, version) of the inp/att tensors last converted
+        add = plan.add
 
-        def add(name: str, fn: Callable[[], None]) -> None:
-            plan.steps.append(fn)
-            plan.names.append(name)
-
+        # encoder (core/update.py:62-70): motion = [conv(cat[cor, d]) (127) | disp (1)]  -- side lane
+        add(FORK, FORK)
+        plan.lane = 1
+        c1, c2, d1, d2, motion = new(0, 256), new(0, 256), new(0, 64), new(0, 64), new(0, hd)
+        self._conv(plan, "encoder.convc1", "convc1", [plan.corr16], [(1, [0])], "convc1", _lib.FSB_EPI_RELU, out=c1)
+        self._conv(plan, "encoder.convc2", "convc2", [c1], [(3, [0])], "convc2", _lib.FSB_EPI_RELU, out=c2)
+        add("encoder.convd1", lambda: C.conv7x7_c1(plan.disp, self.f["convd1.w"], self.f["convd1.b"], d1, 64, motion,
+                                                    hd - 1))
+        self._conv(plan, "encoder.convd2", "convd2", [d1], [(3, [0])], "convd2", _lib.FSB_EPI_RELU, out=d2)
+        self._conv(plan, "encoder.conv", "enc_conv", [c2, d2], [(3, [0, 1])], "enc_conv", _lib.FSB_EPI_RELU, out=motion)
+        plan.lane = 0
         # gru16: x = [inp[2], pool2x(net[1])]                                   (core/update.py:143)
         p1 = new(2, hd)
         add("pool2x(net1)", lambda: C.pool2x(plan.h32[1], p1))
@@ -196,18 +230,19 @@ class SelectiveUpdateBlock:
         add("pool2x(net0)", lambda: C.pool2x(plan.h32[0], p0))
         add("interp(net2)", lambda: C.resize(plan.h32[2], u2))
         self._gru(plan, "gru08", 1, [plan.inp16[1], p0, u2])
-        # encoder (core/update.py:62-70): motion = [conv(cat[cor, d]) (127) | disp (1)]
-        c1, c2, d1, d2, motion = new(0, 256), new(0, 256), new(0, 64), new(0, 64), new(0, hd)
-        self._conv(plan, "encoder.convc1", "convc1", [plan.corr16], [(1, [0])], "convc1", _lib.FSB_EPI_RELU, out=c1)
-        self._conv(plan, "encoder.convc2", "convc2", [c1], [(3, [0])], "convc2", _lib.FSB_EPI_RELU, out=c2)
-        add("encoder.convd1", lambda: C.conv7x7_c1(plan.disp, self.f["convd1.w"], self.f["convd1.b"], d1, 64, motion,
-                                                    hd - 1))
-        self._conv(plan, "encoder.convd2", "convd2", [d1], [(3, [0])], "convd2", _lib.FSB_EPI_RELU, out=d2)
-        self._conv(plan, "encoder.conv", "enc_conv", [c2, d2], [(3, [0, 1])], "enc_conv", _lib.FSB_EPI_RELU, out=motion)
+        add(JOIN, JOIN)
         # gru04: x = [inp[0], motion, interp(net[1])]                           (:151-153)
         u1 = new(0, hd)
         add("interp(net1)", lambda: C.resize(plan.h32[1], u1))
         self._gru(plan, "gru04", 0, [plan.inp16[0], motion, u1])
+        # mask head (core/update.py:134-139,158) -- side lane
+        add(FORK, FORK)
+        plan.lane = 1
+        m0 = new(0, 64)
+        self._conv(plan, "mask.0", "mask0", [plan.h16[0]], [(3, [0])], "mask0", _lib.FSB_EPI_RELU, out=m0)
+        self._conv(plan, "mask.2", "mask2", [m0], [(3, [0])], "mask2", _lib.FSB_EPI_RELU, out_f32=plan.mask,
+                   out_scale=0.25)
+        plan.lane = 0
         # disp head (core/update.py:20-32) with EdgeNextConvEncoder (core/submodule.py:565-591)
         y = [new(0, hd) for _ in range(3)]
         t, u = new(0, hd), new(0, 4 * hd)
@@ -220,11 +255,7 @@ class SelectiveUpdateBlock:
                        out=y[k + 1], res=y[k], gamma=self.f[f"gamma{i}"])
         self._conv(plan, "disp_head.conv.4", "head4", [y[2]], [(3, [0])], "head4", _lib.FSB_EPI_BIAS,
                    out_f32=plan.delta)
-        # mask head (core/update.py:134-139,158)
-        m0 = new(0, 64)
-        self._conv(plan, "mask.0", "mask0", [plan.h16[0]], [(3, [0])], "mask0", _lib.FSB_EPI_RELU, out=m0)
-        self._conv(plan, "mask.2", "mask2", [m0], [(3, [0])], "mask2", _lib.FSB_EPI_RELU, out_f32=plan.mask,
-                   out_scale=0.25)
+        add(JOIN, JOIN)
         plan.keep = [p1, p0, u2, c1, c2, d1, d2, motion, u1, y, t, u, m0]
         return plan
 
@@ -244,7 +275,7 @@ class SelectiveUpdateBlock:
             return torch.as_strided(corr, (B, H, W, Pp), (H * W * Pp, W * Pp, Pp, 1))
         return None
 
-    def _ingest(self, plan: _Plan, net, inp, att, corr: Tensor, disp: Tensor) -> None:
+    def _ingest(self, plan: _Plan, net, inp, att, corr: Optional[Tensor], disp: Tensor) -> None:
         for l in range(3):
             n = net[l]
             if not self._is_view_of(n, plan.h32[l]):
@@ -254,22 +285,53 @@ class SelectiveUpdateBlock:
                 C.nchw_to_nhwc(inp[l].float().contiguous(), plan.inp16[l], None)
                 plan.att[l].copy_(att[l].reshape(plan.att[l].shape))
                 plan.src_key[l] = key
-        plan.disp.copy_(disp)
-        if plan.own_corr:
-            C.nchw_to_nhwc(corr.float().contiguous(), plan.corr16, None)
+        if disp.data_ptr() != plan.disp.data_ptr():
+            plan.disp.copy_(disp)
+        if corr is not None:
+            view = self._corr_view(corr)
+            if view is None or view.data_ptr() != plan.corr16.data_ptr():
+                # the reference's fp32 (B, L*K*(Cg+1), H, W) tensor (or a foreign 16-bit one)
+                C.nchw_to_nhwc(corr.float().contiguous(), plan.corr16, None)
 
     # ---- one step -------------------------------------------------------------------------
-    def plan_for(self, B: int, H: int, W: int, corr16: Optional[Tensor] = None) -> _Plan:
-        key = (B, H, W, corr16.data_ptr() if corr16 is not None else 0)
+    def plan_for(self, B: int, H: int, W: int) -> _Plan:
+        key = (B, H, W)
         plan = self._plans.get(key)
         if plan is None:
-            plan = self._plans[key] = self._build_plan(B, H, W, corr16)
+            plan = self._plans[key] = self._build_plan(B, H, W)
         return plan
 
-    def run_steps(self, plan: _Plan) -> None:
-        """The launches of one refinement step on the current stream (no graph)."""
-        for fn in plan.steps:
-            fn()
+    def corr_buffer(self, B: int, H: int, W: int) -> Tensor:
+        """The plan's 16-bit (B,H,W,Cpad) lookup buffer: Combined_Geo_Encoding_Volume's fused
+        output writes here and convc1 reads it in place."""
+        return self.plan_for(B, H, W).corr16
+
+    def run_steps(self, plan: _Plan, lookup: bool = False) -> None:
+        """The launches of one refinement step, issued on the current stream and the plan's
+        side stream (no graph).  With ``lookup`` the bound geometry lookup runs first and the
+        disparity update (core/foundation_stereo.py:242) last: one whole loop iteration."""
+        main = torch.cuda.current_stream()
+        if lookup:
+            plan.lookup()
+        for fn, lane in zip(plan.steps, plan.lanes):
+            if fn is FORK:
+                plan.side.wait_stream(main)
+            elif fn is JOIN:
+                main.wait_stream(plan.side)
+            elif lane == 0:
+                fn()
+            else:
+                with torch.cuda.stream(plan.side):
+                    fn()
+        if lookup:
+            C.axpy(plan.disp, plan.delta)
+
+    def _capture(self, plan: _Plan, lookup: bool) -> torch.cuda.CUDAGraph:
+        g = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g):
+            self.run_steps(plan, lookup)
+        return g
 
     def _execute(self, plan: _Plan) -> None:
         plan.calls += 1
@@ -278,11 +340,7 @@ class SelectiveUpdateBlock:
         if plan.graph is None:
             if plan.calls == 1:  # first call eager: sets kernel attributes, warms the allocator
                 return self.run_steps(plan)
-            g = torch.cuda.CUDAGraph()
-            torch.cuda.synchronize()
-            with torch.cuda.graph(g):
-                self.run_steps(plan)
-            plan.graph = g
+            plan.graph = self._capture(plan, False)
         plan.graph.replay()
 
     @torch.no_grad()
@@ -293,7 +351,7 @@ class SelectiveUpdateBlock:
         if not disp.is_cuda:
             raise _lib.FsbError("SelectiveUpdateBlock runs on CUDA tensors only (no CPU path)")
         B, _, H, W = disp.shape
-        plan = self.plan_for(B, H, W, self._corr_view(corr))
+        plan = self.plan_for(B, H, W)
         self._ingest(plan, net, inp, att, corr, disp)
         self._execute(plan)
         for l in range(3):
@@ -301,3 +359,35 @@ class SelectiveUpdateBlock:
         return net, plan.mask, plan.delta
 
     __call__ = forward
+
+    # ---- the whole refinement loop (core/foundation_stereo.py:236-242) -----------------------
+    @torch.no_grad()
+    def refine(self, geo, net: Sequence[Tensor], inp: Sequence[Tensor], att: Sequence[Tensor], disp: Tensor,
+               iters: int) -> Tuple[Tensor, Tensor, List[Tensor]]:
+        """``iters`` x [geo lookup -> update block -> disp += delta] with every iteration ONE
+        CUDA-graph replay: the lookup writes the 16-bit NHWC tensor convc1 reads, the update
+        runs on the plan's static buffers and the disparity is updated in place, so there is no
+        host work or host sync between iterations.  ``geo`` is a Combined_Geo_Encoding_Volume
+        (its level buffers should have stable addresses -- ``workspace=`` -- or the graph is
+        re-captured).  Returns (disparity (B,1,H,W) fp32, mask features of the last step, net)."""
+        B, _, H, W = disp.shape
+        plan = self.plan_for(B, H, W)
+        self._ingest(plan, list(net), inp, att, None, disp.float())
+        key = tuple(t.data_ptr() for t in list(geo.geo_levels) + list(geo.corr_levels)) + (geo.radius,)
+        if plan.iter_key != key:
+            levels = (list(geo.geo_levels), list(geo.corr_levels), geo.radius)
+            from . import ops
+            plan.lookup = lambda: ops.geo_lookup_nhwc16(levels[0], levels[1], plan.disp, plan.coords, levels[2],
+                                                        plan.corr16)
+            plan.iter_key = key
+            plan.iter_graph = None
+            plan.iter_calls = 0
+        for _ in range(iters):
+            plan.iter_calls += 1
+            if not self.use_graph or plan.iter_calls == 1:
+                self.run_steps(plan, True)
+                continue
+            if plan.iter_graph is None:
+                plan.iter_graph = self._capture(plan, True)
+            plan.iter_graph.replay()
+        return plan.disp.clone(), plan.mask, [plan.h32[l].permute(0, 3, 1, 2) for l in range(3)]

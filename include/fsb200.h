@@ -98,6 +98,7 @@ int fsb_geo_pyramid(const float* vol, float* const* geo_levels, int B, int Cg, i
  *   out    : out_layout 0: (B, L*K*(Cg+1), H, W) fp32   -- the reference's tensor
  *            out_layout 1: (B, H, W, Cpad) fp16, Cpad = L*K*(Cg+1) rounded up to 64,
  *                          pad channels zero -- the A operand of encoder.convc1
+ *            out_layout 2: the same in bf16
  *   K = 2r+1, channel order per level: geo c*K+k (c<Cg), then K correlation taps.    */
 int fsb_geo_lookup(float* const* geo_levels, float* const* corr_levels, const float* disp,
                    const float* coords, void* out, int B, int Cg, int D, int H, int W, int W2,

@@ -235,3 +235,71 @@ def test_hot_path_refinement_loop(fsb):
     assert comb.shape == (1, 32, D, H, W)
     mad = (got.cpu() - want).abs().mean().item()
     assert mad <= 0.05, mad
+
+
+# ------------------------------------------------------------- fused lookup output / fused loop
+@pytest.mark.parametrize("cfg", [
+    # B, H, W, D, Cg, L, r, dtype
+    (1, 24, 40, 16, 28, 2, 4, torch.float16),
+    (2, 7, 23, 13, 28, 3, 4, torch.bfloat16),   # odd sizes, three levels
+    (1, 9, 31, 20, 12, 2, 2, torch.float16),    # other Cg / radius (generic-K kernel)
+    (1, 6, 17, 12, 10, 1, 3, torch.float16),    # Cg % 4 != 0 (scalar window loads)
+])
+def test_lookup_nhwc16_matches_fp32_layout(fsb, cfg):
+    """out_layout 1/2 (16-bit NHWC, the A operand of convc1) holds exactly the samples of
+    out_layout 0 rounded to the 16-bit type; pad channels are zero."""
+    from foundationstereo_b200 import ops
+    B, H, W, D, Cg, L, r, dtype = cfg
+    K = 2 * r + 1
+    x = oracle.make_inputs(B=B, C=16, H=H, W=W, D=D, Cg=Cg, seed=11)
+    dx = torch.linspace(-r, r, K).reshape(1, 1, -1, 1)
+    vol = fsb.Combined_Geo_Encoding_Volume(dev(x["fl"]), dev(x["fr"]), dev(x["volume"]), num_levels=L, dx=dx)
+    disp, coords = dev(x["disp"]), dev(x["coords"])
+    want = vol(disp, coords)                                    # (B, P, H, W) fp32
+    P = L * K * (Cg + 1)
+    cpad = (P + 63) // 64 * 64
+    buf = torch.full((B, H, W, cpad), 3.0, dtype=dtype, device="cuda")
+    view = vol.lookup_nhwc16(disp, coords, buf)
+    assert view.shape == want.shape and view.data_ptr() == buf.data_ptr()
+    eps = 2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7
+    diff = (view.float() - want).abs()
+    assert (diff <= eps * want.abs() + 1e-6).all(), diff.max().item()
+    assert (buf[..., P:] == 0).all()
+    # and against the CPU oracle
+    with torch.no_grad():
+        geo = oracle.GeoEncodingVolume(x["fl"], x["fr"], x["volume"], L, r)
+        ref = geo(x["disp"], x["coords"])
+    assert rel_err(view.float().cpu(), ref) <= 2 * eps
+
+
+def test_fused_loop_equals_stepwise_path(fsb):
+    """SelectiveUpdateBlock.refine (one CUDA graph per iteration: fused lookup -> update ->
+    disp += delta) against the drop-in sequence the unchanged reference caller executes
+    (geo_fn(disp, coords) fp32 -> update_block(...) -> disp + delta): same kernels, same
+    operands after the 16-bit rounding, so the results agree to accumulation-order noise."""
+    H, W, D, iters = 24, 40, 16, 5
+    p = oracle.make_update_block_params(seed=3, delta_scale=0.25)
+    x = oracle.make_inputs(B=1, C=32, H=H, W=W, D=D, Cg=28, seed=6)
+    c = lambda t: t.cuda()
+    dx = torch.linspace(-4, 4, 9).reshape(1, 1, -1, 1)
+    geo = fsb.Combined_Geo_Encoding_Volume(c(x["fl"]), c(x["fr"]), c(x["volume"]), num_levels=2, dx=dx)
+    inp, att = [c(t) for t in x["inp"]], [c(t) for t in x["att"]]
+    # step-wise, no graph
+    ub1 = fsb.SelectiveUpdateBlock(p, "cuda", use_graph=False)
+    net = [c(t) for t in x["net"]]
+    disp = c(x["disp"])
+    coords = c(x["coords"])
+    for _ in range(iters):
+        feat = geo(disp, coords)
+        net, mask1, delta = ub1(net, inp, feat, disp, att)
+        disp = disp + delta
+    # fused, graph replay from the third iteration on
+    ub2 = fsb.SelectiveUpdateBlock(p, "cuda", use_graph=True)
+    got, mask2, net2 = ub2.refine(geo, [c(t) for t in x["net"]], inp, att, c(x["disp"]), iters)
+    assert (got - disp).abs().max().item() <= 2e-3
+    assert rel_err(mask2, mask1) <= 5e-3
+    for a, b in zip(net2, net):
+        assert rel_err(a, b) <= 5e-3
+    # a second pair through the same plan (graph already captured) gives the same answer
+    got2, _, _ = ub2.refine(geo, [c(t) for t in x["net"]], inp, att, c(x["disp"]), iters)
+    assert torch.equal(got2, got)
