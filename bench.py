@@ -38,7 +38,8 @@ UNIT = "pairs/s"
 
 def workload_name():
     return ("hot path of FoundationStereo ViT-S config (BASELINE configs[1]): 1/4-res 120x160, C=128, max_disp=416 "
-            "(D=104), corr_levels=2, radius=4, 32 x (lookup + update block), 1 pair per GPU per step")
+            "(D=104), corr_levels=2, radius=4, 32 x (lookup + update block); a step = one batch of pairs per GPU "
+            "(config.pairs_per_gpu_per_step)")
 
 
 # --------------------------------------------------------------------------------------
@@ -209,7 +210,7 @@ def run_b200(args):
         # convenience: `python bench.py --gpus N` re-launches itself one rank per GPU
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 1000), os.path.abspath(__file__),
-               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup)]
+               "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup), "--pairs", str(args.pairs)]
         return subprocess.call(cmd)
 
     import torch
@@ -228,6 +229,7 @@ def run_b200(args):
     from foundationstereo_b200._lib import FSB_PREC_FP32
 
     c = dict(CFG)
+    c["B"] = args.pairs
     x = synthetic.hot_path_inputs(c["B"], c["C"], c["H"], c["W"], c["D"], c["Cp"], c["Cg"], seed=rank)
     state = synthetic.random_update_block_state(seed=0, corr_levels=c["L"], corr_radius=c["r"], volume_dim=c["Cg"])
     hp = fsb.StereoHotPath(state, max_disp=4 * c["D"], corr_levels=c["L"], corr_radius=c["r"], num_groups=c["G"],
@@ -291,13 +293,10 @@ def run_b200(args):
     ms_e2e = max(f0.elapsed_time(f1), 1e3 * (te1 - te0))
     d2h_bytes = out_host.numel() * out_host.element_size()
 
-    t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=device)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, ms_e2e = float(t[0]), float(t[1])
-    pairs = c["B"] * world * args.steps
-    value = pairs / (ms_total * 1e-3)
-    e2e_value = pairs / (ms_e2e * 1e-3)
+    # whole-job figures: SUM of pairs, MAX of device times over ranks (foundationstereo_b200/shard.py)
+    from foundationstereo_b200 import shard
+    pairs, ms_total, value = shard.reduce_throughput(c["B"] * args.steps, ms_total, device)
+    _, ms_e2e, e2e_value = shard.reduce_throughput(c["B"] * args.steps, ms_e2e, device)
 
     line = None
     if rank == 0:
@@ -421,6 +420,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--pairs", type=int, default=4, help="stereo pairs per GPU per step (one batch through the hot path)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     args = ap.parse_args()
     if args.impl == "reference":

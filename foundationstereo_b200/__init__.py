@@ -12,6 +12,7 @@ from .submodule import build_gwc_volume, build_concat_volume, build_combined_vol
 from .geometry import Combined_Geo_Encoding_Volume  # noqa: F401
 from .update import SelectiveUpdateBlock  # noqa: F401
 from .hotpath import StereoHotPath  # noqa: F401
+from . import shard  # noqa: F401
 from .patch import install, install_update_block, uninstall  # noqa: F401
 
 __all__ = [

@@ -71,6 +71,7 @@ _PROTOS = {
     "fsb_last_error": (c_char_p, []),
     "fsb_launch_count": (c_uint64, []),
     "fsb_volume_gwc_concat": (c_int, [c_void_p] * 6 + [c_int] * 8 + [c_void_p]),
+    "fsb_volume_combined": (c_int, [c_void_p] * 5 + [c_int] * 8 + [c_void_p]),
     "fsb_corr_pyramid": (c_int, [c_void_p, c_void_p, POINTER(c_void_p)] + [c_int] * 7 + [c_void_p]),
     "fsb_geo_pyramid": (c_int, [c_void_p, POINTER(c_void_p)] + [c_int] * 6 + [c_void_p]),
     "fsb_geo_lookup": (c_int, [POINTER(c_void_p), POINTER(c_void_p), c_void_p, c_void_p, c_void_p]

@@ -17,10 +17,10 @@
 //             TMA box (64, block_n) per K step.
 //   D       = fp32 accumulators in TMEM (up to two: the 3x3 "large" and 1x1 "small" GRU).
 //
-// Warp roles (224 threads): warp 0 = TMA producer of the activation tiles, warp 6 = TMA
+// Warp roles (352 threads): warp 0 = TMA producer of the activation tiles, warp 10 = TMA
 // producer of the weight tiles (one elected lane each), warp 1 = TMEM allocator + MMA issuer
-// (one elected lane), warps 2..5 = epilogue (tcgen05.ld, one pixel per thread, 32 output
-// channels per load).  A pipeline stage holds `kper` K steps (1, 2 or 4).  Stages are handed
+// (one elected lane), warps 2..9 = epilogue (tcgen05.ld, one pixel per thread, 32 output
+// channels per load, two warps per TMEM lane quarter).  A pipeline stage holds `kper` K steps (1, 2 or 4).  Stages are handed
 // over with mbarriers: full[s] (both producers -> MMA, transaction bytes), empty[s]
 // (tcgen05.commit -> producers), accum (last commit -> epilogue).
 //
@@ -37,7 +37,8 @@
 
 namespace fsb {
 
-constexpr int kConvThreads = 224;
+constexpr int kConvThreads = 352;  // 11 warps
+constexpr int kWarpB = 10;           // weight producer warp
 constexpr int kMaxSteps = 112;
 constexpr int kBM = 128;
 constexpr int kBK = 64;                      // 16-bit elements per K step (128 B)
@@ -153,6 +154,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
       : "r"(taddr)
       : "memory");
 }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major operand tile, 128-byte swizzle: rows of 128 B, 8-row atoms of 1024 B (SBO), descriptor
@@ -244,7 +254,7 @@ __device__ __forceinline__ void store32f(float* dst, const float (&f)[32]) {
 
 // ------------------------------------------------------------------------------------ kernel
 template <typename T, int EPI>
-__global__ void __launch_bounds__(kConvThreads)
+__global__ void __launch_bounds__(kConvThreads, 2)
 conv_umma_kernel(const __grid_constant__ ConvParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   __shared__ __align__(8) uint64_t bars[2 * 8 + 1];
@@ -282,15 +292,15 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     tma_prefetch_desc(&p.amap[0]);
   }
-  if (warp == 6 && lane == 0) tma_prefetch_desc(&p.wmap);
+  if (warp == kWarpB && lane == 0) tma_prefetch_desc(&p.wmap);
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
                  "r"((uint32_t)p.tmem_cols)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  if (warp >= 2 && warp < 6) {
-    for (int i = threadIdx.x - 64; i < p.nacc * p.BN; i += 128) {
+  if (warp >= 2 && warp < kWarpB) {
+    for (int i = threadIdx.x - 64; i < p.nacc * p.BN; i += 256) {
       const int a = i / p.BN, c = i - a * p.BN;
       bias_s[i] = __ldg(p.bias + (size_t)a * p.rows + n0 + c);
     }
@@ -320,7 +330,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
         if (++s == S) { s = 0; ph ^= 1; }
       }
     }
-  } else if (warp == 6) {
+  } else if (warp == kWarpB) {
     // ====================================================== TMA producer: weight tiles
     if (lane == 0) {
       int s = 0;
@@ -370,9 +380,13 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
       }
       umma_commit(bar_accum);  // all MMAs done -> accumulators complete
     }
-  } else if (warp < 6) {
+  } else if (warp < kWarpB) {
     // ======================================================================== epilogue
+    // 8 warps: warp w reads TMEM lane quarter (w & 3); the two warps of a quarter split the
+    // 32-column chunks between them (grp 0: even chunks, grp 1: odd chunks), which halves the
+    // serial instruction chain of the epilogue -- the whole cost of the small-K layers.
     const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int grp = (warp - 2) >> 2;
     const int r = q * 32 + lane;
     const int ty = r >> p.tw_log2, tx = r & (TW - 1);
     const int y = y0 + ty, x = x0 + tx;
@@ -385,11 +399,13 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
 
     if constexpr (EPI == FSB_EPI_GATE_ZR) {
       const int half = p.BN >> 1;
-      for (int a = 0; a < p.nacc; ++a) {
+      const int cpa = p.BN >> 5;  // chunks per accumulator
+      for (int ci = grp; ci < p.nacc * cpa; ci += 2) {
+        const int a = ci / cpa, c = (ci - a * cpa) << 5;
         T* zb = reinterpret_cast<T*>(a == 0 ? p.z_l : p.z_s);
         T* rb = reinterpret_cast<T*>(a == 0 ? p.rh_l : p.rh_s);
         const float* bias = bias_s + a * p.BN;
-        for (int c = 0; c < p.BN; c += 32) {
+        {
           uint32_t v[32];
           tmem_ld32(taddr + a * p.BN + c, v);
           tmem_ld_wait();
@@ -410,32 +426,46 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
         }
       }
     } else if constexpr (EPI == FSB_EPI_GATE_Q) {
+      // 16 columns per step: keeps the kernel under 93 registers so two CTAs share an SM
       const float att = valid ? __ldg(p.att + pix) : 0.f;
-      for (int c = 0; c < p.BN; c += 32) {
-        uint32_t v0[32], v1[32];
-        tmem_ld32(taddr + c, v0);
-        tmem_ld32(taddr + p.BN + c, v1);
+      for (int c = grp * 16; c < p.BN; c += 32) {
+        uint32_t v0[16], v1[16];
+        tmem_ld16(taddr + c, v0);
+        tmem_ld16(taddr + p.BN + c, v1);
         tmem_ld_wait();
         if (!valid) continue;
         const int ch = n0 + c;
-        float h[32], zl[32], zs[32];
-        load32f(p.h32 + pix * p.hidden + ch, h);
-        load32<T>(reinterpret_cast<const T*>(p.z_l) + pix * p.hidden + ch, zl);
-        load32<T>(reinterpret_cast<const T*>(p.z_s) + pix * p.hidden + ch, zs);
+        const float* hp = p.h32 + pix * p.hidden + ch;
+        const uint4* zlp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.z_l) + pix * p.hidden + ch);
+        const uint4* zsp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.z_s) + pix * p.hidden + ch);
+        float* ho = p.h32_out + pix * p.hidden + ch;
+        uint4* h16o = reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.h16_out) + pix * p.hidden + ch);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const float ql = tanh_f(__uint_as_float(v0[j]) + bias_s[c + j]);
-          const float qs = tanh_f(__uint_as_float(v1[j]) + bias_s[p.BN + c + j]);
-          const float hl = (1.f - zl[j]) * h[j] + zl[j] * ql;
-          const float hs = (1.f - zs[j]) * h[j] + zs[j] * qs;
-          h[j] = hs * att + hl * (1.f - att);
+        for (int o = 0; o < 2; ++o) {  // 8 channels at a time
+          const float4 ha = *reinterpret_cast<const float4*>(hp + 8 * o), hb = *reinterpret_cast<const float4*>(hp + 8 * o + 4);
+          const uint4 zlu = zlp[o], zsu = zsp[o];
+          float h[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
+          const uint32_t zlw[4] = {zlu.x, zlu.y, zlu.z, zlu.w}, zsw[4] = {zsu.x, zsu.y, zsu.z, zsu.w};
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float2 zl2 = unpack2<T>(zlw[j >> 1]), zs2 = unpack2<T>(zsw[j >> 1]);
+            const float zl = (j & 1) ? zl2.y : zl2.x, zs = (j & 1) ? zs2.y : zs2.x;
+            const float ql = tanh_f(__uint_as_float(v0[8 * o + j]) + bias_s[c + 8 * o + j]);
+            const float qs = tanh_f(__uint_as_float(v1[8 * o + j]) + bias_s[p.BN + c + 8 * o + j]);
+            const float hl = (1.f - zl) * h[j] + zl * ql;
+            const float hs = (1.f - zs) * h[j] + zs * qs;
+            h[j] = hs * att + hl * (1.f - att);
+          }
+          *reinterpret_cast<float4*>(ho + 8 * o) = make_float4(h[0], h[1], h[2], h[3]);
+          *reinterpret_cast<float4*>(ho + 8 * o + 4) = make_float4(h[4], h[5], h[6], h[7]);
+          uint4 u;
+          u.x = pack2<T>(h[0], h[1]); u.y = pack2<T>(h[2], h[3]); u.z = pack2<T>(h[4], h[5]); u.w = pack2<T>(h[6], h[7]);
+          h16o[o] = u;
         }
-        store32f(p.h32_out + pix * p.hidden + ch, h);
-        store32<T>(reinterpret_cast<T*>(p.h16_out) + pix * p.hidden + ch, h);
       }
     } else {
       T* out = reinterpret_cast<T*>(p.out);
-      for (int c = 0; c < p.BN; c += 32) {
+      for (int c = grp * 32; c < p.BN; c += 64) {
         uint32_t v[32];
         tmem_ld32(taddr + c, v);
         tmem_ld_wait();

@@ -26,7 +26,7 @@ template <typename T, bool VEC>
 __global__ void __launch_bounds__(kVolThreads)
 volume_kernel(const T* __restrict__ fl, const T* __restrict__ fr, const T* __restrict__ pl,
               const T* __restrict__ pr, T* __restrict__ gwc, T* __restrict__ cat, int C, int Cp, int G,
-              int H, int W, int D) {
+              int H, int W, int D, size_t gwc_bs, size_t cat_bs) {
   extern __shared__ __align__(16) float smem[];
   const int tid = threadIdx.x;
   const int b = blockIdx.x / H;
@@ -66,7 +66,7 @@ volume_kernel(const T* __restrict__ fl, const T* __restrict__ fr, const T* __res
     __syncthreads();
 
     const int nd4 = (D + 3) >> 2;
-    T* out0 = gwc + ((size_t)(b * G + unit) * D) * HW + (size_t)h * W;
+    T* out0 = gwc + (size_t)b * gwc_bs + ((size_t)unit * D) * HW + (size_t)h * W;
     for (int it = tid; it < nd4 * nw4; it += kVolThreads) {
       const int dq = it / nw4;
       const int w = (it - dq * nw4) << 2;
@@ -131,7 +131,7 @@ volume_kernel(const T* __restrict__ fl, const T* __restrict__ fr, const T* __res
     const int w = (rem - d * nw4) << 2;
     const float* s = smem + c * RS + Dpad + w - (right ? d : 0);
     const float v0 = s[0], v1 = s[1], v2 = s[2], v3 = s[3];
-    T* o = cat + ((size_t)(b * 2 * Cp + (right ? Cp : 0) + c0 + c) * D + d) * HW + (size_t)h * W + w;
+    T* o = cat + (size_t)b * cat_bs + ((size_t)((right ? Cp : 0) + c0 + c) * D + d) * HW + (size_t)h * W + w;
     if (VEC) {
       Quad<T>::store(o, v0, v1, v2, v3);
     } else {
@@ -145,8 +145,8 @@ volume_kernel(const T* __restrict__ fl, const T* __restrict__ fr, const T* __res
 
 template <typename T>
 static int launch_volume(const void* fl, const void* fr, const void* pl, const void* pr, void* gwc,
-                         void* cat, int B, int C, int Cp, int G, int H, int W, int D,
-                         cudaStream_t stream) {
+                         void* cat, int B, int C, int Cp, int G, int H, int W, int D, size_t gwc_bs,
+                         size_t cat_bs, cudaStream_t stream) {
   const int Wp = round_up(W, 4), Dpad = round_up(D, 4) + 4, RS = Dpad + Wp;
   const int cpg = gwc ? C / G : 0;
   const size_t smem_gwc = (size_t)(cpg * Wp + cpg * RS) * sizeof(float);
@@ -166,33 +166,51 @@ static int launch_volume(const void* fl, const void* fr, const void* pl, const v
     if (e != cudaSuccess) return cuda_fail(e, "fsb_volume_gwc_concat: cudaFuncSetAttribute");
   }
   kern<<<grid, kVolThreads, smem, stream>>>((const T*)fl, (const T*)fr, (const T*)pl, (const T*)pr,
-                                            (T*)gwc, (T*)cat, C, Cp, G, H, W, D);
+                                            (T*)gwc, (T*)cat, C, Cp, G, H, W, D, gwc_bs, cat_bs);
   FSB_CHECK_LAUNCH("fsb_volume_gwc_concat");
   return FSB_OK;
 }
 
 }  // namespace fsb
 
-extern "C" int fsb_volume_gwc_concat(const void* fl, const void* fr, const void* pl, const void* pr,
-                                     void* gwc, void* cat, int B, int C, int Cp, int G, int H, int W,
-                                     int D, int dtype, fsb_stream_t stream) {
+static int volume_entry(const void* fl, const void* fr, const void* pl, const void* pr, void* gwc, void* cat, int B,
+                        int C, int Cp, int G, int H, int W, int D, size_t gwc_bs, size_t cat_bs, int dtype,
+                        fsb_stream_t stream, const char* who) {
   using namespace fsb;
-  FSB_REQUIRE(gwc || cat, FSB_ERR_ARG, "fsb_volume_gwc_concat: both outputs are NULL");
-  FSB_REQUIRE(!gwc || (fl && fr), FSB_ERR_ARG, "fsb_volume_gwc_concat: gwc requested but fl/fr NULL");
-  FSB_REQUIRE(!cat || (pl && pr), FSB_ERR_ARG, "fsb_volume_gwc_concat: cat requested but pl/pr NULL");
-  FSB_REQUIRE(B > 0 && H > 0 && W > 0 && D > 0, FSB_ERR_ARG,
-              "fsb_volume_gwc_concat: non-positive size B=%d H=%d W=%d D=%d", B, H, W, D);
-  FSB_REQUIRE(!gwc || (G > 0 && C > 0 && C % G == 0), FSB_ERR_ARG,
-              "fsb_volume_gwc_concat: C=%d not divisible by G=%d", C, G);
-  FSB_REQUIRE(!cat || Cp > 0, FSB_ERR_ARG, "fsb_volume_gwc_concat: Cp=%d", Cp);
-  FSB_REQUIRE((long long)B * H < (1ll << 31) && G + 2 * ceil_div(Cp > 0 ? Cp : 1, kCatChunk) < 65536,
-              FSB_ERR_SHAPE, "fsb_volume_gwc_concat: grid too large");
+  FSB_REQUIRE(gwc || cat, FSB_ERR_ARG, "%s: both outputs are NULL", who);
+  FSB_REQUIRE(!gwc || (fl && fr), FSB_ERR_ARG, "%s: gwc requested but fl/fr NULL", who);
+  FSB_REQUIRE(!cat || (pl && pr), FSB_ERR_ARG, "%s: cat requested but pl/pr NULL", who);
+  FSB_REQUIRE(B > 0 && H > 0 && W > 0 && D > 0, FSB_ERR_ARG, "%s: non-positive size B=%d H=%d W=%d D=%d", who, B, H, W, D);
+  FSB_REQUIRE(!gwc || (G > 0 && C > 0 && C % G == 0), FSB_ERR_ARG, "%s: C=%d not divisible by G=%d", who, C, G);
+  FSB_REQUIRE(!cat || Cp > 0, FSB_ERR_ARG, "%s: Cp=%d", who, Cp);
+  FSB_REQUIRE((long long)B * H < (1ll << 31) && G + 2 * ceil_div(Cp > 0 ? Cp : 1, kCatChunk) < 65536, FSB_ERR_SHAPE,
+              "%s: grid too large", who);
   if (!gwc) G = 0;
   cudaStream_t s = (cudaStream_t)stream;
   switch (dtype) {
-    case FSB_F32: return launch_volume<float>(fl, fr, pl, pr, gwc, cat, B, C, Cp, G, H, W, D, s);
-    case FSB_F16: return launch_volume<__half>(fl, fr, pl, pr, gwc, cat, B, C, Cp, G, H, W, D, s);
-    case FSB_BF16: return launch_volume<__nv_bfloat16>(fl, fr, pl, pr, gwc, cat, B, C, Cp, G, H, W, D, s);
-    default: FSB_REQUIRE(false, FSB_ERR_ARG, "fsb_volume_gwc_concat: unknown dtype %d", dtype);
+    case FSB_F32: return launch_volume<float>(fl, fr, pl, pr, gwc, cat, B, C, Cp, G, H, W, D, gwc_bs, cat_bs, s);
+    case FSB_F16: return launch_volume<__half>(fl, fr, pl, pr, gwc, cat, B, C, Cp, G, H, W, D, gwc_bs, cat_bs, s);
+    case FSB_BF16: return launch_volume<__nv_bfloat16>(fl, fr, pl, pr, gwc, cat, B, C, Cp, G, H, W, D, gwc_bs, cat_bs, s);
+    default: FSB_REQUIRE(false, FSB_ERR_ARG, "%s: unknown dtype %d", who, dtype);
   }
+}
+
+extern "C" int fsb_volume_gwc_concat(const void* fl, const void* fr, const void* pl, const void* pr,
+                                     void* gwc, void* cat, int B, int C, int Cp, int G, int H, int W,
+                                     int D, int dtype, fsb_stream_t stream) {
+  const size_t hw = (size_t)(H > 0 ? H : 0) * (W > 0 ? W : 0) * (D > 0 ? D : 0);
+  return volume_entry(fl, fr, pl, pr, gwc, cat, B, C, Cp, G, H, W, D, (size_t)(G > 0 ? G : 0) * hw,
+                      (size_t)2 * (Cp > 0 ? Cp : 0) * hw, dtype, stream, "fsb_volume_gwc_concat");
+}
+
+extern "C" int fsb_volume_combined(const void* fl, const void* fr, const void* pl, const void* pr, void* out, int B,
+                                   int C, int Cp, int G, int H, int W, int D, int dtype, fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(fl && fr && pl && pr && out, FSB_ERR_ARG, "fsb_volume_combined: NULL pointer");
+  FSB_REQUIRE(B > 0 && H > 0 && W > 0 && D > 0 && G > 0 && Cp > 0, FSB_ERR_ARG, "fsb_volume_combined: non-positive size");
+  const size_t hw = (size_t)H * W * D;
+  const size_t bs = (size_t)(G + 2 * Cp) * hw;
+  const size_t esz = dtype == FSB_F32 ? 4 : 2;
+  void* cat = static_cast<char*>(out) + (size_t)G * hw * esz;
+  return volume_entry(fl, fr, pl, pr, out, cat, B, C, Cp, G, H, W, D, bs, bs, dtype, stream, "fsb_volume_combined");
 }

@@ -77,17 +77,9 @@ def combined_volume(fl: torch.Tensor, fr: torch.Tensor, pl: torch.Tensor, pr: to
     fl, fr, pl, pr = fl.contiguous(), fr.contiguous(), pl.contiguous(), pr.contiguous()
     B, C, H, W = fl.shape
     Cp = pl.shape[1]
-    if B != 1:
-        # the two halves are separate (B,*,D,H,W) tensors in the ABI; with B > 1 a shared
-        # allocation would interleave them per batch item, so build per item
-        return torch.cat([combined_volume(fl[b:b + 1], fr[b:b + 1], pl[b:b + 1], pr[b:b + 1], maxdisp, num_groups)
-                          for b in range(B)], 0)
-    out = torch.empty((1, num_groups + 2 * Cp, maxdisp, H, W), dtype=fl.dtype, device=fl.device)
-    gwc = out[:, :num_groups]
-    cat = out[:, num_groups:]
-    check(lib().fsb_volume_gwc_concat(fl.data_ptr(), fr.data_ptr(), pl.data_ptr(), pr.data_ptr(),
-                                      gwc.data_ptr(), cat.data_ptr(), 1, C, Cp, num_groups, H, W, maxdisp,
-                                      _DTYPE[fl.dtype], _stream()))
+    out = torch.empty((B, num_groups + 2 * Cp, maxdisp, H, W), dtype=fl.dtype, device=fl.device)
+    check(lib().fsb_volume_combined(fl.data_ptr(), fr.data_ptr(), pl.data_ptr(), pr.data_ptr(), out.data_ptr(),
+                                    B, C, Cp, num_groups, H, W, maxdisp, _DTYPE[fl.dtype], _stream()))
     return out
 
 

@@ -69,6 +69,11 @@ int fsb_volume_gwc_concat(const void* fl, const void* fr, const void* pl, const 
                           void* gwc, void* cat, int B, int C, int Cp, int G, int H, int W,
                           int D, int dtype, fsb_stream_t stream);
 
+/* The same launch writing ONE tensor out (B, G+2Cp, D, H, W) = torch.cat([gwc, cat], 1), which is what
+ * core/foundation_stereo.py:207-212 assembles with two Python loops and a torch.cat. */
+int fsb_volume_combined(const void* fl, const void* fr, const void* pl, const void* pr, void* out, int B, int C,
+                        int Cp, int G, int H, int W, int D, int dtype, fsb_stream_t stream);
+
 /* ---- kernel 2: init correlation + its avg-pool pyramid ---------------------------
  * replaces Combined_Geo_Encoding_Volume.corr (core/geometry.py:68-77) and the
  * init_corr pyramid (core/geometry.py:31,38-40).

@@ -57,6 +57,9 @@ def test_volumes_vs_oracle(fsb, dtype, shape):
     assert torch.equal(cat.cpu(), want_cat)
     tol = {torch.float32: TOL_FP32, torch.float16: 2e-3, torch.bfloat16: 1.6e-2}[dtype]
     assert rel_err(gwc.float().cpu(), want_gwc.float()) <= tol
+    # the one-launch combined volume (batched: fsb_volume_combined) is the cat of the two
+    comb = fsb.build_combined_volume(fl.cuda(), fr.cuda(), pl.cuda(), pr.cuda(), D, 8)
+    assert torch.equal(comb, torch.cat([gwc, cat], 1))
 
 
 def test_volumes_full_size_properties(fsb):

@@ -19,10 +19,16 @@ from foundationstereo_b200 import synthetic
 H = int(sys.argv[1]) if len(sys.argv) > 1 else 120
 W = int(sys.argv[2]) if len(sys.argv) > 2 else 160
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 20
-B, L, r, Cg = 1, 2, 4, 28
+B = int(sys.argv[4]) if len(sys.argv) > 4 else 1
+L, r, Cg = 2, 4, 28
 
 state = synthetic.random_update_block_state(seed=0, corr_levels=L, corr_radius=r, volume_dim=Cg)
-ub = fsb.SelectiveUpdateBlock(state, "cuda", use_graph=False)
+bn = {}
+for kv in os.environ.get("FSB_BN", "").split(","):
+    if "=" in kv:
+        k, v = kv.split("=")
+        bn[k] = int(v)
+ub = fsb.SelectiveUpdateBlock(state, "cuda", use_graph=False, block_n=bn or None)
 x = synthetic.hot_path_inputs(B, 16, H, W, 8)
 c = lambda t: t.cuda()
 net, inp, att = [c(t) for t in x["net"]], [c(t) for t in x["inp"]], [c(t) for t in x["att"]]
