@@ -306,20 +306,34 @@ def run_b200(args):
         D, G, L, r = c["D"], c["G"], c["L"], c["r"]
         geo = fsb.Combined_Geo_Encoding_Volume(dev["fl"], dev["fr"], dev["volume"], num_levels=L, dx=hp.dx)
         coords = torch.arange(c["W"], dtype=torch.float32, device=device).reshape(1, 1, -1, 1).repeat(c["B"], c["H"], 1, 1)
+        from foundationstereo_b200._lib import FSB_PREC_TF32X3
+        plan_b = hp.update_block.plan_for(c["B"], c["H"], c["W"])
         kern_ms = {
             "volume_gwc_concat": time_kernel(torch, lambda: ops.combined_volume(dev["fl"], dev["fr"], dev["pl"], dev["pr"], D, G), 20, flush),
-            "corr_pyramid": time_kernel(torch, lambda: ops.corr_pyramid(dev["fl"], dev["fr"], L, FSB_PREC_FP32), 20, flush),
+            "corr_pyramid": time_kernel(torch, lambda: ops.corr_pyramid(dev["fl"], dev["fr"], L, FSB_PREC_TF32X3), 20, flush),
+            "corr_pyramid_fp32_cuda_cores": time_kernel(torch, lambda: ops.corr_pyramid(dev["fl"], dev["fr"], L, FSB_PREC_FP32), 20, flush),
             "geo_pyramid": time_kernel(torch, lambda: ops.geo_pyramid(dev["volume"], L), 20, flush),
-            "geo_lookup": time_kernel(torch, lambda: geo(dev["disp"], coords), 20, flush),
+            "geo_lookup": time_kernel(torch, lambda: ops.geo_lookup_nhwc16(geo.geo_levels, geo.corr_levels, dev["disp"], coords, r, plan_b.corr16), 20, flush),
+            "geo_lookup_fp32_nchw": time_kernel(torch, lambda: geo(dev["disp"], coords), 20, flush),
         }
-        per_step = {"volume_gwc_concat": 1, "corr_pyramid": 1, "geo_pyramid": 1, "geo_lookup": c["iters"]}
+        per_step = {"volume_gwc_concat": 1, "corr_pyramid": 1, "corr_pyramid_fp32_cuda_cores": 0, "geo_pyramid": 1,
+                    "geo_lookup": c["iters"], "geo_lookup_fp32_nchw": 0}
         alg = algorithmic_bytes(c)
+        alg["corr_pyramid_fp32_cuda_cores"] = alg["corr_pyramid"]
+        alg["geo_lookup_fp32_nchw"] = alg["geo_lookup"]
+        # the fused lookup writes 16-bit NHWC rows of Cpad channels instead of fp32 NCHW
+        K_ = 2 * r + 1
+        cpad = (L * K_ * (c["Cg"] + 1) + 63) // 64 * 64
+        alg["geo_lookup"] = c["B"] * c["H"] * c["W"] * (4 + L * (c["Cg"] + 1) * (K_ + 1) * 4 + cpad * 2)
         kernels = {}
         for k, ms in kern_ms.items():
             gbs = alg[k] / (ms * 1e-3) / 1e9
             kernels[k] = {"ms": ms, "launches_per_step": per_step[k], "algorithmic_bytes": alg[k],
                           "achieved_gbs": gbs, "frac_of_measured_hbm": gbs / peaks["hbm_gbs"],
                           "share_of_step": ms * per_step[k] / (ms_total / args.steps)}
+        # the gwc half of kernel 1 is fp32-FMA bound, not HBM bound: C/G MACs per output element
+        gwc_macs = c["B"] * c["H"] * c["W"] * c["D"] * c["G"] * (c["C"] // c["G"])
+        kernels["volume_gwc_concat"]["fp32_fma_bound_ms"] = gwc_macs / (148 * 128 * 1.965e9) * 1e3
         top = max(kernels, key=lambda k: kernels[k]["share_of_step"])
         roofline = {"kernel": top, "bound": "hbm", "achieved": kernels[top]["achieved_gbs"], "peak": peaks["hbm_gbs"],
                     "unit": "GB/s", "frac": kernels[top]["frac_of_measured_hbm"], "traffic": None,

@@ -13,7 +13,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG, "libfsb200.so")
 
 FSB_F32, FSB_F16, FSB_BF16 = 0, 1, 2
-FSB_PREC_FP32, FSB_PREC_TF32, FSB_PREC_F16, FSB_PREC_BF16 = 0, 1, 2, 3
+FSB_PREC_FP32, FSB_PREC_TF32, FSB_PREC_F16, FSB_PREC_BF16, FSB_PREC_TF32X3 = 0, 1, 2, 3, 4
 FSB_MAX_LEVELS = 6
 FSB_MAX_SRC = 4
 FSB_EPI_BIAS, FSB_EPI_RELU, FSB_EPI_GATE_ZR, FSB_EPI_GATE_Q = 0, 1, 2, 3

@@ -80,4 +80,8 @@ struct LevelPtrs {
   float* p[FSB_MAX_LEVELS];
 };
 
+// corr_umma.cu: init correlation on tcgen05 (nprod 1 = TF32, 3 = 3xTF32 split, fp32-accurate)
+int launch_corr_umma(const float* f1, const float* f2, const LevelPtrs& lv, int B, int C, int H, int W1, int W2, int L,
+                     int nprod, cudaStream_t stream);
+
 }  // namespace fsb

@@ -170,6 +170,91 @@ geo_pyramid_kernel(const float* __restrict__ vol, LevelPtrs lv, int Cg, int D, i
   if (L > 3) write_level<3>(t, lv.p[3], Cg, D, d0, p0, wvalid, tid);
 }
 
+// Kernel 2b, fast path for compile-time Cg (28 in FoundationStereo): same tile (32 w x 8 d x Cg)
+// but NO per-element index arithmetic -- the generic kernel above spends ~100 instructions per
+// element on runtime divisions and is issue-bound at 1/3 of HBM speed.  Here thread j owns
+// element j = dd*Cg + c of every pixel's 8*Cg-float output run (level 0) and loops over the 32
+// pixels: smem reads t[j][w] are conflict free (row stride 33), global writes are whole
+// 128-byte lines of a contiguous run, and the pooled levels reuse the same shared tile.
+template <int CG>
+__global__ void __launch_bounds__(256)
+geo_pyramid_fast_kernel(const float* __restrict__ vol, LevelPtrs lv, int D, int H, int W, int L) {
+  constexpr int R0 = kGeoTD * CG;  // rows of the tile = floats of a level-0 run
+  static_assert(R0 <= 256, "one thread per run element");
+  __shared__ float t[R0][kGeoTW + 1];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int w0 = blockIdx.x * kGeoTW, d0 = blockIdx.y * kGeoTD;
+  const int bh = blockIdx.z, b = bh / H, h = bh - b * H;
+  const size_t HW = (size_t)H * W;
+  const float* src = vol + (size_t)b * CG * D * HW + (size_t)h * W + w0;
+  const bool wok = w0 + lane < W;
+  // loads: warp = one (c, dd) row of 32 consecutive w (one 128-byte line), 8 rows in flight per warp
+  // (all CG loads of a warp are issued before the first is used: ~14 KB in flight per CTA)
+  static_assert(kGeoTD == 8, "row r = c*8 + dd with r = warp + 8k  =>  dd = warp, c = k");
+  float v[CG];
+  const bool dok = wok && d0 + warp < D;
+#pragma unroll
+  for (int k = 0; k < CG; ++k) v[k] = dok ? __ldg(src + ((size_t)k * D + d0 + warp) * HW + lane) : 0.f;
+#pragma unroll
+  for (int k = 0; k < CG; ++k) t[warp * CG + k][lane] = v[k];
+  __syncthreads();
+  const size_t p0 = (size_t)bh * W + w0;
+  const int wvalid = min(kGeoTW, W - w0);
+  // level 0: run element j = dd*CG + c
+  if (tid < R0) {
+    const int dd = tid / CG;
+    if (d0 + dd < D) {
+      float* o = lv.p[0] + (p0 * D + d0) * CG + tid;
+      for (int w = 0; w < wvalid; ++w) o[(size_t)w * D * CG] = t[tid][w];
+    }
+  }
+  // pooled levels: element j = jj*CG + c of a run of (8 >> l)*CG floats; the warps not needed by a
+  // level are the ones that start on the next (levels are issued from the top thread ids down)
+  if (L > 1) {
+    const int u = 255 - tid;
+    if (u < R0 / 2) {
+      const int jj = u / CG, c = u - jj * CG, D1 = D >> 1, dl = (d0 >> 1) + jj;
+      if (dl < D1) {
+        float* o = lv.p[1] + (p0 * D1 + dl) * CG + c;
+        const float* a = t[(2 * jj) * CG + c];
+        const float* bb = t[(2 * jj + 1) * CG + c];
+        for (int w = 0; w < wvalid; ++w) o[(size_t)w * D1 * CG] = (a[w] + bb[w]) * 0.5f;
+      }
+    }
+  }
+  if (L > 2) {
+    for (int l = 2; l < L; ++l) {
+      const int rows = kGeoTD >> l, Dl = D >> l;
+      if (tid < rows * CG) {
+        const int jj = tid / CG, c = tid - jj * CG, dl = (d0 >> l) + jj;
+        if (dl < Dl) {
+          float* o = lv.p[l] + (p0 * Dl + dl) * CG + c;
+          for (int w = 0; w < wvalid; ++w) {
+            // mean of adjacent pairs, level by level (same rounding as pooling level l-1 again)
+            float acc;
+            if (l == 2) {
+              const float x0 = (t[(4 * jj) * CG + c][w] + t[(4 * jj + 1) * CG + c][w]) * 0.5f;
+              const float x1 = (t[(4 * jj + 2) * CG + c][w] + t[(4 * jj + 3) * CG + c][w]) * 0.5f;
+              acc = (x0 + x1) * 0.5f;
+            } else {
+              float y[2];
+#pragma unroll
+              for (int q = 0; q < 2; ++q) {
+                const int e = 8 * jj + 4 * q;
+                const float x0 = (t[e * CG + c][w] + t[(e + 1) * CG + c][w]) * 0.5f;
+                const float x1 = (t[(e + 2) * CG + c][w] + t[(e + 3) * CG + c][w]) * 0.5f;
+                y[q] = (x0 + x1) * 0.5f;
+              }
+              acc = (y[0] + y[1]) * 0.5f;
+            }
+            o[(size_t)w * Dl * CG] = acc;
+          }
+        }
+      }
+    }
+  }
+}
+
 // =====================================================================================
 // Kernel 3: lookup.  One CTA = 32 consecutive pixels of one image row, all levels.
 //   phase 0: per (pixel, level): sampling positions exactly as the reference computes
@@ -411,8 +496,8 @@ extern "C" int fsb_corr_pyramid(const float* f1, const float* f2, float* const* 
   FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W1 > 0 && W2 > 0, FSB_ERR_ARG, "fsb_corr_pyramid: non-positive size");
   FSB_REQUIRE(L >= 1 && L <= 4, FSB_ERR_SHAPE, "fsb_corr_pyramid: num_levels=%d outside [1,4]", L);
   FSB_REQUIRE((W2 >> (L - 1)) >= 1, FSB_ERR_SHAPE, "fsb_corr_pyramid: W2=%d too small for %d levels", W2, L);
-  FSB_REQUIRE(precision == FSB_PREC_FP32, FSB_ERR_ARG,
-              "fsb_corr_pyramid: precision %d not available (only FSB_PREC_FP32)", precision);
+  FSB_REQUIRE(precision == FSB_PREC_FP32 || precision == FSB_PREC_TF32 || precision == FSB_PREC_TF32X3, FSB_ERR_ARG,
+              "fsb_corr_pyramid: precision %d (FSB_PREC_FP32, FSB_PREC_TF32 or FSB_PREC_TF32X3)", precision);
   FSB_REQUIRE((long long)B * H < 65536, FSB_ERR_SHAPE, "fsb_corr_pyramid: B*H=%lld >= 65536", (long long)B * H);
   LevelPtrs lv{};
   for (int l = 0; l < L; ++l) {
@@ -420,6 +505,8 @@ extern "C" int fsb_corr_pyramid(const float* f1, const float* f2, float* const* 
     FSB_REQUIRE(aligned16(corr_levels[l]), FSB_ERR_ALIGN, "fsb_corr_pyramid: level %d not 16-byte aligned", l);
     lv.p[l] = corr_levels[l];
   }
+  if (precision != FSB_PREC_FP32)
+    return launch_corr_umma(f1, f2, lv, B, C, H, W1, W2, L, precision == FSB_PREC_TF32X3 ? 3 : 1, (cudaStream_t)stream);
   dim3 grid(ceil_div(W2, 128), ceil_div(W1, 64), B * H);
   corr_fp32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(f1, f2, lv, C, H, W1, W2, L);
   FSB_CHECK_LAUNCH("fsb_corr_pyramid");
@@ -446,7 +533,10 @@ extern "C" int fsb_geo_pyramid(const float* vol, float* const* geo_levels, int B
     if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_pyramid: cudaFuncSetAttribute");
   }
   dim3 grid(ceil_div(W, kGeoTW), ceil_div(D, kGeoTD), B * H);
-  geo_pyramid_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(vol, lv, Cg, D, H, W, L);
+  if (Cg == 28)
+    geo_pyramid_fast_kernel<28><<<grid, 256, 0, (cudaStream_t)stream>>>(vol, lv, D, H, W, L);
+  else
+    geo_pyramid_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(vol, lv, Cg, D, H, W, L);
   FSB_CHECK_LAUNCH("fsb_geo_pyramid");
   return FSB_OK;
 }

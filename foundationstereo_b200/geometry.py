@@ -18,7 +18,7 @@ from . import _lib, ops
 
 class Combined_Geo_Encoding_Volume:
     def __init__(self, init_fmap1: torch.Tensor, init_fmap2: torch.Tensor, geo_volume: torch.Tensor,
-                 num_levels: int = 2, dx: Optional[torch.Tensor] = None, precision: int = _lib.FSB_PREC_FP32,
+                 num_levels: int = 2, dx: Optional[torch.Tensor] = None, precision: int = _lib.FSB_PREC_TF32X3,
                  workspace: Optional[dict] = None, nhwc16_out=None):
         """``workspace``: optional {"corr": [...], "geo": [...]} caller-owned level buffers of the
         right shapes (stable addresses, so a CUDA graph that holds the lookup can be replayed
@@ -94,5 +94,5 @@ class Combined_Geo_Encoding_Volume:
         """(B,C,H,W1),(B,C,H,W2) -> (B,H,W1,1,W2) fp32 (core/geometry.py:68-77)."""
         B, _, H, W1 = fmap1.shape
         W2 = fmap2.shape[3]
-        (c,) = ops.corr_pyramid(fmap1, fmap2, 1, _lib.FSB_PREC_FP32)
+        (c,) = ops.corr_pyramid(fmap1, fmap2, 1, _lib.FSB_PREC_TF32X3)
         return c.reshape(B, H, W1, 1, W2)

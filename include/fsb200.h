@@ -47,7 +47,9 @@ enum fsb_precision {
   FSB_PREC_FP32 = 0, /* fp32 FFMA, the parity mode (<= 1e-4 rel of the fp32 reference) */
   FSB_PREC_TF32 = 1, /* tcgen05 kind::tf32, fp32 accumulate in TMEM */
   FSB_PREC_F16 = 2,  /* tcgen05 kind::f16, fp16 operands, fp32 accumulate in TMEM */
-  FSB_PREC_BF16 = 3  /* tcgen05 kind::f16, bf16 operands, fp32 accumulate in TMEM */
+  FSB_PREC_BF16 = 3, /* tcgen05 kind::f16, bf16 operands, fp32 accumulate in TMEM */
+  FSB_PREC_TF32X3 = 4 /* tcgen05 kind::tf32 on hi/lo split operands (hi*hi + hi*lo + lo*hi): fp32-accurate
+                         (~1e-6 relative), the tensor-core parity mode */
 };
 
 int fsb_version(void);
@@ -80,7 +82,8 @@ int fsb_volume_combined(const void* fl, const void* fr, const void* pl, const vo
  *   f1, f2      : (B,C,H,W1), (B,C,H,W2) fp32
  *   corr_levels : HOST array of L device pointers; level l is (B*H*W1, W2 >> l) fp32,
  *                 level l+1 = mean of adjacent pairs of level l (floor length)
- * precision: FSB_PREC_FP32 (parity) or FSB_PREC_TF32.                                */
+ * precision: FSB_PREC_FP32 (CUDA-core FFMA), FSB_PREC_TF32X3 (tcgen05, fp32-accurate: both meet the
+ * 1e-4 parity bar) or FSB_PREC_TF32 (tcgen05 single pass, ~5e-4, reported separately).   */
 int fsb_corr_pyramid(const float* f1, const float* f2, float* const* corr_levels, int B,
                      int C, int H, int W1, int W2, int L, int precision, fsb_stream_t stream);
 
