@@ -18,6 +18,7 @@ FSB_MAX_LEVELS = 6
 FSB_MAX_SRC = 4
 FSB_EPI_BIAS, FSB_EPI_RELU, FSB_EPI_GATE_ZR, FSB_EPI_GATE_Q = 0, 1, 2, 3
 FSB_EPI_GELU, FSB_EPI_SCALE_RES = 4, 5
+FSB_CONV_LAYOUT_TAP, FSB_CONV_LAYOUT_HALO = 0, 1
 
 
 class FsbError(RuntimeError):
@@ -48,6 +49,7 @@ class ConvArgs(ctypes.Structure):
         ("Cout", c_int),
         ("block_n", c_int),
         ("stages", c_int),
+        ("layout", c_int),
         ("epilogue", c_int),
         ("out", c_void_p),
         ("ld_out", c_int),
@@ -70,6 +72,7 @@ _PROTOS = {
     "fsb_version": (c_int, []),
     "fsb_last_error": (c_char_p, []),
     "fsb_launch_count": (c_uint64, []),
+    "fsb_set_pdl": (c_int, [c_int]),
     "fsb_volume_gwc_concat": (c_int, [c_void_p] * 6 + [c_int] * 8 + [c_void_p]),
     "fsb_volume_combined": (c_int, [c_void_p] * 5 + [c_int] * 8 + [c_void_p]),
     "fsb_corr_pyramid": (c_int, [c_void_p, c_void_p, POINTER(c_void_p)] + [c_int] * 7 + [c_void_p]),

@@ -29,10 +29,12 @@ def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
-def pack_segment(w: Tensor, src_channels: Sequence[Tuple[int, int]]) -> Tensor:
-    """(Cout, Cin, k, k) -> (Cout, k*k*sum(Cpad)) in the K order of the kernel: tap (ky, kx)
-    row-major, then source, then channel.  ``src_channels`` lists (real, padded) channels
-    of each source in concatenation order; pad channels get zero weights."""
+def pack_segment(w: Tensor, src_channels: Sequence[Tuple[int, int]], layout: int = 0) -> Tensor:
+    """(Cout, Cin, k, k) -> (Cout, k*k*sum(Cpad)) in the K order of the kernel.
+    layout 0 (FSB_CONV_LAYOUT_TAP): tap (ky, kx) row-major, then source, then channel.
+    layout 1 (FSB_CONV_LAYOUT_HALO): source, then 64-channel chunk, then kx, then ky, then channel.
+    ``src_channels`` lists (real, padded) channels of each source in concatenation order;
+    pad channels get zero weights."""
     if w.dim() == 2:  # nn.Linear == 1x1 convolution
         w = w[:, :, None, None]
     cout, cin, kh, kw = w.shape
@@ -43,8 +45,13 @@ def pack_segment(w: Tensor, src_channels: Sequence[Tuple[int, int]]) -> Tensor:
         part = wt[..., o:o + real]
         if padded > real:
             part = torch.nn.functional.pad(part, (0, padded - real))
+        if layout == _lib.FSB_CONV_LAYOUT_HALO:
+            assert padded % KBLK == 0
+            part = part.reshape(cout, kh, kw, padded // KBLK, KBLK).permute(0, 3, 2, 1, 4).reshape(cout, -1)
         parts.append(part)
         o += real
+    if layout == _lib.FSB_CONV_LAYOUT_HALO:
+        return torch.cat(parts, 1)
     return torch.cat(parts, -1).reshape(cout, -1)
 
 
@@ -78,7 +85,7 @@ class ConvLaunch:
                  gamma: Optional[Tensor] = None, h32: Optional[Tensor] = None, att: Optional[Tensor] = None,
                  z_l: Optional[Tensor] = None, z_s: Optional[Tensor] = None, rh_l: Optional[Tensor] = None,
                  rh_s: Optional[Tensor] = None, h32_out: Optional[Tensor] = None, h16_out: Optional[Tensor] = None,
-                 hidden: int = 0, stages: int = 0, name: str = ""):
+                 hidden: int = 0, stages: int = 0, layout: int = 0, name: str = ""):
         a = ConvArgs()
         B, H, W, _ = srcs[0].shape
         self.dtype = _DT[srcs[0].dtype]
@@ -103,6 +110,7 @@ class ConvLaunch:
         assert bias.dtype == torch.float32 and bias.numel() == len(segs) * rows, (name, bias.shape, rows)
         a.weight, a.bias = weight.data_ptr(), bias.data_ptr()
         a.rows, a.Cout, a.block_n, a.stages, a.epilogue = rows, cout, block_n, stages, epilogue
+        a.layout = layout
         ptr = lambda t: t.data_ptr() if t is not None else None
         if out is not None:
             a.out, a.ld_out, a.ch_off = out.data_ptr(), out.shape[3], ch_off

@@ -35,6 +35,33 @@ inline int cuda_fail(cudaError_t e, const char* what) {
     ::fsb::count_launch();                                       \
   } while (0)
 
+// Programmatic dependent launch (PDL).  Every kernel of the library calls pdl_wait() before it touches
+// memory another kernel may have written and pdl_launch_dependents() as soon as its prologue is done; with
+// the launch attribute below the next kernel on the stream (also inside a captured CUDA graph) is scheduled
+// while this one drains, so its launch latency and prologue (barrier init, TMEM allocation, descriptor and
+// weight prefetch) overlap the predecessor's tail.  Without the attribute both instructions are no-ops.
+bool pdl_enabled();
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                 Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 inline int round_up(int a, int b) { return ceil_div(a, b) * b; }

@@ -57,6 +57,7 @@ struct alignas(64) ConvParams {
   int nsteps;
   int H, W, tiles_x, tiles_y, tw_log2;
   int BN, nacc, tmem_cols, stages, kper;
+  int SA, SB;  // halo kernel: activation / weight ring depths
   uint32_t idesc;
   int rows, Cout;
   const float* bias;
@@ -124,6 +125,22 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
 }
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
+}
+
+// One lane of a converged warp (elect.sync).  The role loops below are executed by the WHOLE warp with
+// warp-uniform state (the warp index comes from a shuffle, so the compiler knows the role branches are
+// uniform) and only the TMA / MMA / commit instructions sit under this predicate.  Written the other
+// way round -- `if (lane == 0) { loop }` -- the compiler cannot keep the operands of the uniform-datapath
+// instructions (UTMALDG, UTCHMMA) in uniform registers and wraps every one of them in an
+// ELECT / R2UR / BRA.U.ANY "waterfall" loop, which made instruction issue the bottleneck of the kernel.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred P;\n\t"
+      "elect.sync _|P, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, P;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
 }
 
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -252,6 +269,121 @@ __device__ __forceinline__ void store32f(float* dst, const float (&f)[32]) {
   for (int q = 0; q < 8; ++q) d[q] = make_float4(f[4 * q + 0], f[4 * q + 1], f[4 * q + 2], f[4 * q + 3]);
 }
 
+// ------------------------------------------------------------------------------------ epilogue
+// One thread = one pixel (TMEM lane); `taddr` = lane quarter + first column of the pixel tile's
+// accumulators; the thread handles the 32-column (16 for GATE_Q) chunks c_first, c_first + c_stride, ...
+template <typename T, int EPI>
+__device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* bias_s, uint32_t taddr, bool valid,
+                                              size_t pix, int b, int y, int x, int n0, int nt, int c_first,
+                                              int c_stride) {
+  if constexpr (EPI == FSB_EPI_GATE_ZR) {
+    const int half = p.BN >> 1;
+    const int cpa = p.BN >> 5;  // chunks per accumulator
+    for (int ci = c_first; ci < p.nacc * cpa; ci += c_stride) {
+      const int a = ci / cpa, c = (ci - a * cpa) << 5;
+      T* zb = reinterpret_cast<T*>(a == 0 ? p.z_l : p.z_s);
+      T* rb = reinterpret_cast<T*>(a == 0 ? p.rh_l : p.rh_s);
+      const float* bias = bias_s + a * p.BN;
+      {
+        uint32_t v[32];
+        tmem_ld32(taddr + a * p.BN + c, v);
+        tmem_ld_wait();
+        if (!valid) continue;
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = sigmoid_f(__uint_as_float(v[j]) + bias[c + j]);
+        if (c < half) {
+          store32<T>(zb + pix * p.hidden + nt * half + c, f);
+        } else {
+          const int ch = nt * half + (c - half);
+          float h[32];
+          load32f(p.h32 + pix * p.hidden + ch, h);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] *= h[j];
+          store32<T>(rb + pix * p.hidden + ch, f);
+        }
+      }
+    }
+  } else if constexpr (EPI == FSB_EPI_GATE_Q) {
+    // 16 columns per step: keeps the kernel under 93 registers so two CTAs share an SM
+    const float att = valid ? __ldg(p.att + pix) : 0.f;
+    for (int c = c_first * 16; c < p.BN; c += 16 * c_stride) {
+      uint32_t v0[16], v1[16];
+      tmem_ld16(taddr + c, v0);
+      tmem_ld16(taddr + p.BN + c, v1);
+      tmem_ld_wait();
+      if (!valid) continue;
+      const int ch = n0 + c;
+      const float* hp = p.h32 + pix * p.hidden + ch;
+      const uint4* zlp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.z_l) + pix * p.hidden + ch);
+      const uint4* zsp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.z_s) + pix * p.hidden + ch);
+      float* ho = p.h32_out + pix * p.hidden + ch;
+      uint4* h16o = reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.h16_out) + pix * p.hidden + ch);
+#pragma unroll
+      for (int o = 0; o < 2; ++o) {  // 8 channels at a time
+        const float4 ha = *reinterpret_cast<const float4*>(hp + 8 * o), hb = *reinterpret_cast<const float4*>(hp + 8 * o + 4);
+        const uint4 zlu = zlp[o], zsu = zsp[o];
+        float h[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
+        const uint32_t zlw[4] = {zlu.x, zlu.y, zlu.z, zlu.w}, zsw[4] = {zsu.x, zsu.y, zsu.z, zsu.w};
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float2 zl2 = unpack2<T>(zlw[j >> 1]), zs2 = unpack2<T>(zsw[j >> 1]);
+          const float zl = (j & 1) ? zl2.y : zl2.x, zs = (j & 1) ? zs2.y : zs2.x;
+          const float ql = tanh_f(__uint_as_float(v0[8 * o + j]) + bias_s[c + 8 * o + j]);
+          const float qs = tanh_f(__uint_as_float(v1[8 * o + j]) + bias_s[p.BN + c + 8 * o + j]);
+          const float hl = (1.f - zl) * h[j] + zl * ql;
+          const float hs = (1.f - zs) * h[j] + zs * qs;
+          h[j] = hs * att + hl * (1.f - att);
+        }
+        *reinterpret_cast<float4*>(ho + 8 * o) = make_float4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<float4*>(ho + 8 * o + 4) = make_float4(h[4], h[5], h[6], h[7]);
+        uint4 u;
+        u.x = pack2<T>(h[0], h[1]); u.y = pack2<T>(h[2], h[3]); u.z = pack2<T>(h[4], h[5]); u.w = pack2<T>(h[6], h[7]);
+        h16o[o] = u;
+      }
+    }
+  } else {
+    T* out = reinterpret_cast<T*>(p.out);
+    for (int c = c_first * 32; c < p.BN; c += 32 * c_stride) {
+      uint32_t v[32];
+      tmem_ld32(taddr + c, v);
+      tmem_ld_wait();
+      const int n = n0 + c;
+      if (!valid || n >= p.Cout) continue;
+      const bool full = (n + 32 <= p.Cout);
+      float f[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        float a = __uint_as_float(v[j]) + bias_s[c + j];  // rows beyond Cout carry zero bias
+        if constexpr (EPI == FSB_EPI_RELU) a = fmaxf(a, 0.f);
+        if constexpr (EPI == FSB_EPI_GELU) a = gelu_f(a);
+        f[j] = a;
+      }
+      if constexpr (EPI == FSB_EPI_SCALE_RES) {
+        float rres[32];
+        load32<T>(reinterpret_cast<const T*>(p.res) + pix * p.ld_res + n, rres);  // Cout % 32 == 0 (host check)
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = rres[j] + __ldg(p.gamma + n + j) * f[j];
+      }
+      if (out != nullptr) {
+        T* o = out + pix * p.ld_out + p.ch_off + n;
+        if (full) {
+          store32<T>(o, f);
+        } else {
+          for (int j = 0; j < 32 && n + j < p.Cout; ++j) o[j] = from_f32<T>(f[j]);
+        }
+      }
+      if (p.out_f32 != nullptr) {
+        const size_t hw = (size_t)p.H * p.W;
+        float* o = p.out_f32 + ((size_t)b * p.Cout + n) * hw + (size_t)y * p.W + x;
+#pragma unroll 4
+        for (int j = 0; j < 32; ++j)
+          if (full || n + j < p.Cout) o[(size_t)j * hw] = f[j] * p.out_scale;
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------ kernel
 template <typename T, int EPI>
 __global__ void __launch_bounds__(kConvThreads, 2)
@@ -261,7 +393,8 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
   __shared__ uint32_t tmem_slot;
   __shared__ __align__(16) float bias_s[2 * 256];  // [nacc][BN] bias of this CTA's output channels
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);  // warp-uniform for the compiler
+  const int lane = threadIdx.x & 31;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int kper = p.kper;
   const uint32_t b_tile_bytes = (uint32_t)p.BN * (kBK * 2);
@@ -309,15 +442,20 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
+  // PDL: the prologue above (and the weight producer below, which only reads parameters that no kernel
+  // writes) overlaps the tail of the previous kernel; everything that touches activations waits here.
+  pdl_launch_dependents();
+  if (warp != kWarpB) pdl_wait();
 
   if (warp == 0) {
     // ================================================== TMA producer: activation tiles
-    if (lane == 0) {
-      int s = 0;
-      uint32_t ph = 0;
-      for (int i = 0; i < p.nsteps; i += kper) {
-        const int n = min(kper, p.nsteps - i);
-        if (i >= S * kper) mbar_wait(bar_empty + 8 * s, ph ^ 1);
+    int s = 0;
+    uint32_t ph = 0;
+    for (int i = 0; i < p.nsteps; i += kper) {
+      const int n = min(kper, p.nsteps - i);
+      if (i >= S * kper) mbar_wait(bar_empty + 8 * s, ph ^ 1);
+      __syncwarp();
+      if (elect_one()) {
         const uint32_t full = bar_full + 8 * s;
         uint32_t dst = smem_base + s * stage_bytes;
         mbar_expect_tx(full, (uint32_t)n * kATileBytes);
@@ -327,17 +465,18 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
           tma_load_4d(dst, &p.amap[src], full, chunk * kBK, x0 + dx, y0 + dy, b);
           dst += kATileBytes;
         }
-        if (++s == S) { s = 0; ph ^= 1; }
       }
+      if (++s == S) { s = 0; ph ^= 1; }
     }
   } else if (warp == kWarpB) {
     // ====================================================== TMA producer: weight tiles
-    if (lane == 0) {
-      int s = 0;
-      uint32_t ph = 0;
-      for (int i = 0; i < p.nsteps; i += kper) {
-        const int n = min(kper, p.nsteps - i);
-        if (i >= S * kper) mbar_wait(bar_empty + 8 * s, ph ^ 1);
+    int s = 0;
+    uint32_t ph = 0;
+    for (int i = 0; i < p.nsteps; i += kper) {
+      const int n = min(kper, p.nsteps - i);
+      if (i >= S * kper) mbar_wait(bar_empty + 8 * s, ph ^ 1);
+      __syncwarp();
+      if (elect_one()) {
         const uint32_t full = bar_full + 8 * s;
         uint32_t dst = smem_base + s * stage_bytes + a_stage_bytes;
         mbar_expect_tx(full, (uint32_t)n * b_tile_bytes);
@@ -345,41 +484,42 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
           tma_load_2d(dst, &p.wmap, full, (i + j) * kBK, n0);
           dst += b_tile_bytes;
         }
-        if (++s == S) { s = 0; ph ^= 1; }
       }
+      if (++s == S) { s = 0; ph ^= 1; }
     }
   } else if (warp == 1) {
     // ====================================================================== MMA issuer
-    if (lane == 0) {
-      uint32_t started = 0;  // bit a: accumulator a already holds a partial sum
-      int s = 0;
-      uint32_t ph = 0;
-      const uint32_t idesc = p.idesc;
-      for (int i = 0; i < p.nsteps; i += kper) {
-        const int n = min(kper, p.nsteps - i);
-        mbar_wait(bar_full + 8 * s, ph);
-        tc_fence_after();
-        const uint32_t a_addr = smem_base + s * stage_bytes;
-        uint64_t adesc = umma_desc_k128(a_addr);
-        uint64_t bdesc = umma_desc_k128(a_addr + a_stage_bytes);
-        for (int j = 0; j < n; ++j) {
-          const int acc = (p.steps[i + j] >> 6) & 1;
-          const uint32_t d = tmem_base + (uint32_t)(acc * p.BN);
-          const uint32_t first = (started >> acc) & 1;
+    uint32_t started = 0;  // bit a: accumulator a already holds a partial sum
+    int s = 0;
+    uint32_t ph = 0;
+    const uint32_t idesc = p.idesc;
+    for (int i = 0; i < p.nsteps; i += kper) {
+      const int n = min(kper, p.nsteps - i);
+      mbar_wait(bar_full + 8 * s, ph);
+      tc_fence_after();
+      __syncwarp();
+      const uint32_t a_addr = smem_base + s * stage_bytes;
+      uint64_t adesc = umma_desc_k128(a_addr);
+      uint64_t bdesc = umma_desc_k128(a_addr + a_stage_bytes);
+      for (int j = 0; j < n; ++j) {
+        const int acc = (p.steps[i + j] >> 6) & 1;
+        const uint32_t d = tmem_base + (uint32_t)(acc * p.BN);
+        const uint32_t first = (started >> acc) & 1;
+        if (elect_one()) {
           // +32 B along K inside the swizzle atom = +2 in the (addr >> 4) field
           umma_f16(d, adesc, bdesc, idesc, first);
           umma_f16(d, adesc + 2, bdesc + 2, idesc, 1);
           umma_f16(d, adesc + 4, bdesc + 4, idesc, 1);
           umma_f16(d, adesc + 6, bdesc + 6, idesc, 1);
-          started |= 1u << acc;
-          adesc += kATileBytes >> 4;
-          bdesc += b_tile_bytes >> 4;
         }
-        umma_commit(bar_empty + 8 * s);  // frees the stage when these MMAs have read it
-        if (++s == S) { s = 0; ph ^= 1; }
+        started |= 1u << acc;
+        adesc += kATileBytes >> 4;
+        bdesc += b_tile_bytes >> 4;
       }
-      umma_commit(bar_accum);  // all MMAs done -> accumulators complete
+      if (elect_one()) umma_commit(bar_empty + 8 * s);  // frees the stage when these MMAs have read it
+      if (++s == S) { s = 0; ph ^= 1; }
     }
+    if (elect_one()) umma_commit(bar_accum);  // all MMAs done -> accumulators complete
   } else if (warp < kWarpB) {
     // ======================================================================== epilogue
     // 8 warps: warp w reads TMEM lane quarter (w & 3); the two warps of a quarter split the
@@ -397,112 +537,177 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
     mbar_wait(bar_accum, 0);
     tc_fence_after();
 
-    if constexpr (EPI == FSB_EPI_GATE_ZR) {
-      const int half = p.BN >> 1;
-      const int cpa = p.BN >> 5;  // chunks per accumulator
-      for (int ci = grp; ci < p.nacc * cpa; ci += 2) {
-        const int a = ci / cpa, c = (ci - a * cpa) << 5;
-        T* zb = reinterpret_cast<T*>(a == 0 ? p.z_l : p.z_s);
-        T* rb = reinterpret_cast<T*>(a == 0 ? p.rh_l : p.rh_s);
-        const float* bias = bias_s + a * p.BN;
-        {
-          uint32_t v[32];
-          tmem_ld32(taddr + a * p.BN + c, v);
-          tmem_ld_wait();
-          if (!valid) continue;
-          float f[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = sigmoid_f(__uint_as_float(v[j]) + bias[c + j]);
-          if (c < half) {
-            store32<T>(zb + pix * p.hidden + nt * half + c, f);
-          } else {
-            const int ch = nt * half + (c - half);
-            float h[32];
-            load32f(p.h32 + pix * p.hidden + ch, h);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) f[j] *= h[j];
-            store32<T>(rb + pix * p.hidden + ch, f);
-          }
-        }
+    conv_epilogue<T, EPI>(p, bias_s, taddr, valid, pix, b, y, x, n0, nt, grp, 2);
+    tc_fence_before();
+  }
+  __syncwarp();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.tmem_cols)
+                 : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------ kernel, halo variant
+// Same GEMM, different operand feed (FSB_CONV_LAYOUT_HALO).  A CTA owns TWO vertically stacked
+// 128-pixel tiles (32 rows x 8 columns of the image) and, per 64-channel chunk and per horizontal
+// tap dx, loads ONE activation box of (32 + 2) rows x 8 pixels x 64 channels (34 KB) instead of
+// one 16 KB box per tap and tile: a tile row of 8 pixels is exactly one 1024-byte swizzle atom,
+// so the vertical taps dy = -1, 0, +1 of tile mt are the SAME box read through UMMA descriptors
+// that start (mt*16 + 1 + dy) atoms into it -- all 1024-byte aligned, no re-load.  Activation
+// traffic per chunk drops from 2 x 9 x 16 KB to 3 x 34 KB (2.8x), and every weight tile feeds 256
+// pixels instead of 128 (weight traffic per FLOP halves).  K order of the packed weights:
+// segment -> source -> 64-channel chunk -> dx -> dy.  Activation and weight tiles travel through
+// separate rings (an activation slot lives for three weight steps).
+// Step word: bits 0-1 source, 2-3 row offset 1+dy, 4-5 dx+1, 6 accumulator, 7 first step of an
+// activation slot, 8-15 channel chunk, 16 last step of the slot.
+constexpr int kHaloRows = 34;
+constexpr int kASlotBytes = kHaloRows * 8 * 128;  // 34816
+
+__host__ __device__ inline uint32_t make_halo_step(int src, int dyrow, int dx, int acc, int chunk, int first, int last) {
+  return (uint32_t)src | ((uint32_t)dyrow << 2) | ((uint32_t)(dx + 1) << 4) | ((uint32_t)acc << 6) |
+         ((uint32_t)first << 7) | ((uint32_t)chunk << 8) | ((uint32_t)last << 16);
+}
+
+template <typename T, int EPI>
+__global__ void __launch_bounds__(kConvThreads, 1)
+conv_halo_kernel(const __grid_constant__ ConvParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  __shared__ __align__(8) uint64_t bars[4 + 4 + 8 + 8 + 1];
+  __shared__ uint32_t tmem_slot;
+  __shared__ __align__(16) float bias_s[2 * 256];
+
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);  // warp-uniform for the compiler
+  const int lane = threadIdx.x & 31;
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const int SA = p.SA, SB = p.SB;
+  const uint32_t b_bytes = (uint32_t)p.BN * (kBK * 2);
+  const uint32_t ring_b = smem_base + (uint32_t)SA * kASlotBytes;
+  const uint32_t fullA = smem_u32(&bars[0]), emptyA = smem_u32(&bars[4]);
+  const uint32_t fullB = smem_u32(&bars[8]), emptyB = smem_u32(&bars[16]);
+  const uint32_t bar_accum = smem_u32(&bars[24]);
+
+  int t = blockIdx.x;
+  const int txi = t % p.tiles_x;
+  t /= p.tiles_x;
+  const int tyi = t % p.tiles_y;
+  const int b = t / p.tiles_y;
+  const int x0 = txi * 8, y0 = tyi * 32;
+  const int nt = blockIdx.y;
+  const int n0 = nt * p.BN;
+  const int nmt = (y0 + 16 < p.H) ? 2 : 1;  // the lower tile may lie entirely below the image
+
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < SA; ++i) { mbar_init(fullA + 8 * i, 1); mbar_init(emptyA + 8 * i, 1); }
+    for (int i = 0; i < SB; ++i) { mbar_init(fullB + 8 * i, 1); mbar_init(emptyB + 8 * i, 1); }
+    mbar_init(bar_accum, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    tma_prefetch_desc(&p.amap[0]);
+  }
+  if (warp == kWarpB && lane == 0) tma_prefetch_desc(&p.wmap);
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
+                 "r"((uint32_t)p.tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (warp >= 2 && warp < kWarpB) {
+    for (int i = threadIdx.x - 64; i < p.nacc * p.BN; i += 256) {
+      const int a = i / p.BN, c = i - a * p.BN;
+      bias_s[i] = __ldg(p.bias + (size_t)a * p.rows + n0 + c);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_slot;
+  // PDL: the prologue above (and the weight producer below, which only reads parameters that no kernel
+  // writes) overlaps the tail of the previous kernel; everything that touches activations waits here.
+  pdl_launch_dependents();
+  if (warp != kWarpB) pdl_wait();
+
+  if (warp == 0) {
+    // ================================================== TMA producer: activation boxes
+    int sa = 0, nslot = 0;
+    uint32_t ph = 0;
+    for (int i = 0; i < p.nsteps; ++i) {
+      const uint32_t st = p.steps[i];
+      if (!((st >> 7) & 1)) continue;
+      if (nslot >= SA) mbar_wait(emptyA + 8 * sa, ph ^ 1);
+      __syncwarp();
+      if (elect_one()) {
+        const int src = st & 3, dx = (int)((st >> 4) & 3) - 1, chunk = (st >> 8) & 0xff;
+        mbar_expect_tx(fullA + 8 * sa, kASlotBytes);
+        tma_load_4d(smem_base + sa * kASlotBytes, &p.amap[src], fullA + 8 * sa, chunk * kBK, x0 + dx, y0 - 1, b);
       }
-    } else if constexpr (EPI == FSB_EPI_GATE_Q) {
-      // 16 columns per step: keeps the kernel under 93 registers so two CTAs share an SM
-      const float att = valid ? __ldg(p.att + pix) : 0.f;
-      for (int c = grp * 16; c < p.BN; c += 32) {
-        uint32_t v0[16], v1[16];
-        tmem_ld16(taddr + c, v0);
-        tmem_ld16(taddr + p.BN + c, v1);
-        tmem_ld_wait();
-        if (!valid) continue;
-        const int ch = n0 + c;
-        const float* hp = p.h32 + pix * p.hidden + ch;
-        const uint4* zlp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.z_l) + pix * p.hidden + ch);
-        const uint4* zsp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.z_s) + pix * p.hidden + ch);
-        float* ho = p.h32_out + pix * p.hidden + ch;
-        uint4* h16o = reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.h16_out) + pix * p.hidden + ch);
-#pragma unroll
-        for (int o = 0; o < 2; ++o) {  // 8 channels at a time
-          const float4 ha = *reinterpret_cast<const float4*>(hp + 8 * o), hb = *reinterpret_cast<const float4*>(hp + 8 * o + 4);
-          const uint4 zlu = zlp[o], zsu = zsp[o];
-          float h[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
-          const uint32_t zlw[4] = {zlu.x, zlu.y, zlu.z, zlu.w}, zsw[4] = {zsu.x, zsu.y, zsu.z, zsu.w};
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float2 zl2 = unpack2<T>(zlw[j >> 1]), zs2 = unpack2<T>(zsw[j >> 1]);
-            const float zl = (j & 1) ? zl2.y : zl2.x, zs = (j & 1) ? zs2.y : zs2.x;
-            const float ql = tanh_f(__uint_as_float(v0[8 * o + j]) + bias_s[c + 8 * o + j]);
-            const float qs = tanh_f(__uint_as_float(v1[8 * o + j]) + bias_s[p.BN + c + 8 * o + j]);
-            const float hl = (1.f - zl) * h[j] + zl * ql;
-            const float hs = (1.f - zs) * h[j] + zs * qs;
-            h[j] = hs * att + hl * (1.f - att);
-          }
-          *reinterpret_cast<float4*>(ho + 8 * o) = make_float4(h[0], h[1], h[2], h[3]);
-          *reinterpret_cast<float4*>(ho + 8 * o + 4) = make_float4(h[4], h[5], h[6], h[7]);
-          uint4 u;
-          u.x = pack2<T>(h[0], h[1]); u.y = pack2<T>(h[2], h[3]); u.z = pack2<T>(h[4], h[5]); u.w = pack2<T>(h[6], h[7]);
-          h16o[o] = u;
-        }
+      ++nslot;
+      if (++sa == SA) { sa = 0; ph ^= 1; }
+    }
+  } else if (warp == kWarpB) {
+    // ====================================================== TMA producer: weight tiles
+    int sb = 0;
+    uint32_t ph = 0;
+    for (int i = 0; i < p.nsteps; ++i) {
+      if (i >= SB) mbar_wait(emptyB + 8 * sb, ph ^ 1);
+      __syncwarp();
+      if (elect_one()) {
+        mbar_expect_tx(fullB + 8 * sb, b_bytes);
+        tma_load_2d(ring_b + sb * b_bytes, &p.wmap, fullB + 8 * sb, i * kBK, n0);
       }
-    } else {
-      T* out = reinterpret_cast<T*>(p.out);
-      for (int c = grp * 32; c < p.BN; c += 64) {
-        uint32_t v[32];
-        tmem_ld32(taddr + c, v);
-        tmem_ld_wait();
-        const int n = n0 + c;
-        if (!valid || n >= p.Cout) continue;
-        const bool full = (n + 32 <= p.Cout);
-        float f[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float a = __uint_as_float(v[j]) + bias_s[c + j];  // rows beyond Cout carry zero bias
-          if constexpr (EPI == FSB_EPI_RELU) a = fmaxf(a, 0.f);
-          if constexpr (EPI == FSB_EPI_GELU) a = gelu_f(a);
-          f[j] = a;
+      if (++sb == SB) { sb = 0; ph ^= 1; }
+    }
+  } else if (warp == 1) {
+    // ====================================================================== MMA issuer
+    uint32_t started = 0;  // bit (mt*2 + acc)
+    int sa = 0, sb = 0;
+    uint32_t pha = 0, phb = 0, a_base = smem_base;
+    const uint32_t idesc = p.idesc;
+    const uint32_t mt_cols = (uint32_t)(p.nacc * p.BN);
+    for (int i = 0; i < p.nsteps; ++i) {
+      const uint32_t st = p.steps[i];
+      if ((st >> 7) & 1) {
+        mbar_wait(fullA + 8 * sa, pha);
+        a_base = smem_base + sa * kASlotBytes;
+      }
+      mbar_wait(fullB + 8 * sb, phb);
+      tc_fence_after();
+      __syncwarp();
+      const int acc = (st >> 6) & 1, dyrow = (st >> 2) & 3;
+      const uint64_t bdesc = umma_desc_k128(ring_b + sb * b_bytes);
+      for (int mt = 0; mt < nmt; ++mt) {
+        const uint64_t adesc = umma_desc_k128(a_base + (uint32_t)(mt * 16 + dyrow) * 1024u);
+        const uint32_t d = tmem_base + mt * mt_cols + (uint32_t)(acc * p.BN);
+        const uint32_t bit = 1u << (mt * 2 + acc);
+        const uint32_t first = (started & bit) ? 1u : 0u;
+        if (elect_one()) {
+          umma_f16(d, adesc, bdesc, idesc, first);
+          umma_f16(d, adesc + 2, bdesc + 2, idesc, 1);
+          umma_f16(d, adesc + 4, bdesc + 4, idesc, 1);
+          umma_f16(d, adesc + 6, bdesc + 6, idesc, 1);
         }
-        if constexpr (EPI == FSB_EPI_SCALE_RES) {
-          float rres[32];
-          load32<T>(reinterpret_cast<const T*>(p.res) + pix * p.ld_res + n, rres);  // Cout % 32 == 0 (host check)
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = rres[j] + __ldg(p.gamma + n + j) * f[j];
-        }
-        if (out != nullptr) {
-          T* o = out + pix * p.ld_out + p.ch_off + n;
-          if (full) {
-            store32<T>(o, f);
-          } else {
-            for (int j = 0; j < 32 && n + j < p.Cout; ++j) o[j] = from_f32<T>(f[j]);
-          }
-        }
-        if (p.out_f32 != nullptr) {
-          const size_t hw = (size_t)p.H * p.W;
-          float* o = p.out_f32 + ((size_t)b * p.Cout + n) * hw + (size_t)y * p.W + x;
-#pragma unroll 4
-          for (int j = 0; j < 32; ++j)
-            if (full || n + j < p.Cout) o[(size_t)j * hw] = f[j] * p.out_scale;
-        }
+        started |= bit;
+      }
+      if (elect_one()) umma_commit(emptyB + 8 * sb);
+      if (++sb == SB) { sb = 0; phb ^= 1; }
+      if ((st >> 16) & 1) {
+        if (elect_one()) umma_commit(emptyA + 8 * sa);
+        if (++sa == SA) { sa = 0; pha ^= 1; }
       }
     }
+    if (elect_one()) umma_commit(bar_accum);
+  } else if (warp < kWarpB) {
+    // ======================================================================== epilogue
+    // warps 2-5: upper tile, warps 6-9: lower tile; warp w reads TMEM lane quarter (w & 3)
+    const int q = warp & 3, mt = (warp - 2) >> 2;
+    const int r = q * 32 + lane;
+    const int y = y0 + mt * 16 + (r >> 3), x = x0 + (r & 7);
+    const bool valid = (y < p.H) && (x < p.W);
+    const size_t pix = valid ? ((size_t)b * p.H + y) * p.W + x : 0;
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(mt * p.nacc * p.BN);
+    mbar_wait(bar_accum, 0);
+    tc_fence_after();
+    if (mt < nmt) conv_epilogue<T, EPI>(p, bias_s, taddr, valid, pix, b, y, x, n0, nt, 0, 1);
     tc_fence_before();
   }
   __syncwarp();
@@ -560,6 +765,19 @@ static auto kernel_for(int epi) -> void (*)(const ConvParams) {
   }
 }
 
+template <typename T>
+static auto halo_kernel_for(int epi) -> void (*)(const ConvParams) {
+  switch (epi) {
+    case FSB_EPI_BIAS: return conv_halo_kernel<T, FSB_EPI_BIAS>;
+    case FSB_EPI_RELU: return conv_halo_kernel<T, FSB_EPI_RELU>;
+    case FSB_EPI_GATE_ZR: return conv_halo_kernel<T, FSB_EPI_GATE_ZR>;
+    case FSB_EPI_GATE_Q: return conv_halo_kernel<T, FSB_EPI_GATE_Q>;
+    case FSB_EPI_GELU: return conv_halo_kernel<T, FSB_EPI_GELU>;
+    case FSB_EPI_SCALE_RES: return conv_halo_kernel<T, FSB_EPI_SCALE_RES>;
+    default: return nullptr;
+  }
+}
+
 }  // namespace fsb
 
 extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t stream) {
@@ -608,6 +826,11 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
                   "fsb_conv2d_nhwc: SCALE_RES needs res, gamma, Cout %% 32 == 0");
   }
 
+  const bool halo = a->layout == FSB_CONV_LAYOUT_HALO;
+  FSB_REQUIRE(halo || a->layout == FSB_CONV_LAYOUT_TAP, FSB_ERR_ARG, "fsb_conv2d_nhwc: unknown weight layout %d", a->layout);
+  FSB_REQUIRE(!halo || 2 * a->nseg * BN <= 512, FSB_ERR_SHAPE,
+              "fsb_conv2d_nhwc: halo layout keeps 2 pixel tiles x %d accumulators of %d columns in TMEM (> 512)", a->nseg, BN);
+
   EncodeTiledFn enc = encode_fn();
   FSB_REQUIRE(enc != nullptr, FSB_ERR_CUDA, "fsb_conv2d_nhwc: cuTensorMapEncodeTiled not available from the driver");
 
@@ -615,7 +838,8 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   memset(&p, 0, sizeof(p));
   int tw_log2 = 4;
   pick_tile(a->H, a->W, &tw_log2);
-  const int TW = 1 << tw_log2, TH = kBM >> tw_log2;
+  if (halo) tw_log2 = 3;                                  // 8-pixel tile rows = one swizzle atom
+  const int TW = 1 << tw_log2, TH = halo ? 32 : (kBM >> tw_log2);  // halo: two stacked 16 x 8 tiles per CTA
   p.H = a->H;
   p.W = a->W;
   p.tiles_x = ceil_div(a->W, TW);
@@ -624,7 +848,7 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   p.BN = BN;
   p.nacc = a->nseg;
   int cols = 32;
-  while (cols < a->nseg * BN) cols <<= 1;
+  while (cols < (halo ? 2 : 1) * a->nseg * BN) cols <<= 1;
   p.tmem_cols = cols;
 
   // K-step program + Ktot
@@ -634,6 +858,20 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
     FSB_REQUIRE(sg.ksize == 1 || sg.ksize == 3, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: segment %d ksize=%d", s, sg.ksize);
     FSB_REQUIRE(sg.nsrc >= 1 && sg.nsrc <= FSB_MAX_SRC, FSB_ERR_ARG, "fsb_conv2d_nhwc: segment %d nsrc=%d", s, sg.nsrc);
     const int rad = sg.ksize / 2;
+    if (halo) {
+      // K order: source -> 64-channel chunk -> dx -> dy (one activation box per (source, chunk, dx))
+      for (int k = 0; k < sg.nsrc; ++k) {
+        const int si = sg.src[k];
+        FSB_REQUIRE(si >= 0 && si < a->nsrc, FSB_ERR_ARG, "fsb_conv2d_nhwc: segment %d source index %d", s, si);
+        for (int c = 0; c < a->src[si].C / kBK; ++c)
+          for (int dx = -rad; dx <= rad; ++dx)
+            for (int dy = -rad; dy <= rad; ++dy) {
+              FSB_REQUIRE(n < kMaxSteps, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: more than %d K steps", kMaxSteps);
+              p.steps[n++] = make_halo_step(si, dy + 1, dx, s, c, dy == -rad, dy == rad);
+            }
+      }
+      continue;
+    }
     for (int dy = -rad; dy <= rad; ++dy)
       for (int dx = -rad; dx <= rad; ++dx)
         for (int k = 0; k < sg.nsrc; ++k) {
@@ -670,14 +908,25 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   if (stages < 1) stages = 1;
   p.stages = stages;
   p.kper = kper;
-  const size_t smem = (size_t)stages * kper * step_bytes + 1024;
+  size_t smem = (size_t)stages * kper * step_bytes + 1024;
+  if (halo) {
+    // activation ring: 3 boxes of 34 KB; weight ring: what is left of 220 KB (2..8 tiles)
+    const size_t b_bytes = (size_t)BN * kBK * 2;
+    p.SA = 3;
+    int sb = (int)((220 * 1024 - 1024 - (size_t)p.SA * kASlotBytes) / b_bytes);
+    if (sb > 8) sb = 8;
+    if (sb > n) sb = n;
+    FSB_REQUIRE(sb >= 2 || n < 2, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: block_n=%d leaves no room for a weight ring", BN);
+    p.SB = sb < 1 ? 1 : sb;
+    smem = (size_t)p.SA * kASlotBytes + (size_t)p.SB * b_bytes + 1024;
+  }
 
   const CUtensorMapDataType dt = dtype == FSB_F16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   for (int i = 0; i < a->nsrc; ++i) {
     const cuuint64_t C = (cuuint64_t)a->src[i].C;
     cuuint64_t dims[4] = {C, (cuuint64_t)a->W, (cuuint64_t)a->H, (cuuint64_t)a->B};
     cuuint64_t strides[3] = {C * 2, C * 2 * a->W, C * 2 * a->W * a->H};
-    cuuint32_t box[4] = {(cuuint32_t)kBK, (cuuint32_t)TW, (cuuint32_t)TH, 1};
+    cuuint32_t box[4] = {(cuuint32_t)kBK, (cuuint32_t)TW, (cuuint32_t)(halo ? kHaloRows : TH), 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = enc(&p.amap[i], dt, 4, const_cast<void*>(a->src[i].ptr), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -717,13 +966,14 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   p.h16_out = a->h16_out;
   p.hidden = a->hidden;
 
-  auto kern = dtype == FSB_F16 ? kernel_for<__half>(epi) : kernel_for<__nv_bfloat16>(epi);
+  auto kern = halo ? (dtype == FSB_F16 ? halo_kernel_for<__half>(epi) : halo_kernel_for<__nv_bfloat16>(epi))
+                   : (dtype == FSB_F16 ? kernel_for<__half>(epi) : kernel_for<__nv_bfloat16>(epi));
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return cuda_fail(e, "fsb_conv2d_nhwc: cudaFuncSetAttribute");
   const long long mtiles = (long long)p.tiles_x * p.tiles_y * a->B;
   FSB_REQUIRE(mtiles < (1ll << 31) && a->rows / BN < 65536, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: grid too large");
   dim3 grid((unsigned)mtiles, (unsigned)(a->rows / BN));
-  kern<<<grid, kConvThreads, smem, (cudaStream_t)stream>>>(p);
+  launch_kernel(kern, dim3(grid), dim3(kConvThreads), smem, (cudaStream_t)stream, p);
   FSB_CHECK_LAUNCH("fsb_conv2d_nhwc");
   return FSB_OK;
 }

@@ -128,6 +128,8 @@ template <int NPROD>
 __global__ void __launch_bounds__(kCuThreads)
 corr_umma_kernel(const float* __restrict__ f1, const float* __restrict__ f2, LevelPtrs lv, int C, int H, int W1,
                  int W2, int L, int nbuf) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ __align__(1024) uint8_t cu_smem[];
   __shared__ __align__(8) uint64_t bars[3];
   __shared__ uint32_t tmem_slot;
@@ -311,7 +313,7 @@ int launch_corr_umma(const float* f1, const float* f2, const LevelPtrs& lv, int 
   auto kern = nprod == 3 ? corr_umma_kernel<3> : corr_umma_kernel<1>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return cuda_fail(e, "fsb_corr_pyramid: cudaFuncSetAttribute");
-  kern<<<grid, kCuThreads, smem, stream>>>(f1, f2, lv, C, H, W1, W2, L, nbuf);
+  launch_kernel(kern, dim3(grid), dim3(kCuThreads), smem, stream, f1, f2, lv, C, H, W1, W2, L, nbuf);
   FSB_CHECK_LAUNCH("fsb_corr_pyramid");
   return FSB_OK;
 }

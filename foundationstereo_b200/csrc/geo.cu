@@ -31,6 +31,8 @@ __device__ __forceinline__ void store_run4(float* row, int col, int len, const f
 __global__ void __launch_bounds__(256)
 corr_fp32_kernel(const float* __restrict__ f1, const float* __restrict__ f2, LevelPtrs lv, int C, int H,
                  int W1, int W2, int L) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   __shared__ __align__(16) float As[kCorrKC][64];
   __shared__ __align__(16) float Bs[kCorrKC][128];
   __shared__ float invA[64], invB[128];
@@ -146,6 +148,8 @@ __device__ __forceinline__ void write_level(const float* t, float* out, int Cg, 
 
 __global__ void __launch_bounds__(256)
 geo_pyramid_kernel(const float* __restrict__ vol, LevelPtrs lv, int Cg, int D, int H, int W, int L) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ float t[];  // [kGeoTD*Cg][kGeoTW+1], row index = dd*Cg + c
   const int tid = threadIdx.x;
   const int w0 = blockIdx.x * kGeoTW, d0 = blockIdx.y * kGeoTD;
@@ -179,6 +183,8 @@ geo_pyramid_kernel(const float* __restrict__ vol, LevelPtrs lv, int Cg, int D, i
 template <int CG>
 __global__ void __launch_bounds__(256)
 geo_pyramid_fast_kernel(const float* __restrict__ vol, LevelPtrs lv, int D, int H, int W, int L) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   constexpr int R0 = kGeoTD * CG;  // rows of the tile = floats of a level-0 run
   static_assert(R0 <= 256, "one thread per run element");
   __shared__ float t[R0][kGeoTW + 1];
@@ -279,6 +285,8 @@ __device__ __forceinline__ float ref_unnormalised(float x, int n) {
 __global__ void __launch_bounds__(kLkThreads)
 lookup_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp, const float* __restrict__ coords,
               float* __restrict__ out, int Cg, int D, int H, int W, int W2, int L, int r) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ float sm[];
   const int K = 2 * r + 1;
   const int run = (K + 1) * Cg;      // floats per pixel window
@@ -397,6 +405,8 @@ template <typename T, int KT>
 __global__ void __launch_bounds__(kLkWarps * 32)
 lookup_nhwc_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp, const float* __restrict__ coords,
                    T* __restrict__ out, int Cg, int D, int W2, int L, int r, int Cpad, int wstride, long long npix) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ __align__(16) float lsm[];
   const int K = KT > 0 ? KT : 2 * r + 1;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -508,7 +518,7 @@ extern "C" int fsb_corr_pyramid(const float* f1, const float* f2, float* const* 
   if (precision != FSB_PREC_FP32)
     return launch_corr_umma(f1, f2, lv, B, C, H, W1, W2, L, precision == FSB_PREC_TF32X3 ? 3 : 1, (cudaStream_t)stream);
   dim3 grid(ceil_div(W2, 128), ceil_div(W1, 64), B * H);
-  corr_fp32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(f1, f2, lv, C, H, W1, W2, L);
+  launch_kernel(corr_fp32_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, f1, f2, lv, C, H, W1, W2, L);
   FSB_CHECK_LAUNCH("fsb_corr_pyramid");
   return FSB_OK;
 }
@@ -534,9 +544,9 @@ extern "C" int fsb_geo_pyramid(const float* vol, float* const* geo_levels, int B
   }
   dim3 grid(ceil_div(W, kGeoTW), ceil_div(D, kGeoTD), B * H);
   if (Cg == 28)
-    geo_pyramid_fast_kernel<28><<<grid, 256, 0, (cudaStream_t)stream>>>(vol, lv, D, H, W, L);
+    launch_kernel(geo_pyramid_fast_kernel<28>, dim3(grid), dim3(256), 0, (cudaStream_t)stream, vol, lv, D, H, W, L);
   else
-    geo_pyramid_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(vol, lv, Cg, D, H, W, L);
+    launch_kernel(geo_pyramid_kernel, dim3(grid), dim3(256), smem, (cudaStream_t)stream, vol, lv, Cg, D, H, W, L);
   FSB_CHECK_LAUNCH("fsb_geo_pyramid");
   return FSB_OK;
 }
@@ -579,7 +589,7 @@ extern "C" int fsb_geo_lookup(float* const* geo_levels, float* const* corr_level
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);          \
       if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_lookup: cudaFuncSetAttribute");                           \
     }                                                                                                              \
-    kern<<<blocks, kLkWarps * 32, smem, (cudaStream_t)stream>>>(g, c, disp, coords, (T*)out, Cg, D, W2, L, r, Cpad, \
+    launch_kernel(kern, dim3(blocks), dim3(kLkWarps * 32), smem, (cudaStream_t)stream, g, c, disp, coords, (T*)out, Cg, D, W2, L, r, Cpad, \
                                                                  wstride, npix);                                   \
   } while (0)
     if (out_layout == 1) {
@@ -599,7 +609,7 @@ extern "C" int fsb_geo_lookup(float* const* geo_levels, float* const* corr_level
     if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_lookup: cudaFuncSetAttribute");
   }
   dim3 grid(ceil_div(W, kLkPix), B * H);
-  lookup_kernel<<<grid, kLkThreads, smem, (cudaStream_t)stream>>>(g, c, disp, coords, (float*)out, Cg, D, H, W,
+  launch_kernel(lookup_kernel, dim3(grid), dim3(kLkThreads), smem, (cudaStream_t)stream, g, c, disp, coords, (float*)out, Cg, D, H, W,
                                                                   W2, L, r);
   FSB_CHECK_LAUNCH("fsb_geo_lookup");
   return FSB_OK;

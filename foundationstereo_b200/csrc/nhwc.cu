@@ -14,6 +14,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 nchw_to_nhwc_kernel(const float* __restrict__ src, T* __restrict__ dst16, float* __restrict__ dst32, int C,
                     int HW, int Cpad) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   __shared__ float t[32][33];
   const int b = blockIdx.z;
   const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
@@ -37,6 +39,8 @@ nchw_to_nhwc_kernel(const float* __restrict__ src, T* __restrict__ dst16, float*
 
 __global__ void __launch_bounds__(256)
 nhwc_to_nchw_kernel(const float* __restrict__ src, float* __restrict__ dst, int C, int HW) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   __shared__ float t[32][33];
   const int b = blockIdx.z;
   const int p0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
@@ -60,6 +64,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 pool2x_kernel(const float* __restrict__ src, T* __restrict__ dst, int C4, int H, int W, int Ho, int Wo,
               size_t total) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
   const int c4 = (int)(i % C4);
@@ -90,6 +96,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 resize_kernel(const float* __restrict__ src, T* __restrict__ dst, int C4, int Hs, int Ws, int Hd, int Wd,
               float sy, float sx, size_t total) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
   const int c4 = (int)(i % C4);
@@ -121,6 +129,8 @@ __global__ void __launch_bounds__(256)
 conv7x7_c1_kernel(const float* __restrict__ disp, const float* __restrict__ weight, const float* __restrict__ bias,
                   T* __restrict__ out, int ld_out, int Cout, T* __restrict__ disp_out, int ld_disp, int disp_ch,
                   int H, int W) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   __shared__ float wsm[49][kC1MaxCout];
   __shared__ float patch[7][32 + 6];
   const int tid = threadIdx.x;
@@ -190,6 +200,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 dwconv7x7_kernel(const T* __restrict__ x, const float* __restrict__ weight, const float* __restrict__ bias,
                  T* __restrict__ out, int C, int H, int W) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ __align__(16) uint8_t dsm_raw[];
   float* wsm = reinterpret_cast<float*>(dsm_raw);                      // [49][kDwC]
   T* patch = reinterpret_cast<T*>(dsm_raw + 49 * kDwC * sizeof(float));  // [kDwPY][kDwPX][kDwC]
@@ -246,6 +258,8 @@ dwconv7x7_kernel(const T* __restrict__ x, const float* __restrict__ weight, cons
 }
 
 __global__ void __launch_bounds__(256) axpy_kernel(float* __restrict__ y, const float* __restrict__ x, size_t n) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) y[i] += x[i];
 }
@@ -271,7 +285,7 @@ extern "C" int fsb_nchw_to_nhwc(const float* src, void* dst16, float* dst32, int
   const int HW = H * W;
   FSB_REQUIRE(B < 65536 && ceil_div(Cpad, 32) < 65536, FSB_ERR_SHAPE, "fsb_nchw_to_nhwc: grid too large");
   dim3 grid(ceil_div(HW, 32), ceil_div(Cpad, 32), B);
-  FSB_DISPATCH16(dtype, (nchw_to_nhwc_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>(src, (T*)dst16, dst32, C, HW, Cpad)));
+  FSB_DISPATCH16(dtype, (launch_kernel(nchw_to_nhwc_kernel<T>, dim3(grid), dim3(256), 0, (cudaStream_t)stream, src, (T*)dst16, dst32, C, HW, Cpad)));
   FSB_CHECK_LAUNCH("fsb_nchw_to_nhwc");
   return FSB_OK;
 }
@@ -282,7 +296,7 @@ extern "C" int fsb_nhwc_to_nchw(const float* src, float* dst, int B, int C, int 
   FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, FSB_ERR_ARG, "fsb_nhwc_to_nchw: non-positive size");
   FSB_REQUIRE(B < 65536 && ceil_div(C, 32) < 65536, FSB_ERR_SHAPE, "fsb_nhwc_to_nchw: grid too large");
   dim3 grid(ceil_div(H * W, 32), ceil_div(C, 32), B);
-  nhwc_to_nchw_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst, C, H * W);
+  launch_kernel(nhwc_to_nchw_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, src, dst, C, H * W);
   FSB_CHECK_LAUNCH("fsb_nhwc_to_nchw");
   return FSB_OK;
 }
@@ -296,7 +310,7 @@ extern "C" int fsb_pool2x_nhwc(const float* src, void* dst, int B, int C, int H,
   const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
   const size_t total = (size_t)B * Ho * Wo * (C / 4);
   const unsigned blocks = (unsigned)((total + 255) / 256);
-  FSB_DISPATCH16(dtype, (pool2x_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(src, (T*)dst, C / 4, H, W, Ho, Wo, total)));
+  FSB_DISPATCH16(dtype, (launch_kernel(pool2x_kernel<T>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, src, (T*)dst, C / 4, H, W, Ho, Wo, total)));
   FSB_CHECK_LAUNCH("fsb_pool2x_nhwc");
   return FSB_OK;
 }
@@ -312,7 +326,7 @@ extern "C" int fsb_resize_nhwc(const float* src, void* dst, int B, int C, int Hs
   const float sx = Wd > 1 ? (float)(Ws - 1) / (float)(Wd - 1) : 0.f;
   const size_t total = (size_t)B * Hd * Wd * (C / 4);
   const unsigned blocks = (unsigned)((total + 255) / 256);
-  FSB_DISPATCH16(dtype, (resize_kernel<T><<<blocks, 256, 0, (cudaStream_t)stream>>>(src, (T*)dst, C / 4, Hs, Ws, Hd, Wd, sy, sx, total)));
+  FSB_DISPATCH16(dtype, (launch_kernel(resize_kernel<T>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, src, (T*)dst, C / 4, Hs, Ws, Hd, Wd, sy, sx, total)));
   FSB_CHECK_LAUNCH("fsb_resize_nhwc");
   return FSB_OK;
 }
@@ -328,7 +342,7 @@ extern "C" int fsb_conv7x7_c1(const float* disp, const float* weight, const floa
   FSB_REQUIRE(!disp_out || (disp_ch >= 0 && disp_ch < ld_disp), FSB_ERR_ARG, "fsb_conv7x7_c1: disp_ch=%d ld_disp=%d", disp_ch, ld_disp);
   FSB_REQUIRE(H < 65536 && B < 65536, FSB_ERR_SHAPE, "fsb_conv7x7_c1: grid too large");
   dim3 grid(ceil_div(W, 32), H, B);
-  FSB_DISPATCH16(dtype, (conv7x7_c1_kernel<T><<<grid, 256, 0, (cudaStream_t)stream>>>(disp, weight, bias, (T*)out, ld_out, Cout,
+  FSB_DISPATCH16(dtype, (launch_kernel(conv7x7_c1_kernel<T>, dim3(grid), dim3(256), 0, (cudaStream_t)stream, disp, weight, bias, (T*)out, ld_out, Cout,
                                                                                        (T*)disp_out, ld_disp, disp_ch, H, W)));
   FSB_CHECK_LAUNCH("fsb_conv7x7_c1");
   return FSB_OK;
@@ -346,11 +360,11 @@ extern "C" int fsb_dwconv7x7_nhwc(const void* x, const float* weight, const floa
   if (dtype == FSB_F16) {
     cudaError_t e = cudaFuncSetAttribute(dwconv7x7_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return cuda_fail(e, "fsb_dwconv7x7_nhwc: cudaFuncSetAttribute");
-    dwconv7x7_kernel<__half><<<grid, 256, smem, (cudaStream_t)stream>>>((const __half*)x, weight, bias, (__half*)out, C, H, W);
+    launch_kernel(dwconv7x7_kernel<__half>, dim3(grid), dim3(256), smem, (cudaStream_t)stream, (const __half*)x, weight, bias, (__half*)out, C, H, W);
   } else {
     cudaError_t e = cudaFuncSetAttribute(dwconv7x7_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return cuda_fail(e, "fsb_dwconv7x7_nhwc: cudaFuncSetAttribute");
-    dwconv7x7_kernel<__nv_bfloat16><<<grid, 256, smem, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, weight, bias,
+    launch_kernel(dwconv7x7_kernel<__nv_bfloat16>, dim3(grid), dim3(256), smem, (cudaStream_t)stream, (const __nv_bfloat16*)x, weight, bias,
                                                                                (__nv_bfloat16*)out, C, H, W);
   }
   FSB_CHECK_LAUNCH("fsb_dwconv7x7_nhwc");
@@ -361,7 +375,7 @@ extern "C" int fsb_axpy_f32(float* y, const float* x, size_t n, fsb_stream_t str
   using namespace fsb;
   FSB_REQUIRE(y && x, FSB_ERR_ARG, "fsb_axpy_f32: NULL pointer");
   if (n == 0) return FSB_OK;
-  axpy_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(y, x, n);
+  launch_kernel(axpy_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, (cudaStream_t)stream, y, x, n);
   FSB_CHECK_LAUNCH("fsb_axpy_f32");
   return FSB_OK;
 }

@@ -27,6 +27,8 @@ __global__ void __launch_bounds__(kVolThreads)
 volume_kernel(const T* __restrict__ fl, const T* __restrict__ fr, const T* __restrict__ pl,
               const T* __restrict__ pr, T* __restrict__ gwc, T* __restrict__ cat, int C, int Cp, int G,
               int H, int W, int D, size_t gwc_bs, size_t cat_bs) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ __align__(16) float smem[];
   const int tid = threadIdx.x;
   const int b = blockIdx.x / H;
@@ -165,7 +167,7 @@ static int launch_volume(const void* fl, const void* fr, const void* pl, const v
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return cuda_fail(e, "fsb_volume_gwc_concat: cudaFuncSetAttribute");
   }
-  kern<<<grid, kVolThreads, smem, stream>>>((const T*)fl, (const T*)fr, (const T*)pl, (const T*)pr,
+  launch_kernel(kern, dim3(grid), dim3(kVolThreads), smem, stream, (const T*)fl, (const T*)fr, (const T*)pl, (const T*)pr,
                                             (T*)gwc, (T*)cat, C, Cp, G, H, W, D, gwc_bs, cat_bs);
   FSB_CHECK_LAUNCH("fsb_volume_gwc_concat");
   return FSB_OK;

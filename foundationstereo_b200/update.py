@@ -34,6 +34,12 @@ DEFAULT_BLOCK_N = {
 }
 
 
+# layers fed through the halo variant of the kernel (FSB_CONV_LAYOUT_HALO: two stacked pixel tiles per
+# CTA, one activation box per horizontal tap); the rest use FSB_CONV_LAYOUT_TAP.  The coarse GRU levels
+# stay on the tap layout: their few pixel tiles need the narrow-N / many-CTA shape.
+DEFAULT_HALO: set = set()
+
+
 def _down(n: int) -> int:
     return (n + 1) // 2
 
@@ -83,7 +89,7 @@ class SelectiveUpdateBlock:
 
     def __init__(self, state_dict: Dict[str, Tensor], device: torch.device | str = "cuda",
                  dtype: torch.dtype = torch.float16, use_graph: bool = True,
-                 block_n: Optional[Dict[str, int]] = None):
+                 block_n: Optional[Dict[str, int]] = None, halo: Optional[Sequence[str]] = None):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("SelectiveUpdateBlock runs on CUDA only (no CPU path)")
@@ -94,6 +100,9 @@ class SelectiveUpdateBlock:
         self.bn = dict(DEFAULT_BLOCK_N)
         if block_n:
             self.bn.update(block_n)
+        self.halo = set(DEFAULT_HALO if halo is None else halo)
+        self.replayed_kernels = 0  # libfsb200 kernels launched through CUDA-graph replays (not seen by fsb_launch_count)
+        self.fixed_tiles = block_n is not None or halo is not None  # explicit tuning tables switch the heuristics off
         sd = {k: v.detach().to(self.device, torch.float32) for k, v in state_dict.items()}
         assert "gru16.conv0.0.weight" in sd and "gru08.conv0.0.weight" in sd, \
             "only the n_gru_layers == 3 configuration of the reference is supported"
@@ -101,77 +110,100 @@ class SelectiveUpdateBlock:
         assert self.hidden == 128, "hidden_dim 128 (core/foundation_stereo.py:137)"
         self.planes = sd["encoder.convc1.weight"].shape[1]
         self.planes_pad = pad64(self.planes)
-        self.w: Dict[str, Tuple[Tensor, Tensor, int]] = {}  # name -> (packed weight, bias fp32, Cout)
+        self.spec: Dict[str, tuple] = {}                    # weight key -> (launch name, segments, biases, Cout, block_n)
+        self.w: Dict[tuple, Tuple[Tensor, Tensor, int]] = {}  # (key, layout, block_n) -> (packed weight, bias fp32, Cout)
+        self._sd = sd
         self.f: Dict[str, Tensor] = {}                      # fp32 side parameters
         self._pack(sd)
         self._plans: Dict[Tuple[int, int, int], _Plan] = {}
 
     # ---- weight packing -----------------------------------------------------------------
-    def _put(self, name: str, mats: Sequence[Tensor], biases: Sequence[Tensor], cout: int, bn: int) -> None:
-        rows = (max(m.shape[0] for m in mats) + bn - 1) // bn * bn
-        w = pack_rows(mats, rows).to(self.dtype).contiguous()
-        b = torch.zeros(len(biases), rows, dtype=torch.float32, device=self.device)
-        for i, bi in enumerate(biases):
-            b[i, :bi.numel()] = bi
-        self.w[name] = (w, b.contiguous(), cout)
+    def _lay(self, launch: str) -> int:
+        return _lib.FSB_CONV_LAYOUT_HALO if launch in self.halo else _lib.FSB_CONV_LAYOUT_TAP
 
     def _bn(self, key: str, g: Optional[str] = None) -> int:
         return self.bn.get(f"{g}.{key}", self.bn[key]) if g else self.bn[key]
+
+    def _put(self, name: str, launch: str, segs, biases, cout: int, bn: int) -> None:
+        """Register the weights of launch `launch` under key `name`: `segs` = one (weight, source
+        channels) pair per segment, or a callable block_n -> (segs, biases) when the row order depends
+        on the N tile (the interleaved z|r gates).  Packing (K order of the layout, row padding to the
+        N tile) happens on first use per (layout, block_n) -- a plan may pick a different tile shape
+        for a large batch than for a single pair."""
+        self.spec[name] = (launch, segs, biases, cout, bn)
+
+    def _weights(self, name: str, lay: int, bn: int) -> Tuple[Tensor, Tensor, int]:
+        key = (name, lay, bn)
+        hit = self.w.get(key)
+        if hit is None:
+            _, segs, biases, cout, _ = self.spec[name]
+            if callable(segs):
+                segs, biases = segs(bn)
+            mats = [pack_segment(w, src, lay) for w, src in segs]
+            rows = (max(m.shape[0] for m in mats) + bn - 1) // bn * bn
+            w = pack_rows(mats, rows).to(self.dtype).contiguous()
+            b = torch.zeros(len(biases), rows, dtype=torch.float32, device=self.device)
+            for i, bi in enumerate(biases):
+                b[i, :bi.numel()] = bi
+            hit = self.w[key] = (w, b.contiguous(), cout)
+        return hit
 
     def _pack(self, sd: Dict[str, Tensor]) -> None:
         hd = self.hidden
         bn = self.bn
         for g, cin in (("gru16", 2 * hd), ("gru08", 3 * hd), ("gru04", 3 * hd)):
             nx = cin // hd
-            self._put(f"{g}.conv0", [pack_segment(sd[f"{g}.conv0.0.weight"], [(hd, hd)] * nx)],
+            self._put(f"{g}.conv0", f"{g}.conv0", [(sd[f"{g}.conv0.0.weight"], [(hd, hd)] * nx)],
                       [sd[f"{g}.conv0.0.bias"]], cin, self._bn("conv0", g))
-            self._put(f"{g}.conv1", [pack_segment(sd[f"{g}.conv1.0.weight"], [(cin, cin), (hd, hd)])],
+            self._put(f"{g}.conv1", f"{g}.conv1", [(sd[f"{g}.conv1.0.weight"], [(cin, cin), (hd, hd)])],
                       [sd[f"{g}.conv1.0.bias"]], cin + hd, self._bn("conv1", g))
-            hx = [(cin + hd, cin + hd)]
-            zr_w, zr_b = [], []
-            for gru in ("large_gru", "small_gru"):
-                z = pack_segment(sd[f"{g}.{gru}.convz.weight"], hx)
-                r = pack_segment(sd[f"{g}.{gru}.convr.weight"], hx)
-                zr_w.append(interleave_zr(z, r, self._bn("zr", g)))
-                zr_b.append(interleave_zr(sd[f"{g}.{gru}.convz.bias"][:, None], sd[f"{g}.{gru}.convr.bias"][:, None],
-                                          self._bn("zr", g)).flatten())
-            self._put(f"{g}.zr", zr_w, zr_b, 2 * hd, self._bn("zr", g))
+            # z and r gates of one GRU share a launch: rows interleaved per N tile [z | r]
+            def zr(bnz, g=g, cin=cin):
+                hx = [(cin + hd, cin + hd)]
+                segs, zr_b = [], []
+                for gru in ("large_gru", "small_gru"):
+                    segs.append((interleave_zr(sd[f"{g}.{gru}.convz.weight"], sd[f"{g}.{gru}.convr.weight"], bnz), hx))
+                    zr_b.append(interleave_zr(sd[f"{g}.{gru}.convz.bias"][:, None],
+                                              sd[f"{g}.{gru}.convr.bias"][:, None], bnz).flatten())
+                return segs, zr_b
+            self._put(f"{g}.zr", f"{g}.zr", zr, None, 2 * hd, self._bn("zr", g))
             rhx = [(hd, hd), (cin, cin)]
-            self._put(f"{g}.q", [pack_segment(sd[f"{g}.large_gru.convq.weight"], rhx),
-                                 pack_segment(sd[f"{g}.small_gru.convq.weight"], rhx)],
+            self._put(f"{g}.q", f"{g}.q", [(sd[f"{g}.large_gru.convq.weight"], rhx),
+                                           (sd[f"{g}.small_gru.convq.weight"], rhx)],
                       [sd[f"{g}.large_gru.convq.bias"], sd[f"{g}.small_gru.convq.bias"]], hd, self._bn("q", g))
         P, Pp = self.planes, self.planes_pad
-        self._put("convc1", [pack_segment(sd["encoder.convc1.weight"], [(P, Pp)])], [sd["encoder.convc1.bias"]], 256,
-                  bn["convc1"])
-        self._put("convc2", [pack_segment(sd["encoder.convc2.weight"], [(256, 256)])], [sd["encoder.convc2.bias"]],
+        self._put("convc1", "encoder.convc1", [(sd["encoder.convc1.weight"], [(P, Pp)])], [sd["encoder.convc1.bias"]],
+                  256, bn["convc1"])
+        self._put("convc2", "encoder.convc2", [(sd["encoder.convc2.weight"], [(256, 256)])], [sd["encoder.convc2.bias"]],
                   256, bn["convc2"])
-        self._put("convd2", [pack_segment(sd["encoder.convd2.weight"], [(64, 64)])], [sd["encoder.convd2.bias"]], 64,
-                  bn["convd2"])
-        self._put("enc_conv", [pack_segment(sd["encoder.conv.weight"], [(256, 256), (64, 64)])],
+        self._put("convd2", "encoder.convd2", [(sd["encoder.convd2.weight"], [(64, 64)])], [sd["encoder.convd2.bias"]],
+                  64, bn["convd2"])
+        self._put("enc_conv", "encoder.conv", [(sd["encoder.conv.weight"], [(256, 256), (64, 64)])],
                   [sd["encoder.conv.bias"]], hd - 1, bn["enc_conv"])
         self.f["convd1.w"] = sd["encoder.convd1.weight"].reshape(64, 49).contiguous()
         self.f["convd1.b"] = sd["encoder.convd1.bias"].contiguous()
-        self._put("head0", [pack_segment(sd["disp_head.conv.0.weight"], [(hd, hd)])], [sd["disp_head.conv.0.bias"]],
-                  hd, bn["head0"])
+        self._put("head0", "disp_head.conv.0", [(sd["disp_head.conv.0.weight"], [(hd, hd)])],
+                  [sd["disp_head.conv.0.bias"]], hd, bn["head0"])
         for i in (2, 3):
             pre = f"disp_head.conv.{i}"
             self.f[f"dw{i}.w"] = sd[pre + ".dwconv.weight"].reshape(hd, 49).contiguous()
             self.f[f"dw{i}.b"] = sd[pre + ".dwconv.bias"].contiguous()
             self.f[f"gamma{i}"] = sd[pre + ".gamma"].contiguous()
-            self._put(f"pw1_{i}", [pack_segment(sd[pre + ".pwconv1.weight"], [(hd, hd)])], [sd[pre + ".pwconv1.bias"]],
-                      4 * hd, bn["pw1"])
-            self._put(f"pw2_{i}", [pack_segment(sd[pre + ".pwconv2.weight"], [(4 * hd, 4 * hd)])],
+            self._put(f"pw1_{i}", pre + ".pwconv1", [(sd[pre + ".pwconv1.weight"], [(hd, hd)])],
+                      [sd[pre + ".pwconv1.bias"]], 4 * hd, bn["pw1"])
+            self._put(f"pw2_{i}", pre + ".pwconv2", [(sd[pre + ".pwconv2.weight"], [(4 * hd, 4 * hd)])],
                       [sd[pre + ".pwconv2.bias"]], hd, bn["pw2"])
-        self._put("head4", [pack_segment(sd["disp_head.conv.4.weight"], [(hd, hd)])], [sd["disp_head.conv.4.bias"]], 1,
-                  bn["head4"])
-        self._put("mask0", [pack_segment(sd["mask.0.weight"], [(hd, hd)])], [sd["mask.0.bias"]], 64, bn["mask0"])
-        self._put("mask2", [pack_segment(sd["mask.2.weight"], [(64, 64)])], [sd["mask.2.bias"]], 32, bn["mask2"])
+        self._put("head4", "disp_head.conv.4", [(sd["disp_head.conv.4.weight"], [(hd, hd)])],
+                  [sd["disp_head.conv.4.bias"]], 1, bn["head4"])
+        self._put("mask0", "mask.0", [(sd["mask.0.weight"], [(hd, hd)])], [sd["mask.0.bias"]], 64, bn["mask0"])
+        self._put("mask2", "mask.2", [(sd["mask.2.weight"], [(64, 64)])], [sd["mask.2.bias"]], 32, bn["mask2"])
 
     # ---- per-shape plan -------------------------------------------------------------------
     def _conv(self, plan: _Plan, name: str, wname: str, srcs, segs, bn_key: str, epilogue: int, **kw) -> None:
-        w, b, cout = self.w[wname]
-        launch = ConvLaunch(srcs=srcs, segs=segs, weight=w, bias=b, cout=cout, block_n=self.bn.get(name, self.bn[bn_key]),
-                            epilogue=epilogue, name=name, **kw)
+        lay, bn = plan.tile.get(name, (self._lay(name), self.bn.get(name, self.bn[bn_key])))
+        w, b, cout = self._weights(wname, lay, bn)
+        launch = ConvLaunch(srcs=srcs, segs=segs, weight=w, bias=b, cout=cout, block_n=bn, epilogue=epilogue, name=name,
+                            layout=lay, **kw)
         plan.add(name, launch)
         plan.flops += launch.flops
 
@@ -196,6 +228,13 @@ class SelectiveUpdateBlock:
     def _build_plan(self, B: int, H: int, W: int) -> _Plan:
         hd, dev, dt = self.hidden, self.device, self.dtype
         plan = _Plan()
+        # tile shape per launch: with >= 2 pairs' worth of pixels the two largest 3x3 layers run the halo
+        # variant with wide N tiles (a weight tile feeds 256 pixels, N = 256 keeps the MMA off the shared-
+        # memory bandwidth limit); a single 120x160 pair has too few pixel tiles for that to pay
+        plan.tile = {}
+        if B * H * W >= 2 * 19200 and not self.fixed_tiles:
+            plan.tile = {"gru04.conv0": (_lib.FSB_CONV_LAYOUT_HALO, 192), "gru04.conv1": (_lib.FSB_CONV_LAYOUT_HALO, 256),
+                         "encoder.convc2": (_lib.FSB_CONV_LAYOUT_TAP, 256)}
         plan.shape = [(B, H, W), (B, _down(H), _down(W)), (B, _down(_down(H)), _down(_down(W)))]
         new = lambda lvl, c, dtype=dt: torch.empty(*plan.shape[lvl], c, dtype=dtype, device=dev)
         plan.h32 = [new(l, hd, torch.float32) for l in range(3)]
@@ -329,9 +368,15 @@ class SelectiveUpdateBlock:
     def _capture(self, plan: _Plan, lookup: bool) -> torch.cuda.CUDAGraph:
         g = torch.cuda.CUDAGraph()
         torch.cuda.synchronize()
+        n0 = _lib.launch_count()
         with torch.cuda.graph(g):
             self.run_steps(plan, lookup)
+        g.fsb_kernels = _lib.launch_count() - n0  # libfsb200 kernels one replay launches
         return g
+
+    def _replay(self, g: torch.cuda.CUDAGraph) -> None:
+        g.replay()
+        self.replayed_kernels += g.fsb_kernels
 
     def _execute(self, plan: _Plan) -> None:
         plan.calls += 1
@@ -341,7 +386,7 @@ class SelectiveUpdateBlock:
             if plan.calls == 1:  # first call eager: sets kernel attributes, warms the allocator
                 return self.run_steps(plan)
             plan.graph = self._capture(plan, False)
-        plan.graph.replay()
+        self._replay(plan.graph)
 
     @torch.no_grad()
     def forward(self, net: List[Tensor], inp: Sequence[Tensor], corr: Tensor, disp: Tensor,
@@ -389,5 +434,5 @@ class SelectiveUpdateBlock:
                 continue
             if plan.iter_graph is None:
                 plan.iter_graph = self._capture(plan, True)
-            plan.iter_graph.replay()
+            self._replay(plan.iter_graph)
         return plan.disp.clone(), plan.mask, [plan.h32[l].permute(0, 3, 1, 2) for l in range(3)]

@@ -57,6 +57,9 @@ const char* fsb_last_error(void);
 /* number of kernels launched by this thread through the library since load
  * (bench.py's gpu_launches) */
 uint64_t fsb_launch_count(void);
+/* Programmatic dependent launch between consecutive kernels of a stream / captured graph (default on, or
+ * FSB_PDL=0 in the environment).  Returns the previous setting. */
+int fsb_set_pdl(int enable);
 
 /* ---- kernel 1: build_gwc_volume + build_concat_volume ----------------------------
  * replaces core/submodule.py:399-412 (with groupwise_correlation :388-397) and
@@ -153,6 +156,15 @@ enum fsb_epilogue {
   FSB_EPI_SCALE_RES = 5
 };
 
+/* K order of the packed weights = operand-feed strategy of the kernel:
+ *   FSB_CONV_LAYOUT_TAP  : segment -> tap (ky,kx row-major) -> source -> channel.  One 128-pixel tile per CTA,
+ *                          one 16 KB activation box per tap and 64-channel chunk.
+ *   FSB_CONV_LAYOUT_HALO : segment -> source -> 64-channel chunk -> kx -> ky -> channel.  Two stacked 16x8-pixel
+ *                          tiles per CTA; per chunk and kx ONE (32+2)-row activation box serves the three ky taps
+ *                          of both tiles through shifted UMMA descriptors, and every weight tile feeds 256 pixels.
+ *                          Needs 2 * nseg * block_n <= 512 TMEM columns. */
+enum fsb_conv_layout { FSB_CONV_LAYOUT_TAP = 0, FSB_CONV_LAYOUT_HALO = 1 };
+
 typedef struct fsb_conv_src {
   const void* ptr; /* (B,H,W,C) 16-bit */
   int C;           /* channels = pixel stride, multiple of 64 */
@@ -176,6 +188,7 @@ typedef struct fsb_conv_args {
   int Cout;           /* valid output channels per accumulator */
   int block_n;        /* 16, 32, 64, 96, 128, 160, 192, 224 or 256; nseg*block_n <= 512 */
   int stages;         /* smem pipeline depth, 0 = choose */
+  int layout;         /* fsb_conv_layout: K order of `weight` and operand feed of the kernel */
   int epilogue;       /* fsb_epilogue */
   void* out;          /* 16-bit NHWC or NULL */
   int ld_out;         /* channels per pixel of out */

@@ -49,7 +49,8 @@ def _rand(*shape, seed=0, scale=1.0):
     (1, 17, 31, [64], 32, 3, 32, "bias"),
     (1, 5, 7, [128], 1, 3, 16, "bias"),                # disparity head output
 ])
-def test_conv_vs_torch(fsb, dtype, cfg):
+@pytest.mark.parametrize("layout", [0, 1])  # FSB_CONV_LAYOUT_TAP / FSB_CONV_LAYOUT_HALO
+def test_conv_vs_torch(fsb, dtype, cfg, layout):
     from foundationstereo_b200 import _lib
     from foundationstereo_b200.conv import ConvLaunch, pack_rows, pack_segment
     B, H, W, cins, cout, k, bn, epi = cfg
@@ -61,7 +62,7 @@ def test_conv_vs_torch(fsb, dtype, cfg):
     want = {"relu": F.relu, "gelu": F.gelu, "bias": lambda t: t}[epi](want)
     srcs = [_nhwc(x, x.shape[1], dtype) for x in xs]
     rows = (cout + bn - 1) // bn * bn
-    wp = pack_rows([pack_segment(w, [(c, c) for c in cins])], rows).to(dtype).cuda().contiguous()
+    wp = pack_rows([pack_segment(w, [(c, c) for c in cins], layout)], rows).to(dtype).cuda().contiguous()
     bp = torch.zeros(1, rows)
     bp[0, :cout] = b
     ld = (cout + 7) // 8 * 8 + 8
@@ -70,7 +71,7 @@ def test_conv_vs_torch(fsb, dtype, cfg):
     code = {"relu": _lib.FSB_EPI_RELU, "gelu": _lib.FSB_EPI_GELU, "bias": _lib.FSB_EPI_BIAS}[epi]
     n0 = fsb.launch_count()
     ConvLaunch(srcs=srcs, segs=[(k, list(range(len(cins))))], weight=wp, bias=bp.cuda(), cout=cout, block_n=bn,
-               epilogue=code, out=out, ch_off=8, out_f32=out32, out_scale=0.5)()
+               epilogue=code, out=out, ch_off=8, out_f32=out32, out_scale=0.5, layout=layout)()
     torch.cuda.synchronize()
     assert fsb.launch_count() == n0 + 1
     assert rel_err(out32.cpu(), 0.5 * want) <= 1e-4
@@ -98,8 +99,9 @@ def test_conv_scale_residual(fsb, dtype):
 
 
 @pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
-@pytest.mark.parametrize("shape", [(1, 30, 40, 256), (2, 7, 9, 384)])
-def test_gru_gates_vs_torch(fsb, dtype, shape):
+@pytest.mark.parametrize("shape", [(1, 30, 40, 256), (2, 7, 9, 384), (1, 40, 20, 384)])
+@pytest.mark.parametrize("layout", [0, 1])
+def test_gru_gates_vs_torch(fsb, dtype, shape, layout):
     """The two gate launches reproduce RaftConvGRU small (1x1) + large (3x3) and the
     SelectiveConvGRU blend (core/update.py:90-95,119) from the same hx / x / h."""
     from foundationstereo_b200 import _lib
@@ -132,19 +134,20 @@ def test_gru_gates_vs_torch(fsb, dtype, shape):
     h32 = h.permute(0, 2, 3, 1).contiguous().cuda()
     hx16, x16 = _nhwc(hx, cin + hd, dtype), _nhwc(x, cin, dtype)
     hxs = [(cin + hd, cin + hd)]
-    zr_w = [interleave_zr(pack_segment(W_[g + "z"][0], hxs), pack_segment(W_[g + "r"][0], hxs), bn) for g in "ls"]
+    zr_w = [interleave_zr(pack_segment(W_[g + "z"][0], hxs, layout), pack_segment(W_[g + "r"][0], hxs, layout), bn)
+            for g in "ls"]
     zr_b = torch.stack([interleave_zr(W_[g + "z"][1][:, None], W_[g + "r"][1][:, None], bn).flatten() for g in "ls"])
     ConvLaunch(srcs=[hx16], segs=[(3, [0]), (1, [0])], weight=pack_rows(zr_w, 2 * hd).to(dtype).cuda(), bias=zr_b.cuda(),
                cout=2 * hd, block_n=bn, epilogue=_lib.FSB_EPI_GATE_ZR, h32=h32, z_l=z_l, z_s=z_s, rh_l=rh_l, rh_s=rh_s,
-               hidden=hd)()
+               hidden=hd, layout=layout)()
     rhx = [(hd, hd), (cin, cin)]
-    q_w = [pack_segment(W_[g + "q"][0], rhx) for g in "ls"]
+    q_w = [pack_segment(W_[g + "q"][0], rhx, layout) for g in "ls"]
     q_b = torch.stack([W_[g + "q"][1] for g in "ls"])
     h16 = new(hd)
     h32_out = torch.empty_like(h32)
     ConvLaunch(srcs=[rh_l, rh_s, x16], segs=[(3, [0, 2]), (1, [1, 2])], weight=pack_rows(q_w, hd).to(dtype).cuda(),
                bias=q_b.cuda(), cout=hd, block_n=64, epilogue=_lib.FSB_EPI_GATE_Q, h32=h32, att=att.reshape(B, H, W).cuda(),
-               z_l=z_l, z_s=z_s, h32_out=h32_out, h16_out=h16, hidden=hd)()
+               z_l=z_l, z_s=z_s, h32_out=h32_out, h16_out=h16, hidden=hd, layout=layout)()
     got = h32_out.permute(0, 3, 1, 2).cpu()
     # r*h and z are rounded to 16 bits at slightly different values than in the torch restatement
     # (fp32 accumulation order), so allow a few output ulps

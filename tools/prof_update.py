@@ -28,7 +28,9 @@ for kv in os.environ.get("FSB_BN", "").split(","):
     if "=" in kv:
         k, v = kv.split("=")
         bn[k] = int(v)
-ub = fsb.SelectiveUpdateBlock(state, "cuda", use_graph=False, block_n=bn or None)
+halo = os.environ.get("FSB_HALO")
+halo = None if halo is None else ([] if halo == "none" else halo.split(","))
+ub = fsb.SelectiveUpdateBlock(state, "cuda", use_graph=False, block_n=bn or None, halo=halo)
 x = synthetic.hot_path_inputs(B, 16, H, W, 8)
 c = lambda t: t.cuda()
 net, inp, att = [c(t) for t in x["net"]], [c(t) for t in x["inp"]], [c(t) for t in x["att"]]

@@ -20,6 +20,11 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t ph) {
   long long t0 = clock64();
   while (!mbar_try(bar, ph)) { if (clock64() - t0 > 2000000000ll) __trap(); }
 }
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 struct P {
   CUtensorMap map2;
   const uint8_t* flat;
@@ -29,14 +34,17 @@ struct P {
 __global__ void __launch_bounds__(128) pipe_kernel(const __grid_constant__ P p) {
   extern __shared__ __align__(1024) uint8_t sm[];
   __shared__ __align__(8) uint64_t bars[4][16];
-  const int warp = threadIdx.x >> 5;
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const uint32_t opbytes = (uint32_t)p.rows * 128u;
   const uint32_t stbytes = opbytes * p.ops;
   const int S = p.stages;
   const uint32_t base = ((smem_u32(sm) + 1023u) & ~1023u) + warp * S * stbytes;
-  if ((threadIdx.x & 31) == 0) {
-    for (int s = 0; s < S; ++s) mbar_init(smem_u32(&bars[warp][s]), 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  {
+    if ((threadIdx.x & 31) == 0) {
+      for (int s = 0; s < S; ++s) mbar_init(smem_u32(&bars[warp][s]), 1);
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
     const long long t0 = clock64();
     // lean loop: no integer division (running stage index / phase bit, incrementing coordinates)
     int s = 0;
@@ -50,7 +58,8 @@ __global__ void __launch_bounds__(128) pipe_kernel(const __grid_constant__ P p) 
       if (i >= S) {
         while (!mbar_try(full, ph ^ 1)) {}
       }
-      if (i < steps) {
+      __syncwarp();
+      if (i < steps && elect_one()) {
         mbar_expect_tx(full, stbytes);
         uint32_t dst = base + s * stbytes;
         for (int j = 0; j < nops; ++j) {
@@ -70,7 +79,7 @@ __global__ void __launch_bounds__(128) pipe_kernel(const __grid_constant__ P p) 
       }
       if (++s == S) { s = 0; ph ^= 1; }
     }
-    p.cycles[blockIdx.x * 4 + warp] = clock64() - t0;
+    if ((threadIdx.x & 31) == 0) p.cycles[blockIdx.x * 4 + warp] = clock64() - t0;
   }
 }
 typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
