@@ -389,90 +389,79 @@ lookup_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp, cons
 }
 
 // =====================================================================================
-// Kernel 3, fused output (out_layout 1): the same samples written as the 16-bit NHWC tensor
+// Kernel 3, fused output (out_layout 1/2): the same samples written as the 16-bit NHWC tensor
 // (B,H,W,Cpad) that encoder.convc1 (core/update.py:56,63) reads as its GEMM A operand -- the
-// "packing of the motion-encoder input".  One WARP per pixel:
+// "packing of the motion-encoder input".  One WARP per pixel, LANE = CHANNEL:
 //   phase A: lanes 0..K-1 / 16..16+K-1 compute the geo / corr sampling positions of every
-//            level (same fp32 round trip as above), window bases broadcast by shuffle;
-//   phase B: the (K+1) x Cg window of a level is one contiguous, 16-byte aligned run:
-//            float4 loads, all levels issued before any is used (memory-level parallelism);
-//   phase C: lane j computes outputs j, j+32, ... (channel order c*K+k, then the K corr
-//            taps) into a shared-memory row, which leaves as 16-byte coalesced stores.
+//            level (same fp32 round trip as above); window bases broadcast by shuffle, the
+//            per-tap fractions stay in the lane that computed them;
+//   phase B: in the (BHW, D_l, Cg) layout row dd of a pixel's window is Cg contiguous floats:
+//            lane c loads element c of the K+1 rows (one coalesced 4*Cg-byte request per row,
+//            no shared-memory staging), lane Cg loads the K+1 correlation taps.  The loads of
+//            ALL levels are issued before the first use (memory-level parallelism);
+//   phase C: lane c lerps its K outputs (fractions by shuffle) into a shared-memory row in
+//            the reference's channel order (level, c*K + k | K corr taps), which leaves as
+//            16-byte coalesced stores.
+// Channel groups beyond the first 32 (Cg + 1 > 32) are handled by repeating B/C per group.
 // =====================================================================================
 constexpr int kLkWarps = 8;
 
-template <typename T, int KT>
-__global__ void __launch_bounds__(kLkWarps * 32)
+template <typename T, int KT, int LT>
+__global__ void __launch_bounds__(kLkWarps * 32, 5)
 lookup_nhwc_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp, const float* __restrict__ coords,
-                   T* __restrict__ out, int Cg, int D, int W2, int L, int r, int Cpad, int wstride, long long npix) {
+                   T* __restrict__ out, int Cg, int D, int W2, int Lrt, int r, int Cpad, long long npix) {
   pdl_launch_dependents();  // the next kernel may start its prologue
   pdl_wait();               // inputs written by the previous kernel are complete and visible
-  extern __shared__ __align__(16) float lsm[];
-  const int K = KT > 0 ? KT : 2 * r + 1;
+  extern __shared__ __align__(16) uint8_t lsm[];
+  constexpr int K = KT;
+  const int L = LT > 0 ? LT : Lrt;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long pix = (long long)blockIdx.x * kLkWarps + warp;
   if (pix >= npix) return;
-  // per-warp shared memory: L windows of wstride floats, then 2*L*kLkKMax fractions, then the output row
-  // (every section a multiple of 4 floats so windows and the output row stay 16-byte aligned)
-  const int nfr = (2 * L * kLkKMax + 3) & ~3;
-  const int per_warp = L * wstride + nfr + ((Cpad * (int)sizeof(T) + 15) / 16) * 4;
-  float* wbase = lsm + (size_t)warp * per_warp;
-  float* frs = wbase + L * wstride;
-  T* orow = reinterpret_cast<T*>(frs + nfr);
-  const int run = (K + 1) * Cg;
+  T* orow = reinterpret_cast<T*>(lsm + (size_t)warp * Cpad * sizeof(T));
   const float dsp = __ldg(disp + pix), xco = __ldg(coords + pix);
-
-  // ---- phase A + B (unrolled over the <= 4 levels so the level pointers stay in the parameter bank)
-#pragma unroll
-  for (int l = 0; l < 4; ++l) {
-    if (l >= L) break;
-    const int Dl = D >> l, Wl = W2 >> l;
-    const float inv = 1.f / (float)(1 << l);
-    const float d = dsp * inv;
-    const bool is_cor = lane >= 16;
-    const int k = lane & 15;
-    const float xc = is_cor ? __fsub_rn(xco * inv, d) : d;
-    const int n = is_cor ? Wl : Dl;
-    const float ix0 = ref_unnormalised(__fadd_rn(xc, (float)(-r)), n);
-    const int base = (int)fminf(fmaxf(floorf(ix0), -1.0e6f), 1.0e6f);
-    if (k < K) {
-      const float ix = ref_unnormalised(__fadd_rn(xc, (float)(k - r)), n);
-      frs[(2 * l + (is_cor ? 1 : 0)) * kLkKMax + k] = ix - (float)(base + k);
-    }
-    const int gbase = __shfl_sync(0xffffffffu, base, 0), cbase = __shfl_sync(0xffffffffu, base, 16);
-    float* win = wbase + l * wstride;
-    const float* g = geo.p[l] + (size_t)pix * Dl * Cg;
-    if ((Cg & 3) == 0) {
-      const int q = Cg >> 2;  // float4 per window row
-      for (int i = lane; i < (K + 1) * q; i += 32) {
-        const int row = i / q, dd = gbase + row;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (dd >= 0 && dd < Dl) v = __ldg(reinterpret_cast<const float4*>(g + (size_t)dd * Cg) + (i - row * q));
-        *reinterpret_cast<float4*>(win + 4 * i) = v;
-      }
-    } else {
-      for (int i = lane; i < run; i += 32) {
-        const int row = i / Cg, dd = gbase + row;
-        win[i] = (dd >= 0 && dd < Dl) ? __ldg(g + (size_t)dd * Cg + (i - row * Cg)) : 0.f;
-      }
-    }
-    if (lane <= K) {
-      const int x = cbase + lane;
-      win[run + lane] = (x >= 0 && x < Wl) ? __ldg(cor.p[l] + (size_t)pix * Wl + x) : 0.f;
-    }
-  }
-  __syncwarp();
-  // ---- phase C
   const int nout = K * (Cg + 1);
-  for (int l = 0; l < L; ++l) {
-    const float* win = wbase + l * wstride;
-    const float* fg = frs + 2 * l * kLkKMax;
-    for (int j = lane; j < nout; j += 32) {
-      const int c = j / K, k = j - c * K;
-      float lo, hi, f;
-      if (c < Cg) { lo = win[k * Cg + c]; hi = win[(k + 1) * Cg + c]; f = fg[k]; }
-      else        { lo = win[run + k];    hi = win[run + k + 1];      f = fg[kLkKMax + k]; }
-      orow[l * nout + j] = from_f32<T>(lo * (1.f - f) + hi * f);
+  const bool is_cor_lane = lane >= 16;
+  const int kk = lane & 15;
+
+  for (int c0 = 0; c0 <= Cg; c0 += 32) {
+    const int c = c0 + lane;
+    const bool geo_ch = c < Cg, cor_ch = c == Cg;
+    float v[LT > 0 ? LT : 4][K + 1];
+    float frac[LT > 0 ? LT : 4];
+    // ---- phase A + B
+#pragma unroll
+    for (int l = 0; l < (LT > 0 ? LT : 4); ++l) {
+      if (l >= L) break;
+      const int Dl = D >> l, Wl = W2 >> l;
+      const float inv = 1.f / (float)(1 << l);
+      const float d = dsp * inv;
+      const float xc = is_cor_lane ? __fsub_rn(xco * inv, d) : d;
+      const int n = is_cor_lane ? Wl : Dl;
+      const float ix0 = ref_unnormalised(__fadd_rn(xc, (float)(-r)), n);
+      const int base = (int)fminf(fmaxf(floorf(ix0), -1.0e6f), 1.0e6f);
+      const float ix = ref_unnormalised(__fadd_rn(xc, (float)(kk - r)), n);
+      frac[l] = ix - (float)(base + kk);
+      const int gbase = __shfl_sync(0xffffffffu, base, 0), cbase = __shfl_sync(0xffffffffu, base, 16);
+      // lane-uniform form of "geo row dd, channel c" / "corr tap x": one pointer, one stride, one range
+      const int lo = geo_ch ? gbase : cbase;
+      const unsigned nl = (c <= Cg) ? (unsigned)(geo_ch ? Dl : Wl) : 0u;
+      const int st = geo_ch ? Cg : 1;
+      const float* src = geo_ch ? geo.p[l] + ((size_t)pix * Dl + lo) * Cg + c : cor.p[l] + (size_t)pix * Wl + lo;
+#pragma unroll
+      for (int j = 0; j <= K; ++j) v[l][j] = ((unsigned)(lo + j) < nl) ? __ldg(src + j * st) : 0.f;
+    }
+    // ---- phase C
+#pragma unroll
+    for (int l = 0; l < (LT > 0 ? LT : 4); ++l) {
+      if (l >= L) break;
+      T* o = orow + l * nout + c * K;
+#pragma unroll
+      for (int k = 0; k < K; ++k) {
+        const float f = __shfl_sync(0xffffffffu, frac[l], k + (cor_ch ? 16 : 0));
+        const float s = v[l][k] * (1.f - f) + v[l][k + 1] * f;
+        if (c <= Cg) o[k] = from_f32<T>(s);
+      }
     }
   }
   for (int j = L * nout + lane; j < Cpad; j += 32) orow[j] = from_f32<T>(0.f);
@@ -480,14 +469,6 @@ lookup_nhwc_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp,
   const uint4* src = reinterpret_cast<const uint4*>(orow);
   uint4* dst = reinterpret_cast<uint4*>(out + (size_t)pix * Cpad);
   for (int i = lane; i < Cpad * (int)sizeof(T) / 16; i += 32) dst[i] = src[i];
-}
-
-static size_t lookup_nhwc_smem(int Cg, int r, int L, int Cpad, int* wstride) {
-  const int K = 2 * r + 1;
-  const int ws = (((K + 1) * Cg + (K + 1)) + 3) & ~3;  // keeps every window 16-byte aligned
-  *wstride = ws;
-  const int per_warp = L * ws + ((2 * L * kLkKMax + 3) & ~3) + ((Cpad * 2 + 15) / 16) * 4;
-  return (size_t)kLkWarps * per_warp * sizeof(float);
 }
 
 static size_t lookup_smem_bytes(int Cg, int r) {
@@ -573,30 +554,36 @@ extern "C" int fsb_geo_lookup(float* const* geo_levels, float* const* corr_level
     const int K = 2 * r + 1;
     const int Cpad = round_up(L * K * (Cg + 1), 64);
     FSB_REQUIRE(aligned16(out), FSB_ERR_ALIGN, "fsb_geo_lookup: out not 16-byte aligned");
-    if ((Cg & 3) == 0)
-      for (int l = 0; l < L; ++l)
-        FSB_REQUIRE(aligned16(geo_levels[l]), FSB_ERR_ALIGN, "fsb_geo_lookup: geo level %d not 16-byte aligned", l);
-    int wstride = 0;
-    const size_t smem = lookup_nhwc_smem(Cg, r, L, Cpad, &wstride);
+    const size_t smem = (size_t)kLkWarps * Cpad * 2;
     FSB_REQUIRE(smem <= 227 * 1024, FSB_ERR_SHAPE, "fsb_geo_lookup: Cg=%d r=%d L=%d needs %zu B shared memory", Cg, r, L, smem);
     const long long npix = (long long)B * H * W;
     FSB_REQUIRE(npix / kLkWarps < (1ll << 31) - 1, FSB_ERR_SHAPE, "fsb_geo_lookup: too many pixels");
     const unsigned blocks = (unsigned)((npix + kLkWarps - 1) / kLkWarps);
-#define FSB_LAUNCH_LK(T, KT)                                                                                       \
+#define FSB_LAUNCH_LK(T, KT, LT)                                                                                   \
   do {                                                                                                             \
-    auto kern = lookup_nhwc_kernel<T, KT>;                                                                         \
+    auto kern = lookup_nhwc_kernel<T, KT, LT>;                                                                     \
     if (smem > 48 * 1024) {                                                                                        \
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);          \
       if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_lookup: cudaFuncSetAttribute");                           \
     }                                                                                                              \
-    launch_kernel(kern, dim3(blocks), dim3(kLkWarps * 32), smem, (cudaStream_t)stream, g, c, disp, coords, (T*)out, Cg, D, W2, L, r, Cpad, \
-                                                                 wstride, npix);                                   \
+    launch_kernel(kern, dim3(blocks), dim3(kLkWarps * 32), smem, (cudaStream_t)stream, g, c, disp, coords,         \
+                  (T*)out, Cg, D, W2, L, r, Cpad, npix);                                                           \
+  } while (0)
+#define FSB_LAUNCH_LK_K(T, LT)                                                                                     \
+  do {                                                                                                             \
+    switch (r) {                                                                                                   \
+      case 1: FSB_LAUNCH_LK(T, 3, LT); break;                                                                      \
+      case 2: FSB_LAUNCH_LK(T, 5, LT); break;                                                                      \
+      case 3: FSB_LAUNCH_LK(T, 7, LT); break;                                                                      \
+      default: FSB_LAUNCH_LK(T, 9, LT); break;                                                                     \
+    }                                                                                                              \
   } while (0)
     if (out_layout == 1) {
-      if (r == 4) FSB_LAUNCH_LK(__half, 9); else FSB_LAUNCH_LK(__half, 0);
+      if (L == 2) FSB_LAUNCH_LK_K(__half, 2); else FSB_LAUNCH_LK_K(__half, 0);
     } else {
-      if (r == 4) FSB_LAUNCH_LK(__nv_bfloat16, 9); else FSB_LAUNCH_LK(__nv_bfloat16, 0);
+      if (L == 2) FSB_LAUNCH_LK_K(__nv_bfloat16, 2); else FSB_LAUNCH_LK_K(__nv_bfloat16, 0);
     }
+#undef FSB_LAUNCH_LK_K
 #undef FSB_LAUNCH_LK
     FSB_CHECK_LAUNCH("fsb_geo_lookup");
     return FSB_OK;

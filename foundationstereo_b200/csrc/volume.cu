@@ -4,23 +4,35 @@
 // build_concat_volume (core/submodule.py:416-427) of the reference.
 //
 // HBM-write bound: per pixel the kernel must emit (G + 2*Cp) * D values and read only
-// 2*C + 2*Cp.  One CTA owns one image row (b,h) and one "unit" of output channels:
-//   unit <  G            : correlation group g = unit        (D*W outputs, cpg FMAs each)
-//   unit >= G            : a chunk of kCatChunk concat channels, left half then right half
-// The source rows of the unit are staged ONCE in shared memory as fp32 with a zero
-// apron of round4(D)+4 columns on the left, so the sliding disparity window needs no
-// bounds test and the w < d zero region of the reference falls out of the arithmetic.
-// The per-group L2 normalisation (x / max(||x||, 1e-12), fp32) is done once per row in
-// shared memory instead of once per disparity as the reference does.
-// Each thread produces a 4(d) x 4(w) register block per step: three 128-bit shared
-// loads per channel feed 16 FMAs, and every global store is a full 16-byte (fp32) or
-// 8-byte (fp16/bf16) vector along W.
+// 2*C + 2*Cp, so everything here is about spending as few instructions per 16-byte store as
+// possible.  One CTA owns one image row (b,h) and one "unit" of output channels:
+//   unit <  G : correlation group g = unit.  A thread loads one column of the group (C/G
+//               channels of one pixel, coalesced along W), L2-normalises it in registers
+//               (x / max(||x||, 1e-12), fp32, once per row instead of once per disparity as
+//               the reference does) and writes it to shared memory; the right row gets a zero
+//               apron of round4(D)+4 columns, so the sliding disparity window needs no bounds
+//               test.  Outputs are produced as 4(d) x 4(w) register blocks (three 128-bit
+//               shared loads per channel feed 16 FMAs); blocks that lie entirely in the
+//               reference's w < d zero triangle (32 % of them at W=160, D=104) are never
+//               computed, only zero-filled.
+//   unit >= G : a chunk of kCatChunk concat channels, left half then right half.  A thread
+//               owns one float4 column and walks down the disparities: the left half stores
+//               the same register D/nrow times; the right half keeps four copies of the row in
+//               shared memory, copy k shifted by k floats, so the window of disparity d is ONE
+//               aligned 128-bit shared load from copy (d & 3).
+// Every global store is a full 16-byte (fp32) or 8-byte (fp16/bf16) vector along W.
 #include "common.cuh"
 
 namespace fsb {
 
 constexpr int kVolThreads = 256;
 constexpr int kCatChunk = 3;  // concat channels per CTA (Cp = 12 -> 4 + 4 units)
+
+// number of non-zero 4x4 blocks in block rows [0, dq): row j keeps the blocks w4 >= j
+__host__ __device__ inline int vol_row_start(int dq, int nw4) {
+  const int m = dq < nw4 ? dq : nw4;
+  return m * nw4 - (m * (m - 1)) / 2;
+}
 
 template <typename T, bool VEC>
 __global__ void __launch_bounds__(kVolThreads)
@@ -46,32 +58,61 @@ volume_kernel(const T* __restrict__ fl, const T* __restrict__ fr, const T* __res
     const int cpg = C / G;
     float* Ls = smem;             // [cpg][Wp]
     float* Rs = smem + cpg * Wp;  // [cpg][RS]
-    for (int i = tid; i < cpg * Wp + cpg * RS; i += kVolThreads) smem[i] = 0.f;
-    __syncthreads();
-    const size_t row0 = ((size_t)(b * C + unit * cpg) * H + h) * W;
-    for (int i = tid; i < cpg * W; i += kVolThreads) {
-      const int c = i / W, w = i - c * W;
-      const size_t src = row0 + (size_t)c * HW + w;
-      Ls[c * Wp + w] = to_f32<T>(fl[src]);
-      Rs[c * RS + Dpad + w] = to_f32<T>(fr[src]);
+    // zero apron (and the <= 3 pad columns on the right of both rows)
+    for (int j = tid; j < Dpad; j += kVolThreads)
+      for (int c = 0; c < cpg; ++c) Rs[c * RS + j] = 0.f;
+    if (Wp != W && tid < cpg * (Wp - W)) {
+      const int c = tid / (Wp - W), j = W + tid - c * (Wp - W);
+      Ls[c * Wp + j] = 0.f;
+      Rs[c * RS + Dpad + j] = 0.f;
     }
-    __syncthreads();
-    // F.normalize: x / max(sqrt(sum x^2), eps)
-    for (int w = tid; w < 2 * W; w += kVolThreads) {
-      float* col = (w < W) ? (Ls + w) : (Rs + Dpad + (w - W));
-      const int st = (w < W) ? Wp : RS;
+    // F.normalize: x / max(sqrt(sum x^2), eps), one column per thread (second pass hits L1)
+    const size_t row0 = ((size_t)(b * C + unit * cpg) * H + h) * W;
+    for (int it = tid; it < 2 * W; it += kVolThreads) {
+      const bool right = it >= W;
+      const int w = right ? it - W : it;
+      const T* src = (right ? fr : fl) + row0 + w;
       float ss = 0.f;
-      for (int c = 0; c < cpg; ++c) ss = fmaf(col[c * st], col[c * st], ss);
+      for (int c = 0; c < cpg; ++c) {
+        const float x = to_f32<T>(src[(size_t)c * HW]);
+        ss = fmaf(x, x, ss);
+      }
       const float den = fmaxf(sqrtf(ss), 1e-12f);
-      for (int c = 0; c < cpg; ++c) col[c * st] = __fdiv_rn(col[c * st], den);
+      float* dst = right ? (Rs + Dpad + w) : (Ls + w);
+      const int st = right ? RS : Wp;
+      for (int c = 0; c < cpg; ++c) dst[c * st] = __fdiv_rn(to_f32<T>(src[(size_t)c * HW]), den);
     }
     __syncthreads();
 
     const int nd4 = (D + 3) >> 2;
     T* out0 = gwc + (size_t)b * gwc_bs + ((size_t)unit * D) * HW + (size_t)h * W;
-    for (int it = tid; it < nd4 * nw4; it += kVolThreads) {
-      const int dq = it / nw4;
-      const int w = (it - dq * nw4) << 2;
+    // zero triangle: out[d][w] = 0 for the float4 columns w4 < d/4 (the rest of w < d falls out of the apron)
+    {
+      const int lane = tid & 31, warp = tid >> 5;
+      for (int d = warp; d < D; d += kVolThreads / 32) {
+        const int nz = min(d >> 2, nw4);
+        for (int w4 = lane; w4 < nz; w4 += 32) {
+          T* o = out0 + (size_t)d * HW + 4 * w4;
+          if (VEC) {
+            Quad<T>::store(o, 0.f, 0.f, 0.f, 0.f);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if (4 * w4 + i < W) o[i] = from_f32<T>(0.f);
+          }
+        }
+      }
+    }
+    const int total = vol_row_start(nd4, nw4);
+    for (int it = tid; it < total; it += kVolThreads) {
+      // block row dq = the last one that starts at or before item `it`
+      int lo = 0, hi = min(nd4, nw4) - 1;
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (vol_row_start(mid, nw4) <= it) lo = mid; else hi = mid - 1;
+      }
+      const int dq = lo;
+      const int w = (dq + it - vol_row_start(dq, nw4)) << 2;
       const int d0 = dq << 2;
       float acc[4][4];
 #pragma unroll
@@ -118,29 +159,53 @@ volume_kernel(const T* __restrict__ fl, const T* __restrict__ fr, const T* __res
   const int c0 = (right ? u - nchunk : u) * kCatChunk;
   const int nc = min(kCatChunk, Cp - c0);
   const T* src = right ? pr : pl;
-  for (int i = tid; i < nc * RS; i += kVolThreads) smem[i] = 0.f;
+  // four copies of each source row, copy k shifted right by k floats: [k][c][RS + 4]
+  const int CS = RS + 4;
+  for (int i = tid; i < 4 * nc * CS; i += kVolThreads) smem[i] = 0.f;
   __syncthreads();
-  for (int i = tid; i < nc * W; i += kVolThreads) {
-    const int c = i / W, w = i - c * W;
-    smem[c * RS + Dpad + w] = to_f32<T>(src[((size_t)(b * Cp + c0 + c) * H + h) * W + w]);
-  }
-  __syncthreads();
-  const int per_c = D * nw4;
-  for (int it = tid; it < nc * per_c; it += kVolThreads) {
-    const int c = it / per_c;
-    const int rem = it - c * per_c;
-    const int d = rem / nw4;
-    const int w = (rem - d * nw4) << 2;
-    const float* s = smem + c * RS + Dpad + w - (right ? d : 0);
-    const float v0 = s[0], v1 = s[1], v2 = s[2], v3 = s[3];
-    T* o = cat + (size_t)b * cat_bs + ((size_t)((right ? Cp : 0) + c0 + c) * D + d) * HW + (size_t)h * W + w;
-    if (VEC) {
-      Quad<T>::store(o, v0, v1, v2, v3);
-    } else {
-      const float v[4] = {v0, v1, v2, v3};
+  for (int c = 0; c < nc; ++c)
+    for (int w = tid; w < W; w += kVolThreads) {
+      const float v = to_f32<T>(src[((size_t)(b * Cp + c0 + c) * H + h) * W + w]);
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
-        if (w + i < W) o[i] = from_f32<T>(v[i]);
+      for (int k = 0; k < 4; ++k) smem[(k * nc + c) * CS + Dpad + w + k] = v;
+    }
+  __syncthreads();
+  // thread = (disparity phase dsub, float4 column w4); rows of the output are W floats apart by HW
+  const int nrow = nw4 < kVolThreads ? kVolThreads / nw4 : 1;
+  const int dsub = nw4 < kVolThreads ? tid / nw4 : 0;
+  const int wstep = nw4 < kVolThreads ? nw4 : kVolThreads;
+  if (dsub >= nrow) return;
+  for (int w4 = tid - dsub * nw4; w4 < nw4; w4 += wstep) {
+    const int w = w4 << 2;
+    for (int c = 0; c < nc; ++c) {
+      T* o = cat + (size_t)b * cat_bs + ((size_t)((right ? Cp : 0) + c0 + c) * D + dsub) * HW + (size_t)h * W + w;
+      if (!right) {
+        const float4 v = *reinterpret_cast<const float4*>(smem + c * CS + Dpad + w);
+        for (int d = dsub; d < D; d += nrow, o += (size_t)nrow * HW) {
+          if (VEC) {
+            Quad<T>::store(o, v.x, v.y, v.z, v.w);
+          } else {
+            const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if (w + i < W) o[i] = from_f32<T>(vv[i]);
+          }
+        }
+      } else {
+        for (int d = dsub; d < D; d += nrow, o += (size_t)nrow * HW) {
+          // R[w - d + i], i = 0..3  ==  copy (d & 3) at the aligned offset Dpad + w - d + (d & 3)
+          const int k = d & 3;
+          const float4 v = *reinterpret_cast<const float4*>(smem + (k * nc + c) * CS + Dpad + w - d + k);
+          if (VEC) {
+            Quad<T>::store(o, v.x, v.y, v.z, v.w);
+          } else {
+            const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if (w + i < W) o[i] = from_f32<T>(vv[i]);
+          }
+        }
+      }
     }
   }
 }
@@ -152,7 +217,7 @@ static int launch_volume(const void* fl, const void* fr, const void* pl, const v
   const int Wp = round_up(W, 4), Dpad = round_up(D, 4) + 4, RS = Dpad + Wp;
   const int cpg = gwc ? C / G : 0;
   const size_t smem_gwc = (size_t)(cpg * Wp + cpg * RS) * sizeof(float);
-  const size_t smem_cat = cat ? (size_t)kCatChunk * RS * sizeof(float) : 0;
+  const size_t smem_cat = cat ? (size_t)4 * kCatChunk * (RS + 4) * sizeof(float) : 0;
   const size_t smem = smem_gwc > smem_cat ? smem_gwc : smem_cat;
   FSB_REQUIRE(smem <= 227 * 1024, FSB_ERR_SHAPE,
               "fsb_volume_gwc_concat: row of C/G=%d x W=%d with D=%d needs %zu B shared memory (> 227 KB)",
