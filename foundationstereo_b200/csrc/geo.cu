@@ -262,14 +262,10 @@ geo_pyramid_fast_kernel(const float* __restrict__ vol, LevelPtrs lv, int D, int 
 }
 
 // =====================================================================================
-// Kernel 3: lookup.  One CTA = 32 consecutive pixels of one image row, all levels.
-//   phase 0: per (pixel, level): sampling positions exactly as the reference computes
-//            them (x -> 2x/(n-1)-1 -> ((.+1)/2)*(n-1), fp32, no FMA contraction), window
-//            base = floor of the first tap, per-tap fraction relative to base+k.
-//   phase 1: the (K+1) x Cg window of each pixel is ONE contiguous run in the
-//            (BHW, D_l, Cg) layout: coalesced loads into smem (row stride odd).
-//   phase 2: lane = pixel, warps stride over channels: 10 conflict-free smem reads ->
-//            9 outputs, stored straight to NCHW (128-byte coalesced along W).
+// Kernel 3: lookup (core/geometry.py:43-65, bilinear_sampler core/utils/utils.py:44-55).
+//   positions: exactly as the reference computes them (x -> 2x/(n-1)-1 -> ((.+1)/2)*(n-1), fp32,
+//   no FMA contraction); window base = floor of the first tap, per-tap fraction relative to base+k.
+//   In the (BHW, D_l, Cg) layout the (K+1) x Cg window of a pixel is one contiguous run.
 // =====================================================================================
 constexpr int kLkPix = 32;
 constexpr int kLkThreads = 256;
@@ -280,112 +276,6 @@ __device__ __forceinline__ float ref_unnormalised(float x, int n) {
   const float nm1 = (float)(n - 1);
   const float g = __fsub_rn(__fdiv_rn(__fmul_rn(2.f, x), nm1), 1.f);
   return __fmul_rn(__fmul_rn(__fadd_rn(g, 1.f), 0.5f), nm1);
-}
-
-__global__ void __launch_bounds__(kLkThreads)
-lookup_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp, const float* __restrict__ coords,
-              float* __restrict__ out, int Cg, int D, int H, int W, int W2, int L, int r) {
-  pdl_launch_dependents();  // the next kernel may start its prologue
-  pdl_wait();               // inputs written by the previous kernel are complete and visible
-  extern __shared__ float sm[];
-  const int K = 2 * r + 1;
-  const int run = (K + 1) * Cg;      // floats per pixel window
-  const int PS = run | 1;            // odd pixel stride -> lane==pixel reads are conflict free
-  float* win = sm;                   // [32][PS]
-  float* cwin = win + kLkPix * PS;   // [32][K+2]
-  float* gfr = cwin + kLkPix * (K + 2);       // [32][kLkKMax] geo fractions
-  float* cfr = gfr + kLkPix * kLkKMax;        // [32][kLkKMax] corr fractions
-  int* gbase = reinterpret_cast<int*>(cfr + kLkPix * kLkKMax);  // [32]
-  int* cbase = gbase + kLkPix;                                   // [32]
-
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int w0 = blockIdx.x * kLkPix;
-  const int bh = blockIdx.y, b = bh / H, h = bh - b * H;
-  const size_t p0 = (size_t)bh * W + w0;
-  const int npix = min(kLkPix, W - w0);
-  const int CH = L * K * (Cg + 1);
-  const size_t HW = (size_t)H * W;
-  float* obase = out + ((size_t)b * CH * H + h) * W + w0;
-
-  for (int l = 0; l < L; ++l) {
-    const int Dl = D >> l, Wl = W2 >> l;
-    const float inv = 1.f / (float)(1 << l);
-    // ---- phase 0
-    if (tid < 2 * kLkPix) {
-      const int pix = tid & 31;
-      const bool is_cor = tid >= kLkPix;
-      if (pix < npix) {
-        const float d = disp[p0 + pix] * inv;  // exact: power-of-two scale
-        const float xc = is_cor ? __fsub_rn(coords[p0 + pix] * inv, d) : d;
-        const int n = is_cor ? Wl : Dl;
-        float* fr = (is_cor ? cfr : gfr) + pix * kLkKMax;
-        int base = 0;
-        for (int k = 0; k < K; ++k) {
-          const float ix = ref_unnormalised(__fadd_rn(xc, (float)(k - r)), n);
-          if (k == 0) {
-            // clamp so that int conversion is safe for wild disparities; any base outside
-            // [-(K+1), n] gives an all-zero window, exactly like the reference's padding
-            base = (int)fminf(fmaxf(floorf(ix), -1.0e6f), 1.0e6f);
-          }
-          fr[k] = ix - (float)(base + k);
-        }
-        (is_cor ? cbase : gbase)[pix] = base;
-      }
-    }
-    __syncthreads();
-    // ---- phase 1: windows -> smem (zero outside [0, n-1])
-    {
-      const float* g = geo.p[l];
-      for (int i = tid; i < kLkPix * run; i += kLkThreads) {
-        const int pix = i / run, j = i - pix * run;
-        float v = 0.f;
-        if (pix < npix) {
-          const int row = j / Cg;
-          const int dd = gbase[pix] + row;
-          if (dd >= 0 && dd < Dl) v = g[((p0 + pix) * Dl + dd) * Cg + (j - row * Cg)];
-        }
-        win[pix * PS + j] = v;
-      }
-      const float* cr = cor.p[l];
-      for (int i = tid; i < kLkPix * (K + 1); i += kLkThreads) {
-        const int pix = i / (K + 1), j = i - pix * (K + 1);
-        float v = 0.f;
-        if (pix < npix) {
-          const int x = cbase[pix] + j;
-          if (x >= 0 && x < Wl) v = cr[(p0 + pix) * Wl + x];
-        }
-        cwin[pix * (K + 2) + j] = v;
-      }
-    }
-    __syncthreads();
-    // ---- phase 2
-    if (lane < npix) {
-      float fg[kLkKMax], fc[kLkKMax];
-#pragma unroll
-      for (int k = 0; k < kLkKMax; ++k) {
-        fg[k] = (k < K) ? gfr[lane * kLkKMax + k] : 0.f;
-        fc[k] = (k < K) ? cfr[lane * kLkKMax + k] : 0.f;
-      }
-      float* ol = obase + (size_t)l * K * (Cg + 1) * HW + lane;
-      for (int c = warp; c <= Cg; c += kLkThreads / 32) {
-        const bool is_cor = (c == Cg);
-        const float* src = is_cor ? (cwin + lane * (K + 2)) : (win + lane * PS + c);
-        const int st = is_cor ? 1 : Cg;
-        float* o = ol + (size_t)c * K * HW;
-        float lo = src[0];
-#pragma unroll
-        for (int k = 0; k < kLkKMax; ++k) {
-          if (k < K) {
-            const float hi = src[(k + 1) * st];
-            const float f = is_cor ? fc[k] : fg[k];
-            o[(size_t)k * HW] = lo * (1.f - f) + hi * f;
-            lo = hi;
-          }
-        }
-      }
-    }
-    __syncthreads();
-  }
 }
 
 // =====================================================================================
@@ -406,61 +296,83 @@ lookup_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp, cons
 // =====================================================================================
 constexpr int kLkWarps = 8;
 
-template <typename T, int KT, int LT>
+// Phases A + B for one level of one pixel (whole warp, see lookup_nhwc_kernel): returns this lane's
+// geo window v[0..K] (channel c of rows gbase .. gbase+K, zero outside [0, Dl)), this lane's correlation
+// tap cv (lane j <= K holds tap cbase + j), and this lane's per-tap fraction (lane k: geo tap k, lane 16+k:
+// corr tap k).  Window bases are warp-uniform, so the "whole window inside" fast path is a uniform branch.
+template <int K>
+__device__ __forceinline__ void lookup_level(const float* __restrict__ gl, const float* __restrict__ cl, long long pix,
+                                             int Cg, int Dl, int Wl, float d, float xcor, int r, int lane, int c,
+                                             bool geo_ch, float (&v)[K + 1], float& cv, float& frac) {
+  const bool is_cor_lane = lane >= 16;
+  const int kk = lane & 15;
+  const float xc = is_cor_lane ? xcor : d;
+  const int n = is_cor_lane ? Wl : Dl;
+  const float ix = ref_unnormalised(__fadd_rn(xc, (float)(kk - r)), n);
+  const float ix0 = __shfl_sync(0xffffffffu, ix, lane & 16);  // tap 0 of this lane's half
+  const int base = (int)fminf(fmaxf(floorf(ix0), -1.0e6f), 1.0e6f);
+  frac = ix - (float)(base + kk);
+  const int gbase = __shfl_sync(0xffffffffu, base, 0), cbase = __shfl_sync(0xffffffffu, base, 16);
+  const float* g = gl + ((size_t)pix * Dl + gbase) * Cg + c;  // dereferenced only where the row exists
+  if (gbase >= 0 && gbase + K < Dl) {
+    if (geo_ch) {
+#pragma unroll
+      for (int j = 0; j <= K; ++j) v[j] = __ldg(g + j * Cg);
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j <= K; ++j) v[j] = (geo_ch && (unsigned)(gbase + j) < (unsigned)Dl) ? __ldg(g + j * Cg) : 0.f;
+  }
+  const int x = cbase + lane;
+  cv = (lane <= K && (unsigned)x < (unsigned)Wl) ? __ldg(cl + (size_t)pix * Wl + x) : 0.f;
+}
+
+template <typename T, int KT, int LT, int CGT>
 __global__ void __launch_bounds__(kLkWarps * 32, 5)
 lookup_nhwc_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp, const float* __restrict__ coords,
-                   T* __restrict__ out, int Cg, int D, int W2, int Lrt, int r, int Cpad, long long npix) {
+                   T* __restrict__ out, int Cgrt, int D, int W2, int Lrt, int r, int Cpad, long long npix) {
   pdl_launch_dependents();  // the next kernel may start its prologue
   pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ __align__(16) uint8_t lsm[];
   constexpr int K = KT;
+  constexpr int NL = LT > 0 ? LT : 4;
   const int L = LT > 0 ? LT : Lrt;
+  const int Cg = CGT > 0 ? CGT : Cgrt;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long pix = (long long)blockIdx.x * kLkWarps + warp;
   if (pix >= npix) return;
   T* orow = reinterpret_cast<T*>(lsm + (size_t)warp * Cpad * sizeof(T));
   const float dsp = __ldg(disp + pix), xco = __ldg(coords + pix);
   const int nout = K * (Cg + 1);
-  const bool is_cor_lane = lane >= 16;
-  const int kk = lane & 15;
 
-  for (int c0 = 0; c0 <= Cg; c0 += 32) {
+  for (int c0 = 0; c0 < Cg; c0 += 32) {
     const int c = c0 + lane;
-    const bool geo_ch = c < Cg, cor_ch = c == Cg;
-    float v[LT > 0 ? LT : 4][K + 1];
-    float frac[LT > 0 ? LT : 4];
-    // ---- phase A + B
+    const bool geo_ch = c < Cg;
+    float v[NL][K + 1], cv[NL], frac[NL];
+    // ---- phases A + B, all levels before the first use
 #pragma unroll
-    for (int l = 0; l < (LT > 0 ? LT : 4); ++l) {
+    for (int l = 0; l < NL; ++l) {
       if (l >= L) break;
-      const int Dl = D >> l, Wl = W2 >> l;
       const float inv = 1.f / (float)(1 << l);
-      const float d = dsp * inv;
-      const float xc = is_cor_lane ? __fsub_rn(xco * inv, d) : d;
-      const int n = is_cor_lane ? Wl : Dl;
-      const float ix0 = ref_unnormalised(__fadd_rn(xc, (float)(-r)), n);
-      const int base = (int)fminf(fmaxf(floorf(ix0), -1.0e6f), 1.0e6f);
-      const float ix = ref_unnormalised(__fadd_rn(xc, (float)(kk - r)), n);
-      frac[l] = ix - (float)(base + kk);
-      const int gbase = __shfl_sync(0xffffffffu, base, 0), cbase = __shfl_sync(0xffffffffu, base, 16);
-      // lane-uniform form of "geo row dd, channel c" / "corr tap x": one pointer, one stride, one range
-      const int lo = geo_ch ? gbase : cbase;
-      const unsigned nl = (c <= Cg) ? (unsigned)(geo_ch ? Dl : Wl) : 0u;
-      const int st = geo_ch ? Cg : 1;
-      const float* src = geo_ch ? geo.p[l] + ((size_t)pix * Dl + lo) * Cg + c : cor.p[l] + (size_t)pix * Wl + lo;
-#pragma unroll
-      for (int j = 0; j <= K; ++j) v[l][j] = ((unsigned)(lo + j) < nl) ? __ldg(src + j * st) : 0.f;
+      const float d = dsp * inv;  // exact: power-of-two scale
+      lookup_level<K>(geo.p[l], cor.p[l], pix, Cg, D >> l, W2 >> l, d, __fsub_rn(xco * inv, d), r, lane, c, geo_ch,
+                      v[l], cv[l], frac[l]);
     }
-    // ---- phase C
+    // ---- phase C.  The 16-bit result cannot tell lo*(1-f) + hi*f from lo + f*(hi-lo): the shorter form is used.
 #pragma unroll
-    for (int l = 0; l < (LT > 0 ? LT : 4); ++l) {
+    for (int l = 0; l < NL; ++l) {
       if (l >= L) break;
       T* o = orow + l * nout + c * K;
 #pragma unroll
       for (int k = 0; k < K; ++k) {
-        const float f = __shfl_sync(0xffffffffu, frac[l], k + (cor_ch ? 16 : 0));
-        const float s = v[l][k] * (1.f - f) + v[l][k + 1] * f;
-        if (c <= Cg) o[k] = from_f32<T>(s);
+        const float f = __shfl_sync(0xffffffffu, frac[l], k);
+        const float s = fmaf(f, v[l][k + 1] - v[l][k], v[l][k]);
+        if (geo_ch) o[k] = from_f32<T>(s);
+      }
+      if (c0 == 0) {
+        const float hi = __shfl_down_sync(0xffffffffu, cv[l], 1);
+        const float f = __shfl_sync(0xffffffffu, frac[l], (lane + 16) & 31);
+        if (lane < K) orow[l * nout + Cg * K + lane] = from_f32<T>(fmaf(f, hi - cv[l], cv[l]));
       }
     }
   }
@@ -471,10 +383,83 @@ lookup_nhwc_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp,
   for (int i = lane; i < Cpad * (int)sizeof(T) / 16; i += 32) dst[i] = src[i];
 }
 
+// Kernel 3, reference output (out_layout 0): (B, L*K*(Cg+1), H, W) fp32, the tensor geo_fn returns in the
+// reference (core/geometry.py:60-65).  Same lane = channel gather as above; one CTA owns 32 consecutive
+// pixels of an image row, each warp gathers four of them per level into a [K*(Cg+1)][32 + 1] shared tile
+// (channel-major: bank = 9c + k + pixel, conflict free), and the tile leaves as 128-byte rows along W.
+// The lerp keeps the reference's form lo*(1-f) + hi*f.
+template <int KT, int CGT>
+__global__ void __launch_bounds__(kLkThreads, 4)
+lookup_nchw_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp, const float* __restrict__ coords,
+                   float* __restrict__ out, int Cgrt, int D, int H, int W, int W2, int L, int r) {
+  pdl_launch_dependents();  // the next kernel may start its prologue
+  pdl_wait();               // inputs written by the previous kernel are complete and visible
+  extern __shared__ float sm[];  // [nout][33]
+  constexpr int K = KT;
+  constexpr int PPW = kLkPix / (kLkThreads / 32);  // pixels per warp
+  const int Cg = CGT > 0 ? CGT : Cgrt;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int w0 = blockIdx.x * kLkPix;
+  const int bh = blockIdx.y, b = bh / H, h = bh - b * H;
+  const long long p0 = (long long)bh * W + w0;
+  const int npix = min(kLkPix, W - w0);
+  const int nout = K * (Cg + 1);
+  const size_t HW = (size_t)H * W;
+  float* obase = out + ((size_t)b * L * nout * H + h) * W + w0;
+  float dsp[PPW], xco[PPW];
+#pragma unroll
+  for (int i = 0; i < PPW; ++i) {
+    const int px = warp * PPW + i;
+    dsp[i] = px < npix ? __ldg(disp + p0 + px) : 0.f;
+    xco[i] = px < npix ? __ldg(coords + p0 + px) : 0.f;
+  }
+  for (int l = 0; l < L; ++l) {
+    const int Dl = D >> l, Wl = W2 >> l;
+    const float inv = 1.f / (float)(1 << l);
+    for (int c0 = 0; c0 < Cg; c0 += 32) {
+      const int c = c0 + lane;
+      const bool geo_ch = c < Cg;
+#pragma unroll
+      for (int i0 = 0; i0 < PPW; i0 += 2) {
+        float v[2][K + 1], cv[2], frac[2];
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int px = warp * PPW + i0 + i;
+          const float d = dsp[i0 + i] * inv;
+          // a slot beyond the row end gathers the row's last pixel again (harmless, never stored)
+          lookup_level<K>(geo.p[l], cor.p[l], p0 + min(px, npix - 1), Cg, Dl, Wl, d, __fsub_rn(xco[i0 + i] * inv, d), r, lane, c, geo_ch,
+                          v[i], cv[i], frac[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          const int px = warp * PPW + i0 + i;
+          const bool live = px < npix;  // warp-uniform
+          float* t = sm + (c * K) * (kLkPix + 1) + px;
+#pragma unroll
+          for (int k = 0; k < K; ++k) {
+            const float f = __shfl_sync(0xffffffffu, frac[i], k);
+            if (live && geo_ch) t[k * (kLkPix + 1)] = v[i][k] * (1.f - f) + v[i][k + 1] * f;
+          }
+          if (c0 == 0) {
+            const float hi = __shfl_down_sync(0xffffffffu, cv[i], 1);
+            const float f = __shfl_sync(0xffffffffu, frac[i], (lane + 16) & 31);
+            if (live && lane < K) sm[(Cg * K + lane) * (kLkPix + 1) + px] = cv[i] * (1.f - f) + hi * f;
+          }
+        }
+      }
+    }
+    __syncthreads();
+    if (lane < npix) {
+      float* ol = obase + (size_t)l * nout * HW + lane;
+      for (int j = warp; j < nout; j += kLkThreads / 32) ol[(size_t)j * HW] = sm[j * (kLkPix + 1) + lane];
+    }
+    __syncthreads();
+  }
+}
+
 static size_t lookup_smem_bytes(int Cg, int r) {
   const int K = 2 * r + 1;
-  const int PS = ((K + 1) * Cg) | 1;
-  return (size_t)(kLkPix * PS + kLkPix * (K + 2) + 2 * kLkPix * kLkKMax + 2 * kLkPix) * sizeof(float);
+  return (size_t)K * (Cg + 1) * (kLkPix + 1) * sizeof(float);
 }
 
 }  // namespace fsb
@@ -561,7 +546,7 @@ extern "C" int fsb_geo_lookup(float* const* geo_levels, float* const* corr_level
     const unsigned blocks = (unsigned)((npix + kLkWarps - 1) / kLkWarps);
 #define FSB_LAUNCH_LK(T, KT, LT)                                                                                   \
   do {                                                                                                             \
-    auto kern = lookup_nhwc_kernel<T, KT, LT>;                                                                     \
+    auto kern = Cg == 28 ? lookup_nhwc_kernel<T, KT, LT, 28> : lookup_nhwc_kernel<T, KT, LT, 0>;                                                                   \
     if (smem > 48 * 1024) {                                                                                        \
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);          \
       if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_lookup: cudaFuncSetAttribute");                           \
@@ -591,13 +576,24 @@ extern "C" int fsb_geo_lookup(float* const* geo_levels, float* const* corr_level
   FSB_REQUIRE((long long)B * H < 65536, FSB_ERR_SHAPE, "fsb_geo_lookup: B*H too large");
   const size_t smem = lookup_smem_bytes(Cg, r);
   FSB_REQUIRE(smem <= 227 * 1024, FSB_ERR_SHAPE, "fsb_geo_lookup: Cg=%d r=%d needs %zu B shared memory", Cg, r, smem);
-  if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(lookup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_lookup: cudaFuncSetAttribute");
-  }
   dim3 grid(ceil_div(W, kLkPix), B * H);
-  launch_kernel(lookup_kernel, dim3(grid), dim3(kLkThreads), smem, (cudaStream_t)stream, g, c, disp, coords, (float*)out, Cg, D, H, W,
-                                                                  W2, L, r);
+#define FSB_LAUNCH_LKN(KT)                                                                                         \
+  do {                                                                                                             \
+    auto kern = Cg == 28 ? lookup_nchw_kernel<KT, 28> : lookup_nchw_kernel<KT, 0>;                                 \
+    if (smem > 48 * 1024) {                                                                                        \
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);          \
+      if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_lookup: cudaFuncSetAttribute");                           \
+    }                                                                                                              \
+    launch_kernel(kern, dim3(grid), dim3(kLkThreads), smem, (cudaStream_t)stream, g, c, disp, coords, (float*)out, \
+                  Cg, D, H, W, W2, L, r);                                                                          \
+  } while (0)
+  switch (r) {
+    case 1: FSB_LAUNCH_LKN(3); break;
+    case 2: FSB_LAUNCH_LKN(5); break;
+    case 3: FSB_LAUNCH_LKN(7); break;
+    default: FSB_LAUNCH_LKN(9); break;
+  }
+#undef FSB_LAUNCH_LKN
   FSB_CHECK_LAUNCH("fsb_geo_lookup");
   return FSB_OK;
 }

@@ -12,14 +12,18 @@ from foundationstereo_b200 import ops, synthetic
 from foundationstereo_b200._lib import FSB_PREC_FP32
 
 B, C, H, W, D, L, r = 1, 128, 120, 160, 104, 2, 4
+B = int(sys.argv[2]) if len(sys.argv) > 2 else B
 x = synthetic.hot_path_inputs(B, C, H, W, D)
 d = {k: v.cuda() for k, v in x.items() if isinstance(v, torch.Tensor)}
 dx = torch.linspace(-r, r, 2 * r + 1).reshape(1, 1, -1, 1)
 coords = torch.arange(W, dtype=torch.float32, device="cuda").reshape(1, 1, W, 1).repeat(B, H, 1, 1)
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
+Cpad = (L * (2 * r + 1) * 29 + 63) // 64 * 64
+out16 = torch.zeros(B, H, W, Cpad, dtype=torch.float16, device="cuda")
 for _ in range(reps):
     ops.combined_volume(d["fl"], d["fr"], d["pl"], d["pr"], D, 8)
     geo = fsb.Combined_Geo_Encoding_Volume(d["fl"], d["fr"], d["volume"], num_levels=L, dx=dx)
     out = geo(d["disp"], coords)
+    geo.lookup_nhwc16(d["disp"], coords, out16)
 torch.cuda.synchronize()
 print("ok", out.shape, fsb.launch_count())
