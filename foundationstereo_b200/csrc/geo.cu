@@ -294,7 +294,7 @@ __device__ __forceinline__ float ref_unnormalised(float x, int n) {
 //            16-byte coalesced stores.
 // Channel groups beyond the first 32 (Cg + 1 > 32) are handled by repeating B/C per group.
 // =====================================================================================
-constexpr int kLkWarps = 8;
+constexpr int kLkWarps = 4;
 
 // Phases A + B for one level of one pixel (whole warp, see lookup_nhwc_kernel): returns this lane's
 // geo window v[0..K] (channel c of rows gbase .. gbase+K, zero outside [0, Dl)), this lane's correlation
@@ -328,7 +328,7 @@ __device__ __forceinline__ void lookup_level(const float* __restrict__ gl, const
 }
 
 template <typename T, int KT, int LT, int CGT>
-__global__ void __launch_bounds__(kLkWarps * 32, 5)
+__global__ void __launch_bounds__(kLkWarps * 32, 12)
 lookup_nhwc_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp, const float* __restrict__ coords,
                    T* __restrict__ out, int Cgrt, int D, int W2, int Lrt, int r, int Cpad, long long npix) {
   pdl_launch_dependents();  // the next kernel may start its prologue

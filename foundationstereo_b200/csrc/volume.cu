@@ -47,7 +47,7 @@ __device__ __forceinline__ void store_quad(T* o, const float4 v, int w, int W) {
 }
 
 template <typename T, bool VEC>
-__global__ void __launch_bounds__(kVolThreads)
+__global__ void __launch_bounds__(kVolThreads, 4)
 volume_kernel(const T* __restrict__ fl, const T* __restrict__ fr, const T* __restrict__ pl,
               const T* __restrict__ pr, T* __restrict__ gwc, T* __restrict__ cat, int C, int Cp, int G,
               int H, int W, int D, size_t gwc_bs, size_t cat_bs) {
@@ -55,9 +55,11 @@ volume_kernel(const T* __restrict__ fl, const T* __restrict__ fr, const T* __res
   pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ __align__(16) float smem[];
   const int tid = threadIdx.x;
-  const int b = blockIdx.x / H;
-  const int h = blockIdx.x - b * H;
-  const int unit = blockIdx.y;
+  // unit is the fastest grid index: the FMA-heavy correlation CTAs and the store-only concat CTAs of a row
+  // are co-resident on an SM, so the arithmetic of the former hides under the HBM writes of the latter
+  const int b = blockIdx.y / H;
+  const int h = blockIdx.y - b * H;
+  const int unit = blockIdx.x;
   const int Wp = (W + 3) & ~3;
   const int Dpad = ((D + 3) & ~3) + 4;
   const int RS = Dpad + Wp;  // row stride of an apron-padded row
@@ -234,7 +236,7 @@ static int launch_volume(const void* fl, const void* fr, const void* pl, const v
               "fsb_volume_gwc_concat: row of C/G=%d x W=%d with D=%d needs %zu B shared memory (> 227 KB)",
               cpg, W, D, smem);
   const int nchunk = cat ? ceil_div(Cp, kCatChunk) : 0;
-  dim3 grid(B * H, G + 2 * nchunk);
+  dim3 grid(G + 2 * nchunk, B * H);
   const size_t esz = sizeof(T);
   const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(gwc) % (4 * esz)) == 0) &&
                    ((reinterpret_cast<uintptr_t>(cat) % (4 * esz)) == 0);
@@ -261,7 +263,7 @@ static int volume_entry(const void* fl, const void* fr, const void* pl, const vo
   FSB_REQUIRE(B > 0 && H > 0 && W > 0 && D > 0, FSB_ERR_ARG, "%s: non-positive size B=%d H=%d W=%d D=%d", who, B, H, W, D);
   FSB_REQUIRE(!gwc || (G > 0 && C > 0 && C % G == 0), FSB_ERR_ARG, "%s: C=%d not divisible by G=%d", who, C, G);
   FSB_REQUIRE(!cat || Cp > 0, FSB_ERR_ARG, "%s: Cp=%d", who, Cp);
-  FSB_REQUIRE((long long)B * H < (1ll << 31) && G + 2 * ceil_div(Cp > 0 ? Cp : 1, kCatChunk) < 65536, FSB_ERR_SHAPE,
+  FSB_REQUIRE((long long)B * H < 65536 && G + 2 * ceil_div(Cp > 0 ? Cp : 1, kCatChunk) < 65536, FSB_ERR_SHAPE,
               "%s: grid too large", who);
   if (!gwc) G = 0;
   cudaStream_t s = (cudaStream_t)stream;
