@@ -40,6 +40,7 @@ namespace fsb {
 constexpr int kConvThreads = 352;  // 11 warps
 constexpr int kWarpB = 10;           // weight producer warp
 constexpr int kMaxSteps = 112;
+constexpr int kMaxRows = 512;                // output rows (padded Cout) whose bias a persistent CTA keeps in shared memory
 constexpr int kBM = 128;
 constexpr int kBK = 64;                      // 16-bit elements per K step (128 B)
 constexpr int kATileBytes = kBM * kBK * 2;   // 16 KB
@@ -57,6 +58,7 @@ struct alignas(64) ConvParams {
   int nsteps;
   int H, W, tiles_x, tiles_y, tw_log2;
   int BN, nacc, tmem_cols, stages, kper;
+  int nbuf, ntiles, ntiles_n;  // persistent tap kernel: TMEM accumulator buffers, work items, N tiles per pixel tile
   int SA, SB;  // halo kernel: activation / weight ring depths
   uint32_t idesc;
   int rows, Cout;
@@ -84,6 +86,9 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
@@ -275,7 +280,7 @@ __device__ __forceinline__ void store32f(float* dst, const float (&f)[32]) {
 template <typename T, int EPI>
 __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* bias_s, uint32_t taddr, bool valid,
                                               size_t pix, int b, int y, int x, int n0, int nt, int c_first,
-                                              int c_stride) {
+                                              int c_stride, int bstride) {
   if constexpr (EPI == FSB_EPI_GATE_ZR) {
     const int half = p.BN >> 1;
     const int cpa = p.BN >> 5;  // chunks per accumulator
@@ -283,7 +288,7 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* 
       const int a = ci / cpa, c = (ci - a * cpa) << 5;
       T* zb = reinterpret_cast<T*>(a == 0 ? p.z_l : p.z_s);
       T* rb = reinterpret_cast<T*>(a == 0 ? p.rh_l : p.rh_s);
-      const float* bias = bias_s + a * p.BN;
+      const float* bias = bias_s + a * bstride;
       {
         uint32_t v[32];
         tmem_ld32(taddr + a * p.BN + c, v);
@@ -330,7 +335,7 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* 
           const float2 zl2 = unpack2<T>(zlw[j >> 1]), zs2 = unpack2<T>(zsw[j >> 1]);
           const float zl = (j & 1) ? zl2.y : zl2.x, zs = (j & 1) ? zs2.y : zs2.x;
           const float ql = tanh_f(__uint_as_float(v0[8 * o + j]) + bias_s[c + 8 * o + j]);
-          const float qs = tanh_f(__uint_as_float(v1[8 * o + j]) + bias_s[p.BN + c + 8 * o + j]);
+          const float qs = tanh_f(__uint_as_float(v1[8 * o + j]) + bias_s[bstride + c + 8 * o + j]);
           const float hl = (1.f - zl) * h[j] + zl * ql;
           const float hs = (1.f - zs) * h[j] + zs * qs;
           h[j] = hs * att + hl * (1.f - att);
@@ -385,13 +390,22 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* 
 }
 
 // ------------------------------------------------------------------------------------ kernel
+// PERSISTENT: one CTA per SM walks the work list  tile = blockIdx.x, blockIdx.x + gridDim.x, ...  with
+// tile = m_tile * ntiles_n + n_tile (N fastest: the CTAs that run side by side read the same activation
+// boxes, which then come from L2 instead of HBM).  The shared-memory ring, its phases and the two
+// producers run straight through tile boundaries, and the accumulators are double-buffered in TMEM
+// (2 x nacc x block_n columns): while the eight epilogue warps drain buffer i & 1 the MMA warp is
+// already accumulating tile i + 1 into the other one.  Measured before this change (tools/conv_sweep.py):
+// a CTA that lives for one small-K tile spends ~15k cycles on launch, TMEM allocation, pipeline fill and
+// a serial epilogue around 512 cycles of MMA, and the GRU q gate lost 45 % of its time to an epilogue
+// nothing overlapped.
 template <typename T, int EPI>
-__global__ void __launch_bounds__(kConvThreads, 2)
+__global__ void __launch_bounds__(kConvThreads, 1)
 conv_umma_kernel(const __grid_constant__ ConvParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  __shared__ __align__(8) uint64_t bars[2 * 8 + 1];
+  __shared__ __align__(8) uint64_t bars[2 * 8 + 4];
   __shared__ uint32_t tmem_slot;
-  __shared__ __align__(16) float bias_s[2 * 256];  // [nacc][BN] bias of this CTA's output channels
+  __shared__ __align__(16) float bias_s[2 * kMaxRows];  // [nacc][rows]
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);  // warp-uniform for the compiler
   const int lane = threadIdx.x & 31;
@@ -403,25 +417,22 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
   const int S = p.stages;
   const uint32_t bar_full = smem_u32(&bars[0]);
   const uint32_t bar_empty = smem_u32(&bars[8]);
-  const uint32_t bar_accum = smem_u32(&bars[16]);
-
-  // tile coordinates
-  int t = blockIdx.x;
-  const int txi = t % p.tiles_x;
-  t /= p.tiles_x;
-  const int tyi = t % p.tiles_y;
-  const int b = t / p.tiles_y;
+  const uint32_t bar_tfull = smem_u32(&bars[16]);   // [2] accumulator buffer complete (MMA -> epilogue)
+  const uint32_t bar_tempty = smem_u32(&bars[18]);  // [2] accumulator buffer drained (epilogue -> MMA)
+  const int nbuf = p.nbuf;
+  const uint32_t buf_cols = (uint32_t)(p.nacc * p.BN);
   const int TW = 1 << p.tw_log2, TH = kBM >> p.tw_log2;
-  const int x0 = txi * TW, y0 = tyi * TH;
-  const int nt = blockIdx.y;
-  const int n0 = nt * p.BN;
+  const int ntn = p.ntiles_n, ntiles = p.ntiles;
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < S; ++s) {
       mbar_init(bar_full + 8 * s, 2);   // one expect_tx arrival from each producer
       mbar_init(bar_empty + 8 * s, 1);
     }
-    mbar_init(bar_accum, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar_tfull + 8 * i, 1);
+      mbar_init(bar_tempty + 8 * i, 8);  // one arrival per epilogue warp
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     tma_prefetch_desc(&p.amap[0]);
   }
@@ -433,10 +444,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   if (warp >= 2 && warp < kWarpB) {
-    for (int i = threadIdx.x - 64; i < p.nacc * p.BN; i += 256) {
-      const int a = i / p.BN, c = i - a * p.BN;
-      bias_s[i] = __ldg(p.bias + (size_t)a * p.rows + n0 + c);
-    }
+    for (int i = threadIdx.x - 64; i < p.nacc * p.rows; i += 256) bias_s[i] = __ldg(p.bias + i);
   }
   tc_fence_before();
   __syncthreads();
@@ -451,75 +459,94 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
     // ================================================== TMA producer: activation tiles
     int s = 0;
     uint32_t ph = 0;
-    for (int i = 0; i < p.nsteps; i += kper) {
-      const int n = min(kper, p.nsteps - i);
-      if (i >= S * kper) mbar_wait(bar_empty + 8 * s, ph ^ 1);
-      __syncwarp();
-      if (elect_one()) {
-        const uint32_t full = bar_full + 8 * s;
-        uint32_t dst = smem_base + s * stage_bytes;
-        mbar_expect_tx(full, (uint32_t)n * kATileBytes);
-        for (int j = 0; j < n; ++j) {
-          const uint32_t st = p.steps[i + j];
-          const int src = st & 3, dy = (int)((st >> 2) & 3) - 1, dx = (int)((st >> 4) & 3) - 1, chunk = (st >> 8) & 0xff;
-          tma_load_4d(dst, &p.amap[src], full, chunk * kBK, x0 + dx, y0 + dy, b);
-          dst += kATileBytes;
+    bool first_round = true;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const int mtile = tile / ntn;
+      const int txi = mtile % p.tiles_x, r1 = mtile / p.tiles_x;
+      const int tyi = r1 % p.tiles_y, b = r1 / p.tiles_y;
+      const int x0 = txi * TW, y0 = tyi * TH;
+      for (int i = 0; i < p.nsteps; i += kper) {
+        const int n = min(kper, p.nsteps - i);
+        if (!first_round) mbar_wait(bar_empty + 8 * s, ph ^ 1);
+        __syncwarp();
+        if (elect_one()) {
+          const uint32_t full = bar_full + 8 * s;
+          uint32_t dst = smem_base + s * stage_bytes;
+          mbar_expect_tx(full, (uint32_t)n * kATileBytes);
+          for (int j = 0; j < n; ++j) {
+            const uint32_t st = p.steps[i + j];
+            const int src = st & 3, dy = (int)((st >> 2) & 3) - 1, dx = (int)((st >> 4) & 3) - 1, chunk = (st >> 8) & 0xff;
+            tma_load_4d(dst, &p.amap[src], full, chunk * kBK, x0 + dx, y0 + dy, b);
+            dst += kATileBytes;
+          }
         }
+        if (++s == S) { s = 0; ph ^= 1; first_round = false; }
       }
-      if (++s == S) { s = 0; ph ^= 1; }
     }
   } else if (warp == kWarpB) {
     // ====================================================== TMA producer: weight tiles
     int s = 0;
     uint32_t ph = 0;
-    for (int i = 0; i < p.nsteps; i += kper) {
-      const int n = min(kper, p.nsteps - i);
-      if (i >= S * kper) mbar_wait(bar_empty + 8 * s, ph ^ 1);
-      __syncwarp();
-      if (elect_one()) {
-        const uint32_t full = bar_full + 8 * s;
-        uint32_t dst = smem_base + s * stage_bytes + a_stage_bytes;
-        mbar_expect_tx(full, (uint32_t)n * b_tile_bytes);
-        for (int j = 0; j < n; ++j) {
-          tma_load_2d(dst, &p.wmap, full, (i + j) * kBK, n0);
-          dst += b_tile_bytes;
+    bool first_round = true;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+      const int n0 = (tile % ntn) * p.BN;
+      for (int i = 0; i < p.nsteps; i += kper) {
+        const int n = min(kper, p.nsteps - i);
+        if (!first_round) mbar_wait(bar_empty + 8 * s, ph ^ 1);
+        __syncwarp();
+        if (elect_one()) {
+          const uint32_t full = bar_full + 8 * s;
+          uint32_t dst = smem_base + s * stage_bytes + a_stage_bytes;
+          mbar_expect_tx(full, (uint32_t)n * b_tile_bytes);
+          for (int j = 0; j < n; ++j) {
+            tma_load_2d(dst, &p.wmap, full, (i + j) * kBK, n0);
+            dst += b_tile_bytes;
+          }
         }
+        if (++s == S) { s = 0; ph ^= 1; first_round = false; }
       }
-      if (++s == S) { s = 0; ph ^= 1; }
     }
   } else if (warp == 1) {
     // ====================================================================== MMA issuer
-    uint32_t started = 0;  // bit a: accumulator a already holds a partial sum
     int s = 0;
     uint32_t ph = 0;
     const uint32_t idesc = p.idesc;
-    for (int i = 0; i < p.nsteps; i += kper) {
-      const int n = min(kper, p.nsteps - i);
-      mbar_wait(bar_full + 8 * s, ph);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const int buf = nbuf == 2 ? (it & 1) : 0;
+      const uint32_t use = (uint32_t)(nbuf == 2 ? (it >> 1) : it);  // how often this buffer was used before
+      mbar_wait(bar_tempty + 8 * buf, (use & 1) ^ 1);                // drained by the epilogue (passes at first use)
       tc_fence_after();
-      __syncwarp();
-      const uint32_t a_addr = smem_base + s * stage_bytes;
-      uint64_t adesc = umma_desc_k128(a_addr);
-      uint64_t bdesc = umma_desc_k128(a_addr + a_stage_bytes);
-      for (int j = 0; j < n; ++j) {
-        const int acc = (p.steps[i + j] >> 6) & 1;
-        const uint32_t d = tmem_base + (uint32_t)(acc * p.BN);
-        const uint32_t first = (started >> acc) & 1;
-        if (elect_one()) {
-          // +32 B along K inside the swizzle atom = +2 in the (addr >> 4) field
-          umma_f16(d, adesc, bdesc, idesc, first);
-          umma_f16(d, adesc + 2, bdesc + 2, idesc, 1);
-          umma_f16(d, adesc + 4, bdesc + 4, idesc, 1);
-          umma_f16(d, adesc + 6, bdesc + 6, idesc, 1);
+      const uint32_t d_base = tmem_base + (uint32_t)buf * buf_cols;
+      uint32_t started = 0;  // bit a: accumulator a already holds a partial sum
+      for (int i = 0; i < p.nsteps; i += kper) {
+        const int n = min(kper, p.nsteps - i);
+        mbar_wait(bar_full + 8 * s, ph);
+        tc_fence_after();
+        __syncwarp();
+        const uint32_t a_addr = smem_base + s * stage_bytes;
+        uint64_t adesc = umma_desc_k128(a_addr);
+        uint64_t bdesc = umma_desc_k128(a_addr + a_stage_bytes);
+        for (int j = 0; j < n; ++j) {
+          const int acc = (p.steps[i + j] >> 6) & 1;
+          const uint32_t d = d_base + (uint32_t)(acc * p.BN);
+          const uint32_t first = (started >> acc) & 1;
+          if (elect_one()) {
+            // +32 B along K inside the swizzle atom = +2 in the (addr >> 4) field
+            umma_f16(d, adesc, bdesc, idesc, first);
+            umma_f16(d, adesc + 2, bdesc + 2, idesc, 1);
+            umma_f16(d, adesc + 4, bdesc + 4, idesc, 1);
+            umma_f16(d, adesc + 6, bdesc + 6, idesc, 1);
+          }
+          started |= 1u << acc;
+          adesc += kATileBytes >> 4;
+          bdesc += b_tile_bytes >> 4;
         }
-        started |= 1u << acc;
-        adesc += kATileBytes >> 4;
-        bdesc += b_tile_bytes >> 4;
+        if (elect_one()) umma_commit(bar_empty + 8 * s);  // frees the stage when these MMAs have read it
+        if (++s == S) { s = 0; ph ^= 1; }
       }
-      if (elect_one()) umma_commit(bar_empty + 8 * s);  // frees the stage when these MMAs have read it
-      if (++s == S) { s = 0; ph ^= 1; }
+      if (elect_one()) umma_commit(bar_tfull + 8 * buf);  // all MMAs of the tile done -> accumulators complete
     }
-    if (elect_one()) umma_commit(bar_accum);  // all MMAs done -> accumulators complete
   } else if (warp < kWarpB) {
     // ======================================================================== epilogue
     // 8 warps: warp w reads TMEM lane quarter (w & 3); the two warps of a quarter split the
@@ -529,16 +556,26 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
     const int grp = (warp - 2) >> 2;
     const int r = q * 32 + lane;
     const int ty = r >> p.tw_log2, tx = r & (TW - 1);
-    const int y = y0 + ty, x = x0 + tx;
-    const bool valid = (y < p.H) && (x < p.W);
-    const size_t pix = valid ? ((size_t)b * p.H + y) * p.W + x : 0;
-    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    int it = 0;
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+      const int mtile = tile / ntn, nt = tile - mtile * ntn;
+      const int txi = mtile % p.tiles_x, r1 = mtile / p.tiles_x;
+      const int tyi = r1 % p.tiles_y, b = r1 / p.tiles_y;
+      const int y = tyi * TH + ty, x = txi * TW + tx;
+      const bool valid = (y < p.H) && (x < p.W);
+      const size_t pix = valid ? ((size_t)b * p.H + y) * p.W + x : 0;
+      const int buf = nbuf == 2 ? (it & 1) : 0;
+      const uint32_t use = (uint32_t)(nbuf == 2 ? (it >> 1) : it);
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * buf_cols;
+      const int n0 = nt * p.BN;
 
-    mbar_wait(bar_accum, 0);
-    tc_fence_after();
-
-    conv_epilogue<T, EPI>(p, bias_s, taddr, valid, pix, b, y, x, n0, nt, grp, 2);
-    tc_fence_before();
+      mbar_wait(bar_tfull + 8 * buf, use & 1);
+      tc_fence_after();
+      conv_epilogue<T, EPI>(p, bias_s + n0, taddr, valid, pix, b, y, x, n0, nt, grp, 2, p.rows);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+    }
   }
   __syncwarp();
   __syncthreads();
@@ -707,7 +744,7 @@ conv_halo_kernel(const __grid_constant__ ConvParams p) {
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(mt * p.nacc * p.BN);
     mbar_wait(bar_accum, 0);
     tc_fence_after();
-    if (mt < nmt) conv_epilogue<T, EPI>(p, bias_s, taddr, valid, pix, b, y, x, n0, nt, 0, 1);
+    if (mt < nmt) conv_epilogue<T, EPI>(p, bias_s, taddr, valid, pix, b, y, x, n0, nt, 0, 1, p.BN);
     tc_fence_before();
   }
   __syncwarp();
@@ -734,6 +771,16 @@ static EncodeTiledFn encode_fn() {
     return reinterpret_cast<EncodeTiledFn>(f);
   }();
   return fn;
+}
+
+static int sm_count() {
+  static int n = [] {
+    int dev = 0, v = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0)
+      v = 148;
+    return v;
+  }();
+  return n;
 }
 
 static int pick_tile(int H, int W, int* tw_log2) {
@@ -847,9 +894,14 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   p.tw_log2 = tw_log2;
   p.BN = BN;
   p.nacc = a->nseg;
+  // tap kernel: two accumulator buffers when they fit the 512 TMEM columns (epilogue of tile i overlaps the MMAs of
+  // tile i + 1); halo kernel: two stacked pixel tiles
+  p.nbuf = (!halo && 2 * a->nseg * BN <= 512) ? 2 : 1;
   int cols = 32;
-  while (cols < (halo ? 2 : 1) * a->nseg * BN) cols <<= 1;
+  while (cols < (halo ? 2 : p.nbuf) * a->nseg * BN) cols <<= 1;
   p.tmem_cols = cols;
+  FSB_REQUIRE(halo || a->nseg * a->rows <= 2 * kMaxRows, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: %d x %d bias values exceed %d",
+              a->nseg, a->rows, 2 * kMaxRows);
 
   // K-step program + Ktot
   int n = 0;
@@ -886,25 +938,15 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   p.nsteps = n;
   const int Ktot = n * kBK;
 
-  // Pipeline shape.  A grid that fits the machine in one wave (<= 148 CTAs) streams its K loop
-  // alone on an SM: it gets stages of 2 (4 for narrow tiles) K steps, as many as shared memory
-  // holds, so each producer pays one mbarrier round per 2-4 loads.  Larger grids keep two CTAs
-  // per SM (<= 108 KB each: one CTA's epilogue overlaps the other's MMAs, and four producer
-  // threads per SM); tiles too big for that (block_n 256) run one CTA per SM.
+  // Pipeline shape of the persistent tap kernel: one CTA per SM owns ~200 KB of shared memory; a stage holds
+  // two K steps for N tiles up to 128 (each producer pays one mbarrier round per two loads), one above.
   const size_t step_bytes = (size_t)kATileBytes + (size_t)BN * kBK * 2;
-  const long long n_ctas = (long long)ceil_div(a->W, TW) * ceil_div(a->H, TH) * a->B * (a->rows / BN);
-  int kper = 1, stages = a->stages;
-  if (n_ctas <= 148 || 2 * step_bytes + 1024 > 108 * 1024) {
-    kper = (BN <= 64) ? 4 : 2;
-    while (kper > 1 && (kper > n || 2 * kper * step_bytes + 1024 > 220 * 1024)) kper >>= 1;
-    if (stages <= 0) stages = (int)((220 * 1024 - 1024) / (kper * step_bytes));
-  } else if (stages <= 0) {
-    stages = (int)((108 * 1024 - 1024) / step_bytes);
-  }
+  int kper = BN <= 128 ? 2 : 1, stages = a->stages;
+  if (kper > n) kper = n;
+  const size_t ring_budget = 200 * 1024;
+  if (stages <= 0) stages = (int)(ring_budget / (kper * step_bytes));
   if (stages > 8) stages = 8;
-  while (stages > 1 && stages * kper * step_bytes + 1024 > 220 * 1024) --stages;
-  const int nstage_iters = ceil_div(n, kper);
-  if (stages > nstage_iters) stages = nstage_iters;
+  while (stages > 1 && stages * kper * step_bytes > ring_budget) --stages;
   if (stages < 1) stages = 1;
   p.stages = stages;
   p.kper = kper;
@@ -971,8 +1013,11 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return cuda_fail(e, "fsb_conv2d_nhwc: cudaFuncSetAttribute");
   const long long mtiles = (long long)p.tiles_x * p.tiles_y * a->B;
-  FSB_REQUIRE(mtiles < (1ll << 31) && a->rows / BN < 65536, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: grid too large");
+  FSB_REQUIRE(mtiles * (a->rows / BN) < (1ll << 31) && a->rows / BN < 65536, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: grid too large");
+  p.ntiles_n = a->rows / BN;
+  p.ntiles = (int)(mtiles * p.ntiles_n);
   dim3 grid((unsigned)mtiles, (unsigned)(a->rows / BN));
+  if (!halo) grid = dim3((unsigned)(p.ntiles < sm_count() ? p.ntiles : sm_count()), 1);
   launch_kernel(kern, dim3(grid), dim3(kConvThreads), smem, (cudaStream_t)stream, p);
   FSB_CHECK_LAUNCH("fsb_conv2d_nhwc");
   return FSB_OK;

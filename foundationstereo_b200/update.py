@@ -24,9 +24,9 @@ Tensor = torch.Tensor
 
 # output channels per CTA of each layer (tuning table; values must divide the padded row count)
 DEFAULT_BLOCK_N = {
-    "conv0": 128, "conv1": 128, "zr": 128, "q": 64,
-    "convc1": 128, "convc2": 128, "convd2": 64, "enc_conv": 64,
-    "head0": 64, "pw1": 128, "pw2": 64, "head4": 16, "mask0": 32, "mask2": 32,
+    "conv0": 128, "conv1": 128, "zr": 128, "q": 128,
+    "convc1": 128, "convc2": 128, "convd2": 64, "enc_conv": 128,
+    "head0": 128, "pw1": 128, "pw2": 128, "head4": 16, "mask0": 64, "mask2": 32,
     # the coarse levels have few pixel tiles (10 at 30x40, 40 at 60x80): narrower N tiles put
     # more CTAs on the 148 SMs (the K loop of a CTA is serial)
     "gru16.conv0": 32, "gru16.conv1": 32, "gru16.zr": 64, "gru16.q": 32,
