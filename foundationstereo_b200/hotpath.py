@@ -53,3 +53,57 @@ class StereoHotPath:
         geo = Combined_Geo_Encoding_Volume(fl.float(), fr.float(), volume, num_levels=self.L, dx=self.dx, workspace=ws)
         disp, mask, _ = self.update_block.refine(geo, net, inp, att, disp, iters)
         return disp, mask, comb
+
+    # ---- host-resident inputs: double-buffered upload -----------------------------------------------
+    @torch.no_grad()
+    def run_pinned(self, batches, iters: int, out_host: Sequence[Tensor] | None = None) -> List[Tensor]:
+        """Runs a sequence of batches whose inputs live in PINNED HOST memory (dicts with the keys of
+        `run`: fl, fr, pl, pr, volume, disp, net, inp, att) and returns the final disparities in pinned
+        host tensors.  Every batch is copied host->device on a copy stream into one of two static
+        device slots while the previous batch computes (the 0.54 GB of inputs per pair take longer over
+        PCIe than a third of the compute, so a serial copy costs 25 % of the throughput); the result
+        goes device->host asynchronously.  Synchronises once, at the end."""
+        batches = list(batches)
+        if not batches:
+            return []
+        main = torch.cuda.current_stream(self.device)
+        if not hasattr(self, "_copy"):
+            self._copy = torch.cuda.Stream(self.device)
+            self._slots = {}
+        flat = lambda d: [t for k in ("fl", "fr", "pl", "pr", "volume", "disp") for t in (d[k],)] + \
+            list(d["net"]) + list(d["inp"]) + list(d["att"])
+        sig = tuple((tuple(t.shape), t.dtype) for t in flat(batches[0]))
+        if sig not in self._slots:
+            self._slots[sig] = [[torch.empty(t.shape, dtype=t.dtype, device=self.device) for t in flat(batches[0])]
+                                for _ in range(2)]
+        slots = self._slots[sig]
+        ready = [torch.cuda.Event() for _ in range(2)]
+        done = [torch.cuda.Event() for _ in range(2)]
+
+        def upload(i: int) -> None:
+            s = i & 1
+            with torch.cuda.stream(self._copy):
+                if i >= 2:
+                    self._copy.wait_event(done[s])  # batch i-2 no longer reads the slot
+                else:
+                    self._copy.wait_stream(main)
+                for dst, src in zip(slots[s], flat(batches[i])):
+                    assert src.is_pinned(), "run_pinned takes pinned host tensors"
+                    dst.copy_(src, non_blocking=True)
+                ready[s].record(self._copy)
+
+        outs: List[Tensor] = []
+        upload(0)
+        for i in range(len(batches)):
+            s = i & 1
+            main.wait_event(ready[s])
+            if i + 1 < len(batches):
+                upload(i + 1)
+            t = slots[s]
+            disp, _, _ = self.run(t[0], t[1], t[2], t[3], t[4], t[5], t[6:9], t[9:12], t[12:15], iters)
+            done[s].record(main)
+            dst = out_host[i] if out_host is not None else torch.empty(disp.shape, dtype=disp.dtype).pin_memory()
+            dst.copy_(disp, non_blocking=True)
+            outs.append(dst)
+        main.synchronize()
+        return outs

@@ -246,7 +246,7 @@ class SelectiveUpdateBlock:
         plan.mask = torch.empty(B, 32, H, W, dtype=torch.float32, device=dev)
         plan.corr16 = torch.zeros(B, H, W, self.planes_pad, dtype=dt, device=dev)
         plan.coords = torch.arange(W, dtype=torch.float32, device=dev).reshape(1, 1, W, 1).repeat(B, H, 1, 1)
-        plan.src_key = [None] * 3  # (data_ptr, version) of the inp/att tensors last converted
+        plan.src_key = [None] * 3  # (tensor, version) of the inp/att tensors last converted
         add = plan.add
 
         # encoder (core/update.py:62-70): motion = [conv(cat[cor, d]) (127) | disp (1)]  -- side lane
@@ -319,8 +319,12 @@ class SelectiveUpdateBlock:
             n = net[l]
             if not self._is_view_of(n, plan.h32[l]):
                 C.nchw_to_nhwc(n.float().contiguous(), plan.h16[l], plan.h32[l])
-            key = (inp[l].data_ptr(), inp[l]._version, att[l].data_ptr(), att[l]._version)
-            if plan.src_key[l] != key:
+            # the context tensors are converted once and reused while the caller passes the SAME tensor objects,
+            # unmodified (the reference loop does).  The key holds the tensors themselves: an address alone can be
+            # recycled by the caching allocator for another batch's data.
+            key = (inp[l], inp[l]._version, att[l], att[l]._version)
+            old = plan.src_key[l]
+            if old is None or old[0] is not key[0] or old[2] is not key[2] or old[1] != key[1] or old[3] != key[3]:
                 C.nchw_to_nhwc(inp[l].float().contiguous(), plan.inp16[l], None)
                 plan.att[l].copy_(att[l].reshape(plan.att[l].shape))
                 plan.src_key[l] = key

@@ -240,6 +240,33 @@ def test_hot_path_refinement_loop(fsb):
     assert mad <= 0.05, mad
 
 
+@pytest.mark.gpu
+def test_run_pinned_matches_run(fsb):
+    """StereoHotPath.run_pinned (double-buffered host->device upload, async result download) returns, batch by
+    batch, exactly what run() returns on the same inputs -- also when consecutive batches differ."""
+    H, W, D, iters = 16, 24, 12, 3
+    p = oracle.make_update_block_params(seed=2, delta_scale=0.25)
+    hp = fsb.StereoHotPath(p, max_disp=4 * D)
+    batches, want = [], []
+    for seed in (4, 5, 6):
+        x = oracle.make_inputs(B=2, C=32, H=H, W=W, D=D, Cg=28, seed=seed)
+        c = lambda t: t.cuda()
+        got, _, _ = hp.run(c(x["fl"]), c(x["fr"]), c(x["pl"]), c(x["pr"]), c(x["volume"]), c(x["disp"]),
+                           [c(t) for t in x["net"]], [c(t) for t in x["inp"]], [c(t) for t in x["att"]], iters)
+        want.append(got.cpu())
+        batches.append({k: ([t.contiguous().pin_memory() for t in v] if isinstance(v, list) else v.contiguous().pin_memory())
+                        for k, v in x.items() if k in ("fl", "fr", "pl", "pr", "volume", "disp", "net", "inp", "att")})
+    # run() must not depend on what ran before it (a recycled device address once matched a stale context cache)
+    x = oracle.make_inputs(B=2, C=32, H=H, W=W, D=D, Cg=28, seed=4)
+    again, _, _ = hp.run(c(x["fl"]), c(x["fr"]), c(x["pl"]), c(x["pr"]), c(x["volume"]), c(x["disp"]),
+                         [c(t) for t in x["net"]], [c(t) for t in x["inp"]], [c(t) for t in x["att"]], iters)
+    assert torch.equal(again.cpu(), want[0])
+    outs = hp.run_pinned(batches, iters)
+    assert len(outs) == 3
+    for o, w in zip(outs, want):
+        assert o.is_pinned() and torch.equal(o, w)
+
+
 # ------------------------------------------------------------- fused lookup output / fused loop
 @pytest.mark.parametrize("cfg", [
     # B, H, W, D, Cg, L, r, dtype

@@ -40,27 +40,24 @@ def run(name, cins, cout, k, bn, layout, reps=20, stages=0):
 
 
 TAP, HALO = _lib.FSB_CONV_LAYOUT_TAP, _lib.FSB_CONV_LAYOUT_HALO
-for bn in (64, 128, 256):
-    run("3x3 512->128", [128, 384], 128, 3, min(bn, 128), TAP) if bn <= 128 else None
-for bn in (128, 256):
-    run("3x3 512->512", [384, 128], 512, 3, bn, TAP)
-    run("3x3 512->512", [384, 128], 512, 3, bn, HALO)
-run("3x3 512->128", [128, 384], 128, 3, 128, HALO)
-run("3x3 512->256", [512], 256, 3, 128, TAP)
-run("3x3 512->256", [512], 256, 3, 128, HALO)
-run("3x3 512->256", [512], 256, 3, 256, HALO)
-run("3x3 256->256", [256], 256, 3, 128, TAP)
-run("3x3 256->256", [256], 256, 3, 256, TAP)
-run("3x3 256->256", [256], 256, 3, 128, HALO)
-run("3x3 256->256", [256], 256, 3, 256, HALO)
-run("3x3 320->128", [256, 64], 128, 3, 64, TAP)
-run("3x3 320->128", [256, 64], 128, 3, 128, TAP)
-run("3x3 320->128", [256, 64], 128, 3, 128, HALO)
-run("3x3 128->128", [128], 128, 3, 64, TAP)
-run("3x3 128->128", [128], 128, 3, 128, TAP)
-run("3x3 128->128", [128], 128, 3, 128, HALO)
-run("1x1 576->256", [576], 256, 1, 128, TAP)
-run("1x1 576->256", [576], 256, 1, 256, TAP)
-run("1x1 128->512", [128], 512, 1, 128, TAP)
-run("1x1 512->128", [512], 128, 1, 64, TAP)
-run("1x1 512->128", [512], 128, 1, 128, TAP)
+only = os.environ.get("SWEEP_ONLY")  # substring filter on "name bn"
+CFG = [
+    ("3x3 512->128", [128, 384], 128, 3, 64, TAP), ("3x3 512->128", [128, 384], 128, 3, 128, TAP),
+    ("3x3 512->128", [128, 384], 128, 3, 128, HALO),
+    ("3x3 512->512", [384, 128], 512, 3, 128, TAP), ("3x3 512->512", [384, 128], 512, 3, 256, TAP),
+    ("3x3 512->512", [384, 128], 512, 3, 256, HALO),
+    ("3x3 384->384", [128, 128, 128], 384, 3, 128, TAP), ("3x3 384->384", [128, 128, 128], 384, 3, 192, TAP),
+    ("3x3 384->384", [128, 128, 128], 384, 3, 192, HALO),
+    ("3x3 512->256", [512], 256, 3, 128, TAP), ("3x3 512->256", [512], 256, 3, 256, TAP),
+    ("3x3 256->256", [256], 256, 3, 128, TAP), ("3x3 256->256", [256], 256, 3, 256, TAP),
+    ("3x3 320->128", [256, 64], 128, 3, 64, TAP), ("3x3 320->128", [256, 64], 128, 3, 128, TAP),
+    ("3x3 128->128", [128], 128, 3, 64, TAP), ("3x3 128->128", [128], 128, 3, 128, TAP),
+    ("3x3 128->64", [128], 64, 3, 64, TAP), ("3x3 64->64", [64], 64, 3, 64, TAP),
+    ("1x1 576->256", [576], 256, 1, 128, TAP), ("1x1 576->256", [576], 256, 1, 256, TAP),
+    ("1x1 128->512", [128], 512, 1, 128, TAP), ("1x1 128->512", [128], 512, 1, 256, TAP),
+    ("1x1 512->128", [512], 128, 1, 64, TAP), ("1x1 512->128", [512], 128, 1, 128, TAP),
+]
+for name, cins, cout, k, bn, lay in CFG:
+    if only and only not in f"{name} bn{bn} lay{lay}":
+        continue
+    run(name, cins, cout, k, bn, lay, reps=int(os.environ.get("SWEEP_REPS", "20")))
