@@ -177,6 +177,17 @@ def dwconv7x7(x: Tensor, weight: Tensor, bias: Tensor, out: Tensor) -> None:
                                    _DT[x.dtype], _stream()))
 
 
+def edgenext_mlp(x: Tensor, w1: Tensor, b1: Tensor, w2: Tensor, b2: Tensor, gamma: Tensor, res: Tensor,
+                 out: Tensor) -> None:
+    """out = res + gamma * (GELU(x @ w1^T + b1) @ w2^T + b2) on 16-bit NHWC tensors (csrc/mlp.cu)."""
+    C, F = w1.shape[1], w1.shape[0]
+    assert x.is_contiguous() and res.is_contiguous() and out.is_contiguous() and x.shape == res.shape == out.shape
+    assert w1.is_contiguous() and w2.is_contiguous() and w2.shape == (C, F) and x.shape[-1] == C
+    assert x.dtype == w1.dtype == w2.dtype == res.dtype == out.dtype and b1.dtype == b2.dtype == gamma.dtype == torch.float32
+    check(lib().fsb_edgenext_mlp(x.data_ptr(), w1.data_ptr(), b1.data_ptr(), w2.data_ptr(), b2.data_ptr(), gamma.data_ptr(),
+                                 res.data_ptr(), out.data_ptr(), x.numel() // C, C, F, _DT[x.dtype], _stream()))
+
+
 def axpy(y: Tensor, x: Tensor) -> None:
     assert y.dtype == x.dtype == torch.float32 and y.numel() == x.numel()
     check(lib().fsb_axpy_f32(y.data_ptr(), x.data_ptr(), y.numel(), _stream()))

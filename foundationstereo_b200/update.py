@@ -89,7 +89,8 @@ class SelectiveUpdateBlock:
 
     def __init__(self, state_dict: Dict[str, Tensor], device: torch.device | str = "cuda",
                  dtype: torch.dtype = torch.float16, use_graph: bool = True,
-                 block_n: Optional[Dict[str, int]] = None, halo: Optional[Sequence[str]] = None):
+                 block_n: Optional[Dict[str, int]] = None, halo: Optional[Sequence[str]] = None,
+                 fused_mlp: bool = True):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("SelectiveUpdateBlock runs on CUDA only (no CPU path)")
@@ -97,6 +98,7 @@ class SelectiveUpdateBlock:
         assert dtype in (torch.float16, torch.bfloat16)
         self.dtype = dtype
         self.use_graph = use_graph
+        self.fused_mlp = fused_mlp  # False: pwconv1 / pwconv2 of the disparity head as two convolution launches
         self.bn = dict(DEFAULT_BLOCK_N)
         if block_n:
             self.bn.update(block_n)
@@ -189,6 +191,10 @@ class SelectiveUpdateBlock:
             self.f[f"dw{i}.w"] = sd[pre + ".dwconv.weight"].reshape(hd, 49).contiguous()
             self.f[f"dw{i}.b"] = sd[pre + ".dwconv.bias"].contiguous()
             self.f[f"gamma{i}"] = sd[pre + ".gamma"].contiguous()
+            self.f[f"pw1_{i}.w"] = sd[pre + ".pwconv1.weight"].to(self.dtype).contiguous()   # (4hd, hd), nn.Linear layout
+            self.f[f"pw1_{i}.b"] = sd[pre + ".pwconv1.bias"].contiguous()
+            self.f[f"pw2_{i}.w"] = sd[pre + ".pwconv2.weight"].to(self.dtype).contiguous()   # (hd, 4hd)
+            self.f[f"pw2_{i}.b"] = sd[pre + ".pwconv2.bias"].contiguous()
             self._put(f"pw1_{i}", pre + ".pwconv1", [(sd[pre + ".pwconv1.weight"], [(hd, hd)])],
                       [sd[pre + ".pwconv1.bias"]], 4 * hd, bn["pw1"])
             self._put(f"pw2_{i}", pre + ".pwconv2", [(sd[pre + ".pwconv2.weight"], [(4 * hd, 4 * hd)])],
@@ -289,6 +295,16 @@ class SelectiveUpdateBlock:
         for k, i in enumerate((2, 3)):
             add(f"disp_head.conv.{i}.dwconv",
                 lambda k=k, i=i: C.dwconv7x7(y[k], self.f[f"dw{i}.w"], self.f[f"dw{i}.b"], t))
+            if self.fused_mlp:
+                # pwconv1 -> GELU -> pwconv2 -> gamma * . + residual in one launch (csrc/mlp.cu): the 512-wide hidden
+                # activations never leave the SM
+                def mlp(k=k, i=i):
+                    C.edgenext_mlp(t, self.f[f"pw1_{i}.w"], self.f[f"pw1_{i}.b"], self.f[f"pw2_{i}.w"],
+                                   self.f[f"pw2_{i}.b"], self.f[f"gamma{i}"], y[k], y[k + 1])
+                mlp.flops = 2.0 * B * H * W * (2 * hd * 4 * hd)
+                add(f"disp_head.conv.{i}.mlp", mlp)
+                plan.flops += mlp.flops
+                continue
             self._conv(plan, f"disp_head.conv.{i}.pwconv1", f"pw1_{i}", [t], [(1, [0])], "pw1", _lib.FSB_EPI_GELU, out=u)
             self._conv(plan, f"disp_head.conv.{i}.pwconv2", f"pw2_{i}", [u], [(1, [0])], "pw2", _lib.FSB_EPI_SCALE_RES,
                        out=y[k + 1], res=y[k], gamma=self.f[f"gamma{i}"])

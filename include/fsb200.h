@@ -236,6 +236,14 @@ int fsb_conv7x7_c1(const float* disp, const float* weight, const float* bias, vo
  * x, out 16-bit NHWC (B,H,W,C); weight fp32 (C,49) */
 int fsb_dwconv7x7_nhwc(const void* x, const float* weight, const float* bias, void* out, int B, int C, int H, int W,
                        int dtype, fsb_stream_t stream);
+/* The pointwise MLP of one EdgeNextConvEncoder block (core/submodule.py:584-590, norm=None) in one launch:
+ *     out = res + gamma * (GELU(x @ w1^T + b1) @ w2^T + b2)
+ * x (the dwconv output), res (the block input), out: 16-bit NHWC flattened to (npix, C); w1 (F,C), w2 (C,F) 16-bit
+ * row-major (the nn.Linear weights as stored); b1 (F), b2 (C), gamma (C) fp32.  C = 128, F = 512 (dim 128,
+ * expan_ratio 4, core/update.py:27).  The 4C-wide hidden activations stay in shared memory / TMEM.        */
+int fsb_edgenext_mlp(const void* x, const void* w1, const float* b1, const void* w2, const float* b2,
+                     const float* gamma, const void* res, void* out, long long npix, int C, int F, int dtype,
+                     fsb_stream_t stream);
 /* y += x (fp32, n elements): the disparity update of core/foundation_stereo.py:242 */
 int fsb_axpy_f32(float* y, const float* x, size_t n, fsb_stream_t stream);
 

@@ -211,3 +211,43 @@ def test_conv7x7_helpers(fsb):
     xx = _rand(1000, seed=8).cuda()
     C.axpy(y, xx)
     assert torch.equal(y, y0 + xx)
+
+
+# ------------------------------------------------------------------ fused EdgeNeXt MLP (csrc/mlp.cu)
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("npix", [128, 300, 148 * 128 * 3 + 77])  # one tile, ragged, several tiles per persistent CTA
+def test_edgenext_mlp_vs_torch(fsb, dtype, npix):
+    """out = res + gamma * (GELU(x W1^T + b1) W2^T + b2) (core/submodule.py:584-590) against fp32 PyTorch on
+    the same 16-bit-rounded operands; the hidden activations are rounded to the 16-bit type in between, as the
+    reference's autocast Linear does."""
+    from foundationstereo_b200 import conv as Cv
+    C_, F_ = 128, 512
+    x = _rand(npix, C_, seed=1).to(dtype)
+    res = _rand(npix, C_, seed=2).to(dtype)
+    w1 = (_rand(F_, C_, seed=3) / C_ ** 0.5).to(dtype)
+    w2 = (_rand(C_, F_, seed=4) / F_ ** 0.5).to(dtype)
+    b1, b2, gamma = _rand(F_, seed=5) * 0.1, _rand(C_, seed=6) * 0.1, _rand(C_, seed=7)
+    h = F.gelu(x.float() @ w1.float().t() + b1).to(dtype).float()
+    want = res.float() + gamma * (h @ w2.float().t() + b2)
+    out = torch.empty(npix, C_, dtype=dtype, device="cuda")
+    c = lambda t: t.cuda()
+    Cv.edgenext_mlp(c(x), c(w1), c(b1), c(w2), c(b2), c(gamma), c(res), out)
+    torch.cuda.synchronize()
+    assert rel_err(out.float().cpu(), want) <= 2 * _tol(dtype)
+
+
+def test_update_block_fused_mlp_equals_two_launches(fsb):
+    """The engine with the fused MLP gives the same step as with pwconv1 / pwconv2 as separate convolutions (same
+    operands, same roundings: only the fp32 accumulation order inside the GEMMs may differ)."""
+    import oracle
+    p = oracle.make_update_block_params(seed=3)
+    x = oracle.make_inputs(B=1, C=16, H=24, W=40, D=8, Cg=28, seed=9)
+    c = lambda t: t.cuda()
+    outs = []
+    for fused in (True, False):
+        ub = fsb.SelectiveUpdateBlock(p, "cuda", use_graph=False, fused_mlp=fused)
+        corr = _rand(1, ub.planes, 24, 40, seed=5).cuda()
+        net, mask, delta = ub([c(t) for t in x["net"]], [c(t) for t in x["inp"]], corr, c(x["disp"]), [c(t) for t in x["att"]])
+        outs.append((delta.clone(), mask.clone()))
+    assert rel_err(outs[0][0].cpu(), outs[1][0].cpu()) <= 4e-3
+    assert torch.equal(outs[0][1], outs[1][1])
