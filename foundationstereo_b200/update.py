@@ -207,11 +207,45 @@ class SelectiveUpdateBlock:
     # ---- per-shape plan -------------------------------------------------------------------
     def _conv(self, plan: _Plan, name: str, wname: str, srcs, segs, bn_key: str, epilogue: int, **kw) -> None:
         lay, bn = plan.tile.get(name, (self._lay(name), self.bn.get(name, self.bn[bn_key])))
+        if name not in plan.tile and not self.fixed_tiles and lay == _lib.FSB_CONV_LAYOUT_TAP:
+            bn = self._pick_block_n(srcs, segs, self.spec[wname][3], epilogue, bn)
         w, b, cout = self._weights(wname, lay, bn)
         launch = ConvLaunch(srcs=srcs, segs=segs, weight=w, bias=b, cout=cout, block_n=bn, epilogue=epilogue, name=name,
                             layout=lay, **kw)
         plan.add(name, launch)
         plan.flops += launch.flops
+
+    @staticmethod
+    def _pick_block_n(srcs, segs, cout: int, epilogue: int, default: int, sms: int = 148) -> int:
+        """N tile of a persistent tap-layout launch from a cost model of csrc/conv.cu (cycles):
+             tile  = K steps x max(MMA 2*bn, operand feed (16 KB + 128*bn B) at ~80 B/cycle from L2) + pipeline fill
+             total = ceil(pixel tiles x N tiles / SMs) x tile
+        The pixel-tile counts of the three GRU levels (e.g. 38 / 160 / 600 at four 480x640 pairs) make the
+        number of rounds, not the tile shape, the first-order term on the coarse levels."""
+        B, H, W, _ = srcs[0].shape
+        mt = B * min(-(-W // (1 << l)) * -(-H // (128 >> l)) for l in range(2, 8))
+        nsteps = sum(k * k * sum(srcs[i].shape[3] // 64 for i in idx) for k, idx in segs)
+        nacc = len(segs)
+        if epilogue == _lib.FSB_EPI_GATE_ZR:
+            cand, rows_of = [64, 128, 256], lambda bn: 2 * cout // 2  # rows == 2 * hidden exactly
+        elif epilogue == _lib.FSB_EPI_GATE_Q:
+            cand, rows_of = [32, 64, 128], lambda bn: cout
+        else:
+            cand, rows_of = ([16] if cout <= 16 else []) + [32, 64, 96, 128, 192, 256], lambda bn: -(-cout // bn) * bn
+        best, best_t = default, None
+        for bn in cand:
+            rows = rows_of(bn)
+            if rows % bn or nacc * bn > 512 or nacc * rows > 1024:
+                continue
+            if epilogue == _lib.FSB_EPI_SCALE_RES and cout % 32:
+                continue
+            tile = nsteps * max(2 * bn, (16384 + 128 * bn) / 80.0) + 3000
+            if nacc * bn > 256:          # accumulators not double-buffered: the epilogue is exposed
+                tile += 60 * bn
+            t = -(-mt * (rows // bn) // sms) * tile
+            if best_t is None or t < best_t:
+                best, best_t = bn, t
+        return best
 
     def _gru(self, plan: _Plan, g: str, lvl: int, xs: Sequence[Tensor]) -> None:
         """SelectiveConvGRU.forward (core/update.py:112-119) on level `lvl`: 4 launches."""
