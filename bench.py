@@ -279,13 +279,13 @@ def run_b200(args):
     # ---- end to end: pinned host buffers in, disparity out, every step -------------------
     # (StereoHotPath.run_pinned: the upload of step i+1 runs on a copy stream while step i computes; every step's
     # inputs cross PCIe inside the timed region and every step's disparity comes back)
-    out_hosts = [torch.empty_like(out, device="cpu").pin_memory() for _ in range(args.steps)]
+    out_hosts = [torch.empty_like(out, device="cpu").pin_memory() for _ in range(max(args.steps, 2))]
     hp.run_pinned([host] * 2, c["iters"], out_hosts[:2])
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     te0 = time.perf_counter()
     f0.record()
-    hp.run_pinned([host] * args.steps, c["iters"], out_hosts)
+    hp.run_pinned([host] * args.steps, c["iters"], out_hosts[:args.steps])
     f1.record()
     barrier()
     te1 = time.perf_counter()
@@ -340,9 +340,12 @@ def run_b200(args):
                     "unit": "GB/s", "frac": kernels[top]["frac_of_measured_hbm"], "traffic": None,
                     "peak_source": peaks["source"] + " (MEASURED_PEAKS.json burst copy)", "kernels": kernels}
         traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(traffic_file):
+        if os.path.exists(traffic_file):  # DRAM bytes per launch from the committed ncu --set full captures
             with open(traffic_file) as fh:
-                roofline["traffic"] = json.load(fh).get(top)
+                tj = json.load(fh)
+            roofline["traffic"] = tj.get(top)
+            for k in kernels:
+                kernels[k]["traffic"] = tj.get(k)
 
         # ---- CPU baseline (oracle port) on the host cores, bounded sample --------------------
         threads = os.cpu_count() or 1

@@ -1,0 +1,45 @@
+#!/usr/bin/env python
+"""profiles/traffic.json from two `ncu --set full` captures (4 pairs per launch, as bench.py's default):
+    python tools/make_traffic.py <update-step capture .ncu-rep> <kernels 1-3 capture .ncu-rep>
+DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per launch; for the update block the sum over the
+tensor-core launches of ONE step (what bench.py's roofline.achieved is defined over)."""
+import csv
+import json
+import os
+import subprocess
+import sys
+
+
+def rows(rep):
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    r = list(csv.reader(raw.splitlines()))
+    hdr, units = r[0], r[1]
+    ix = {h: i for i, h in enumerate(hdr)}
+
+    def to_bytes(v, u):
+        v = float(v.replace(",", ""))
+        return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[u]
+    out = []
+    for x in r[2:]:
+        b = sum(to_bytes(x[ix[m]], units[ix[m]]) for m in ("dram__bytes_read.sum", "dram__bytes_write.sum"))
+        out.append((x[ix["Kernel Name"]], b, float(x[ix["gpu__time_duration.sum"]].replace(",", ""))))
+    return out
+
+
+step, k123 = rows(sys.argv[1]), rows(sys.argv[2])
+t = {}
+tensor = [(n, b) for n, b, _ in step if "conv_umma" in n or "conv_halo" in n or "edgenext_mlp" in n]
+t["conv_umma_kernel"] = sum(b for _, b in tensor)
+t["conv_umma_kernel_launches"] = len(tensor)
+names = {"volume_kernel": "volume_gwc_concat", "corr_umma": "corr_pyramid", "geo_pyramid": "geo_pyramid",
+         "lookup_nhwc": "geo_lookup", "lookup_nchw": "geo_lookup_fp32_nchw"}
+for n, b, _ in k123:
+    for k, v in names.items():
+        if k in n:
+            t[v] = b  # last launch of each kernel
+t["note"] = "bytes per launch at 4 pairs (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum); conv_umma_kernel = " \
+            "sum over the tensor-core launches of one update step"
+root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+with open(os.path.join(root, "profiles", "traffic.json"), "w") as fh:
+    json.dump(t, fh, indent=1)
+print(json.dumps(t, indent=1))
