@@ -196,65 +196,96 @@ template <> __device__ __forceinline__ float4 load4_f32<__nv_bfloat16>(const __n
   return make_float4(a.x, a.y, b.x, b.y);
 }
 
+// PERSISTENT: a CTA keeps the 49 x 64 weights of its channel group in shared memory and walks the pixel tiles
+// tile = blockIdx.x, blockIdx.x + gridDim.x, ...; the input patch of the NEXT tile streams in with cp.async
+// (zero fill outside the image) while the current one is computed -- as one-tile CTAs the kernel spent 40 % of
+// its stall samples waiting for the patch and re-read the weights per tile.
+__device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gsrc, bool valid) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  const int n = valid ? 16 : 0;
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "r"(n) : "memory");
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 dwconv7x7_kernel(const T* __restrict__ x, const float* __restrict__ weight, const float* __restrict__ bias,
-                 T* __restrict__ out, int C, int H, int W) {
+                 T* __restrict__ out, int C, int H, int W, int ntiles) {
   pdl_launch_dependents();  // the next kernel may start its prologue
-  pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ __align__(16) uint8_t dsm_raw[];
-  float* wsm = reinterpret_cast<float*>(dsm_raw);                      // [49][kDwC]
-  T* patch = reinterpret_cast<T*>(dsm_raw + 49 * kDwC * sizeof(float));  // [kDwPY][kDwPX][kDwC]
+  float* wsm = reinterpret_cast<float*>(dsm_raw);                        // [49][kDwC]
+  T* patch0 = reinterpret_cast<T*>(dsm_raw + 49 * kDwC * sizeof(float));  // 2 x [kDwPY][kDwPX][kDwC]
+  constexpr int kPatchElems = kDwPY * kDwPX * kDwC;
   const int tid = threadIdx.x;
-  const int tiles_x = (W + kDwTX - 1) / kDwTX;
-  const int tx0 = (blockIdx.x % tiles_x) * kDwTX, ty0 = (blockIdx.x / tiles_x) * kDwTY;
-  const int c0 = blockIdx.y * kDwC, b = blockIdx.z;
-  for (int i = tid; i < 49 * kDwC; i += 256) {
+  const int tiles_x = (W + kDwTX - 1) / kDwTX, tiles_y = (H + kDwTY - 1) / kDwTY;
+  const int c0 = blockIdx.y * kDwC;
+  for (int i = tid; i < 49 * kDwC; i += 256) {  // parameters: no kernel writes them, no need to wait
     const int c = i / 49, t = i - c * 49;
     wsm[t * kDwC + c] = weight[(size_t)(c0 + c) * 49 + t];
   }
-  // patch: 8 channels (16 bytes) per load, zero outside the image
-  for (int i = tid; i < kDwPY * kDwPX * (kDwC / 8); i += 256) {
-    const int c8 = i & (kDwC / 8 - 1), pp = i >> 3;
-    const int py = pp / kDwPX, px = pp - py * kDwPX;
-    const int yy = ty0 + py - 3, xx = tx0 + px - 3;
-    uint4 u = make_uint4(0u, 0u, 0u, 0u);
-    if (yy >= 0 && yy < H && xx >= 0 && xx < W)
-      u = *reinterpret_cast<const uint4*>(x + (((size_t)b * H + yy) * W + xx) * C + c0 + c8 * 8);
-    *reinterpret_cast<uint4*>(patch + pp * kDwC + c8 * 8) = u;
-  }
-  __syncthreads();
+  pdl_wait();  // inputs written by the previous kernel are complete and visible
+
+  auto prefetch = [&](int tile, T* patch) {
+    const int txi = tile % tiles_x, r1 = tile / tiles_x;
+    const int tx0 = txi * kDwTX, ty0 = (r1 % tiles_y) * kDwTY, b = r1 / tiles_y;
+    // 8 channels (16 bytes) per copy, zero outside the image
+    for (int i = tid; i < kDwPY * kDwPX * (kDwC / 8); i += 256) {
+      const int c8 = i & (kDwC / 8 - 1), pp = i >> 3;
+      const int py = pp / kDwPX, px = pp - py * kDwPX;
+      const int yy = ty0 + py - 3, xx = tx0 + px - 3;
+      const bool ok = yy >= 0 && yy < H && xx >= 0 && xx < W;
+      const T* src = x + (((size_t)b * H + (ok ? yy : 0)) * W + (ok ? xx : 0)) * C + c0 + c8 * 8;
+      cp_async16_zfill(patch + pp * kDwC + c8 * 8, src, ok);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
   const int cq = tid & 15, xs = (tid >> 4) & 1, row = tid >> 5;
-  const int y = ty0 + row, xb = tx0 + xs * kDwR;
-  float acc[kDwR][4];
-  {
-    const float4 bv = *reinterpret_cast<const float4*>(bias + c0 + cq * 4);
+  const float4 bv = *reinterpret_cast<const float4*>(bias + c0 + cq * 4);
+  int buf = 0;
+  if ((int)blockIdx.x < ntiles) prefetch(blockIdx.x, patch0);
+  for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, buf ^= 1) {
+    const T* patch = patch0 + buf * kPatchElems;
+    const int next = tile + gridDim.x;
+    // the other buffer was read by the previous iteration's compute, which ended with a __syncthreads
+    if (next < ntiles) {
+      prefetch(next, patch0 + (buf ^ 1) * kPatchElems);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    const int txi = tile % tiles_x, r1 = tile / tiles_x;
+    const int tx0 = txi * kDwTX, ty0 = (r1 % tiles_y) * kDwTY, b = r1 / tiles_y;
+    const int y = ty0 + row, xb = tx0 + xs * kDwR;
+    float acc[kDwR][4];
 #pragma unroll
     for (int j = 0; j < kDwR; ++j) { acc[j][0] = bv.x; acc[j][1] = bv.y; acc[j][2] = bv.z; acc[j][3] = bv.w; }
-  }
 #pragma unroll 1
-  for (int ky = 0; ky < 7; ++ky) {
-    float4 in[kDwR + 6];
-    const T* prow = patch + ((row + ky) * kDwPX + xs * kDwR) * kDwC + cq * 4;
+    for (int ky = 0; ky < 7; ++ky) {
+      float4 in[kDwR + 6];
+      const T* prow = patch + ((row + ky) * kDwPX + xs * kDwR) * kDwC + cq * 4;
 #pragma unroll
-    for (int j = 0; j < kDwR + 6; ++j) in[j] = load4_f32<T>(prow + j * kDwC);
+      for (int j = 0; j < kDwR + 6; ++j) in[j] = load4_f32<T>(prow + j * kDwC);
 #pragma unroll
-    for (int kx = 0; kx < 7; ++kx) {
-      const float4 w = *reinterpret_cast<const float4*>(wsm + (ky * 7 + kx) * kDwC + cq * 4);
+      for (int kx = 0; kx < 7; ++kx) {
+        const float4 w = *reinterpret_cast<const float4*>(wsm + (ky * 7 + kx) * kDwC + cq * 4);
 #pragma unroll
-      for (int j = 0; j < kDwR; ++j) {
-        acc[j][0] = fmaf(in[j + kx].x, w.x, acc[j][0]);
-        acc[j][1] = fmaf(in[j + kx].y, w.y, acc[j][1]);
-        acc[j][2] = fmaf(in[j + kx].z, w.z, acc[j][2]);
-        acc[j][3] = fmaf(in[j + kx].w, w.w, acc[j][3]);
+        for (int j = 0; j < kDwR; ++j) {
+          acc[j][0] = fmaf(in[j + kx].x, w.x, acc[j][0]);
+          acc[j][1] = fmaf(in[j + kx].y, w.y, acc[j][1]);
+          acc[j][2] = fmaf(in[j + kx].z, w.z, acc[j][2]);
+          acc[j][3] = fmaf(in[j + kx].w, w.w, acc[j][3]);
+        }
       }
     }
-  }
-  if (y >= H) return;
-  T* o = out + (((size_t)b * H + y) * W + xb) * C + c0 + cq * 4;
+    if (y < H) {
+      T* o = out + (((size_t)b * H + y) * W + xb) * C + c0 + cq * 4;
 #pragma unroll
-  for (int j = 0; j < kDwR; ++j)
-    if (xb + j < W) Quad<T>::store(o + (size_t)j * C, acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
+      for (int j = 0; j < kDwR; ++j)
+        if (xb + j < W) Quad<T>::store(o + (size_t)j * C, acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
+    }
+    __syncthreads();  // everyone is done with `patch` before the next iteration's prefetch overwrites it
+  }
 }
 
 __global__ void __launch_bounds__(256) axpy_kernel(float* __restrict__ y, const float* __restrict__ x, size_t n) {
@@ -354,18 +385,27 @@ extern "C" int fsb_dwconv7x7_nhwc(const void* x, const float* weight, const floa
   FSB_REQUIRE(x && weight && bias && out, FSB_ERR_ARG, "fsb_dwconv7x7_nhwc: NULL pointer");
   FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && is16(dtype), FSB_ERR_ARG, "fsb_dwconv7x7_nhwc: bad size or dtype");
   FSB_REQUIRE(C % kDwC == 0 && aligned16(x) && aligned16(out) && aligned16(bias), FSB_ERR_SHAPE, "fsb_dwconv7x7_nhwc: C=%d must be a multiple of %d", C, kDwC);
-  FSB_REQUIRE(B < 65536, FSB_ERR_SHAPE, "fsb_dwconv7x7_nhwc: grid too large");
-  const size_t smem = (size_t)49 * kDwC * sizeof(float) + (size_t)kDwPY * kDwPX * kDwC * 2;
-  dim3 grid(ceil_div(W, kDwTX) * ceil_div(H, kDwTY), C / kDwC, B);
+  const size_t smem = (size_t)49 * kDwC * sizeof(float) + (size_t)2 * kDwPY * kDwPX * kDwC * 2;
+  const long long ntiles = (long long)ceil_div(W, kDwTX) * ceil_div(H, kDwTY) * B;
+  FSB_REQUIRE(ntiles < (1ll << 31), FSB_ERR_SHAPE, "fsb_dwconv7x7_nhwc: too many tiles");
+  // two CTAs per SM (91 KB each); every channel group gets the whole machine
+  int sms = 0, dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+    sms = 148;
+  const int groups = C / kDwC;
+  long long per_group = (2ll * sms + groups - 1) / groups;
+  if (per_group > ntiles) per_group = ntiles;
+  dim3 grid((unsigned)per_group, (unsigned)groups);
   if (dtype == FSB_F16) {
     cudaError_t e = cudaFuncSetAttribute(dwconv7x7_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return cuda_fail(e, "fsb_dwconv7x7_nhwc: cudaFuncSetAttribute");
-    launch_kernel(dwconv7x7_kernel<__half>, dim3(grid), dim3(256), smem, (cudaStream_t)stream, (const __half*)x, weight, bias, (__half*)out, C, H, W);
+    launch_kernel(dwconv7x7_kernel<__half>, dim3(grid), dim3(256), smem, (cudaStream_t)stream, (const __half*)x, weight, bias, (__half*)out, C, H, W,
+                  (int)ntiles);
   } else {
     cudaError_t e = cudaFuncSetAttribute(dwconv7x7_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return cuda_fail(e, "fsb_dwconv7x7_nhwc: cudaFuncSetAttribute");
     launch_kernel(dwconv7x7_kernel<__nv_bfloat16>, dim3(grid), dim3(256), smem, (cudaStream_t)stream, (const __nv_bfloat16*)x, weight, bias,
-                                                                               (__nv_bfloat16*)out, C, H, W);
+                  (__nv_bfloat16*)out, C, H, W, (int)ntiles);
   }
   FSB_CHECK_LAUNCH("fsb_dwconv7x7_nhwc");
   return FSB_OK;
