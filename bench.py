@@ -98,7 +98,7 @@ def run_reference(args):
         "note": "CPU oracle (oracle/hotpath.py), a restatement of the reference's PyTorch code pinned to the "
                 "reference's outputs; the reference itself is Python and /root/reference does not exist on the box",
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -216,7 +216,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     if not torch.cuda.is_available():
-        print(json.dumps({"error": "no CUDA device: the hot path has no CPU fallback"}))
+        emit({"error": "no CUDA device: the hot path has no CPU fallback"})
         return 2
     torch.cuda.set_device(local_rank)
     device = torch.device("cuda", local_rank)
@@ -426,11 +426,33 @@ def run_b200(args):
         if os.path.exists(traffic_file):
             with open(traffic_file) as fh:
                 line["roofline"]["traffic"] = json.load(fh).get("conv_umma_kernel")
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+_REAL_STDOUT = None
+
+
+def _quiet_stdout():
+    """Route fd 1 to stderr for the rest of the run: libraries (NCCL prints its version line on stdout) must not
+    get in front of the ONE JSON line, which emit() writes to the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj) -> None:
+    data = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
@@ -441,6 +463,8 @@ def main():
     ap.add_argument("--pairs", type=int, default=4, help="stereo pairs per GPU per step (one batch through the hot path)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     args = ap.parse_args()
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1 or args.gpus == 1:
+        _quiet_stdout()  # (the --gpus N re-launcher keeps its stdout: its children write the line)
     if args.impl == "reference":
         return run_reference(args)
     return run_b200(args)
