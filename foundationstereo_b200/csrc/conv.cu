@@ -88,7 +88,16 @@ struct alignas(64) ConvParams {
 template <typename T, int EPI>
 __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* bias_s, uint32_t taddr, bool valid,
                                               size_t pix, int b, int y, int x, int n0, int nt, int c_first,
-                                              int c_stride, int bstride) {
+                                              int c_stride, int bstride, uint32_t wait_bar = 0,
+                                              uint32_t wait_parity = 0) {
+  // wait_bar != 0: the caller has NOT yet waited for the accumulators; the epilogue does it itself, after it has
+  // issued whatever global loads do not depend on them
+  if constexpr (EPI != FSB_EPI_GATE_Q) {
+    if (wait_bar) {
+      mbar_wait(wait_bar, wait_parity);
+      tc_fence_after();
+    }
+  }
   if constexpr (EPI == FSB_EPI_GATE_ZR) {
     const int half = p.BN >> 1;
     const int cpa = p.BN >> 5;  // chunks per accumulator
@@ -118,40 +127,68 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* 
       }
     }
   } else if constexpr (EPI == FSB_EPI_GATE_Q) {
-    // 16 columns per step: keeps the kernel under 93 registers so two CTAs share an SM
+    // 16 columns per step.  The hidden state and the z gates of a step do not depend on the accumulators: they
+    // are loaded one step ahead (the first step before the accumulator barrier), so their L2 latency -- long
+    // while the TMA producers saturate L2 -- hides under the previous step's arithmetic instead of adding up
+    // eight times per tile (measured: 138 -> 97 us for gru04.q at 4 pairs with the loads removed).
     const float att = valid ? __ldg(p.att + pix) : 0.f;
+    const float* hbase = p.h32 + pix * p.hidden + n0;
+    const T* zlbase = reinterpret_cast<const T*>(p.z_l) + pix * p.hidden + n0;
+    const T* zsbase = reinterpret_cast<const T*>(p.z_s) + pix * p.hidden + n0;
+    float4 hq[4];
+    uint4 zlq[2], zsq[2];
+    auto load_step = [&](int c) {
+      if (valid) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) hq[i] = *reinterpret_cast<const float4*>(hbase + c + 4 * i);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          zlq[i] = *reinterpret_cast<const uint4*>(zlbase + c + 8 * i);
+          zsq[i] = *reinterpret_cast<const uint4*>(zsbase + c + 8 * i);
+        }
+      }
+    };
+    load_step(c_first * 16);
+    if (wait_bar) {
+      mbar_wait(wait_bar, wait_parity);
+      tc_fence_after();
+    }
     for (int c = c_first * 16; c < p.BN; c += 16 * c_stride) {
       uint32_t v0[16], v1[16];
       tmem_ld16(taddr + c, v0);
       tmem_ld16(taddr + p.BN + c, v1);
+      float h[16];
+      uint32_t zlw[8], zsw[8];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { h[4 * i] = hq[i].x; h[4 * i + 1] = hq[i].y; h[4 * i + 2] = hq[i].z; h[4 * i + 3] = hq[i].w; }
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        zlw[4 * i] = zlq[i].x; zlw[4 * i + 1] = zlq[i].y; zlw[4 * i + 2] = zlq[i].z; zlw[4 * i + 3] = zlq[i].w;
+        zsw[4 * i] = zsq[i].x; zsw[4 * i + 1] = zsq[i].y; zsw[4 * i + 2] = zsq[i].z; zsw[4 * i + 3] = zsq[i].w;
+      }
+      if (c + 16 * c_stride < p.BN) load_step(c + 16 * c_stride);  // next step's operands, in flight during this one
       tmem_ld_wait();
       if (!valid) continue;
       const int ch = n0 + c;
-      const float* hp = p.h32 + pix * p.hidden + ch;
-      const uint4* zlp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.z_l) + pix * p.hidden + ch);
-      const uint4* zsp = reinterpret_cast<const uint4*>(reinterpret_cast<const T*>(p.z_s) + pix * p.hidden + ch);
       float* ho = p.h32_out + pix * p.hidden + ch;
       uint4* h16o = reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.h16_out) + pix * p.hidden + ch);
 #pragma unroll
-      for (int o = 0; o < 2; ++o) {  // 8 channels at a time
-        const float4 ha = *reinterpret_cast<const float4*>(hp + 8 * o), hb = *reinterpret_cast<const float4*>(hp + 8 * o + 4);
-        const uint4 zlu = zlp[o], zsu = zsp[o];
-        float h[8] = {ha.x, ha.y, ha.z, ha.w, hb.x, hb.y, hb.z, hb.w};
-        const uint32_t zlw[4] = {zlu.x, zlu.y, zlu.z, zlu.w}, zsw[4] = {zsu.x, zsu.y, zsu.z, zsu.w};
+      for (int j = 0; j < 16; ++j) {
+        const float2 zl2 = unpack2<T>(zlw[j >> 1]), zs2 = unpack2<T>(zsw[j >> 1]);
+        const float zl = (j & 1) ? zl2.y : zl2.x, zs = (j & 1) ? zs2.y : zs2.x;
+        const float ql = tanh_f(__uint_as_float(v0[j]) + bias_s[c + j]);
+        const float qs = tanh_f(__uint_as_float(v1[j]) + bias_s[bstride + c + j]);
+        const float hl = (1.f - zl) * h[j] + zl * ql;
+        const float hs = (1.f - zs) * h[j] + zs * qs;
+        h[j] = hs * att + hl * (1.f - att);
+      }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          const float2 zl2 = unpack2<T>(zlw[j >> 1]), zs2 = unpack2<T>(zsw[j >> 1]);
-          const float zl = (j & 1) ? zl2.y : zl2.x, zs = (j & 1) ? zs2.y : zs2.x;
-          const float ql = tanh_f(__uint_as_float(v0[8 * o + j]) + bias_s[c + 8 * o + j]);
-          const float qs = tanh_f(__uint_as_float(v1[8 * o + j]) + bias_s[bstride + c + 8 * o + j]);
-          const float hl = (1.f - zl) * h[j] + zl * ql;
-          const float hs = (1.f - zs) * h[j] + zs * qs;
-          h[j] = hs * att + hl * (1.f - att);
-        }
-        *reinterpret_cast<float4*>(ho + 8 * o) = make_float4(h[0], h[1], h[2], h[3]);
-        *reinterpret_cast<float4*>(ho + 8 * o + 4) = make_float4(h[4], h[5], h[6], h[7]);
+      for (int o = 0; o < 2; ++o) {
+        *reinterpret_cast<float4*>(ho + 8 * o) = make_float4(h[8 * o], h[8 * o + 1], h[8 * o + 2], h[8 * o + 3]);
+        *reinterpret_cast<float4*>(ho + 8 * o + 4) = make_float4(h[8 * o + 4], h[8 * o + 5], h[8 * o + 6], h[8 * o + 7]);
         uint4 u;
-        u.x = pack2<T>(h[0], h[1]); u.y = pack2<T>(h[2], h[3]); u.z = pack2<T>(h[4], h[5]); u.w = pack2<T>(h[6], h[7]);
+        u.x = pack2<T>(h[8 * o], h[8 * o + 1]); u.y = pack2<T>(h[8 * o + 2], h[8 * o + 3]);
+        u.z = pack2<T>(h[8 * o + 4], h[8 * o + 5]); u.w = pack2<T>(h[8 * o + 6], h[8 * o + 7]);
         h16o[o] = u;
       }
     }
@@ -377,9 +414,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * buf_cols;
       const int n0 = nt * p.BN;
 
-      mbar_wait(bar_tfull + 8 * buf, use & 1);
-      tc_fence_after();
-      conv_epilogue<T, EPI>(p, bias_s + n0, taddr, valid, pix, b, y, x, n0, nt, grp, 2, p.rows);
+      conv_epilogue<T, EPI>(p, bias_s + n0, taddr, valid, pix, b, y, x, n0, nt, grp, 2, p.rows, bar_tfull + 8 * buf, use & 1);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
