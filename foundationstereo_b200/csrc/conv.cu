@@ -220,7 +220,20 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* 
         if (full) {
           store32<T>(o, f);
         } else {
-          for (int j = 0; j < 32 && n + j < p.Cout; ++j) o[j] = from_f32<T>(f[j]);
+          // ragged last chunk (e.g. the 127 motion channels): whole 16-byte vectors first, scalars for the rest
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            if (n + 8 * q + 8 <= p.Cout) {
+              uint4 u;
+              u.x = pack2<T>(f[8 * q], f[8 * q + 1]); u.y = pack2<T>(f[8 * q + 2], f[8 * q + 3]);
+              u.z = pack2<T>(f[8 * q + 4], f[8 * q + 5]); u.w = pack2<T>(f[8 * q + 6], f[8 * q + 7]);
+              reinterpret_cast<uint4*>(o)[q] = u;
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                if (n + 8 * q + j < p.Cout) o[8 * q + j] = from_f32<T>(f[8 * q + j]);
+            }
+          }
         }
       }
       if (p.out_f32 != nullptr) {

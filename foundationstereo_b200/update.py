@@ -268,13 +268,11 @@ class SelectiveUpdateBlock:
     def _build_plan(self, B: int, H: int, W: int) -> _Plan:
         hd, dev, dt = self.hidden, self.device, self.dtype
         plan = _Plan()
-        # tile shape per launch: with >= 2 pairs' worth of pixels the two largest 3x3 layers run the halo
-        # variant with wide N tiles (a weight tile feeds 256 pixels, N = 256 keeps the MMA off the shared-
-        # memory bandwidth limit); a single 120x160 pair has too few pixel tiles for that to pay
+        # tile shape per launch: explicit entries here override the cost model of _pick_block_n (used for every
+        # tap-layout launch).  Since the tap kernel became persistent it matches or beats the halo variant on every
+        # layer shape of the block (tools/conv_sweep.py: 3x3 512->512 288 vs 295 us, 384->384 182 vs 184 us), so
+        # no launch defaults to the halo layout any more; `halo=[...]` still selects it per launch.
         plan.tile = {}
-        if B * H * W >= 2 * 19200 and not self.fixed_tiles:
-            plan.tile = {"gru04.conv0": (_lib.FSB_CONV_LAYOUT_HALO, 192), "gru04.conv1": (_lib.FSB_CONV_LAYOUT_HALO, 256),
-                         "encoder.convc2": (_lib.FSB_CONV_LAYOUT_TAP, 256)}
         plan.shape = [(B, H, W), (B, _down(H), _down(W)), (B, _down(_down(H)), _down(_down(W)))]
         new = lambda lvl, c, dtype=dt: torch.empty(*plan.shape[lvl], c, dtype=dtype, device=dev)
         plan.h32 = [new(l, hd, torch.float32) for l in range(3)]
