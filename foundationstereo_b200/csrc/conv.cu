@@ -55,6 +55,8 @@ __host__ __device__ inline uint32_t make_step(int src, int dy, int dx, int acc, 
 struct alignas(64) ConvParams {
   CUtensorMap amap[FSB_MAX_SRC];
   CUtensorMap wmap;
+  CUtensorMap omap;  // 16-bit NHWC output, box (32 channels, bw, 32/bw, 1): the TMA-store epilogue of the tap kernel
+  int ostore;        // 1: plain epilogues leave through shared memory + cp.async.bulk.tensor stores
   uint32_t steps[kMaxSteps];
   int nsteps;
   int H, W, tiles_x, tiles_y, tw_log2;
@@ -89,7 +91,7 @@ template <typename T, int EPI>
 __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* bias_s, uint32_t taddr, bool valid,
                                               size_t pix, int b, int y, int x, int n0, int nt, int c_first,
                                               int c_stride, int bstride, uint32_t wait_bar = 0,
-                                              uint32_t wait_parity = 0) {
+                                              uint32_t wait_parity = 0, uint8_t* stage = nullptr) {
   // wait_bar != 0: the caller has NOT yet waited for the accumulators; the epilogue does it itself, after it has
   // issued whatever global loads do not depend on them
   if constexpr (EPI != FSB_EPI_GATE_Q) {
@@ -199,8 +201,41 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* 
       tmem_ld32(taddr + c, v);
       tmem_ld_wait();
       const int n = n0 + c;
-      if (!valid || n >= p.Cout) continue;
       const bool full = (n + 32 <= p.Cout);
+      if (stage != nullptr && full) {
+        // Coalesced path: the warp's 32 pixels x 32 channels go to a 2 KB shared tile (SWIZZLE_64B: 16-byte unit
+        // u of row r at u ^ ((r >> 1) & 3), conflict free) and leave as ONE tensor store; rows outside the image
+        // are clipped by the TMA unit.  Per-lane stores of 64 B at pixel stride touched 32 lines per instruction
+        // and sustained ~1.6 TB/s (tools/conv_sweep.py: time of the 1x1 layers ~ 0.6 us per MB of output).
+        const int lane = threadIdx.x & 31;
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // previous store has read the tile
+        __syncwarp();
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          float a0 = __uint_as_float(v[2 * j]) + bias_s[c + 2 * j], a1 = __uint_as_float(v[2 * j + 1]) + bias_s[c + 2 * j + 1];
+          if constexpr (EPI == FSB_EPI_RELU) { a0 = fmaxf(a0, 0.f); a1 = fmaxf(a1, 0.f); }
+          if constexpr (EPI == FSB_EPI_GELU) { a0 = gelu_f(a0); a1 = gelu_f(a1); }
+          pk[j] = pack2<T>(a0, a1);
+        }
+        uint8_t* row = stage + lane * 64;
+        const int sw = (lane >> 1) & 3;
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          *reinterpret_cast<uint4*>(row + ((u ^ sw) << 4)) = make_uint4(pk[4 * u], pk[4 * u + 1], pk[4 * u + 2], pk[4 * u + 3]);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        const int wx0 = __shfl_sync(0xffffffffu, x, 0), wy0 = __shfl_sync(0xffffffffu, y, 0);  // lane 0 = the warp's first pixel
+        __syncwarp();
+        if (lane == 0) {
+          asm volatile(
+              "cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+              ::"l"(&p.omap), "r"(smem_u32(stage)), "r"(p.ch_off + n), "r"(wx0), "r"(wy0), "r"(b)
+              : "memory");
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        continue;
+      }
+      if (!valid || n >= p.Cout) continue;
       float f[32];
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
@@ -414,6 +449,9 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
     const int grp = (warp - 2) >> 2;
     const int r = q * 32 + lane;
     const int ty = r >> p.tw_log2, tx = r & (TW - 1);
+    // 2 KB store tile of this warp, behind the operand ring
+    uint8_t* stage = p.ostore ? smem_raw + (smem_base - smem_u32(smem_raw)) + (size_t)S * stage_bytes + (size_t)(warp - 2) * 2048
+                              : nullptr;
     int it = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
       const int mtile = tile / ntn, nt = tile - mtile * ntn;
@@ -427,11 +465,13 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * buf_cols;
       const int n0 = nt * p.BN;
 
-      conv_epilogue<T, EPI>(p, bias_s + n0, taddr, valid, pix, b, y, x, n0, nt, grp, 2, p.rows, bar_tfull + 8 * buf, use & 1);
+      conv_epilogue<T, EPI>(p, bias_s + n0, taddr, valid, pix, b, y, x, n0, nt, grp, 2, p.rows, bar_tfull + 8 * buf, use & 1,
+                            stage);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
     }
+    if (p.ostore && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // stores done before smem goes away
   }
   __syncwarp();
   __syncthreads();
@@ -773,14 +813,19 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   const size_t step_bytes = (size_t)kATileBytes + (size_t)BN * kBK * 2;
   int kper = BN <= 128 ? 2 : 1, stages = a->stages;
   if (kper > n) kper = n;
-  const size_t ring_budget = 200 * 1024;
+  // the TMA-store epilogue (plain epilogues with a 16-bit output, decided below with the same condition) keeps
+  // 16 KB of store tiles behind the ring
+  const bool ostore = !halo && a->out != nullptr && a->out_f32 == nullptr &&
+                      (epi == FSB_EPI_BIAS || epi == FSB_EPI_RELU || epi == FSB_EPI_GELU) && a->Cout >= 32;
+  const size_t ring_budget = (ostore ? 184 : 200) * 1024;
+  if (kper == 2 && ring_budget / (2 * step_bytes) < 3) kper = 1;  // at least three stages in flight
   if (stages <= 0) stages = (int)(ring_budget / (kper * step_bytes));
   if (stages > 8) stages = 8;
   while (stages > 1 && stages * kper * step_bytes > ring_budget) --stages;
   if (stages < 1) stages = 1;
   p.stages = stages;
   p.kper = kper;
-  size_t smem = (size_t)stages * kper * step_bytes + 1024;
+  size_t smem = (size_t)stages * kper * step_bytes + 1024 + 8 * 2048;
   if (halo) {
     // activation ring: 3 boxes of 34 KB; weight ring: what is left of 220 KB (2..8 tiles)
     const size_t b_bytes = (size_t)BN * kBK * 2;
@@ -813,6 +858,19 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
     CUresult r = enc(&p.wmap, dt, 2, const_cast<void*>(a->weight), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     FSB_REQUIRE(r == CUDA_SUCCESS, FSB_ERR_CUDA, "fsb_conv2d_nhwc: cuTensorMapEncodeTiled(weight) -> %d", (int)r);
+  }
+  // TMA-store epilogue of the tap kernel: plain epilogues with a 16-bit NHWC output
+  p.ostore = 0;
+  if (ostore) {
+    const int bw = TW < 32 ? TW : 32, bh = 32 / bw;
+    cuuint64_t dims[4] = {(cuuint64_t)a->ld_out, (cuuint64_t)a->W, (cuuint64_t)a->H, (cuuint64_t)a->B};
+    cuuint64_t strides[3] = {(cuuint64_t)a->ld_out * 2, (cuuint64_t)a->ld_out * 2 * a->W, (cuuint64_t)a->ld_out * 2 * a->W * a->H};
+    cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(&p.omap, dt, 4, a->out, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
+                     CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    FSB_REQUIRE(r == CUDA_SUCCESS, FSB_ERR_CUDA, "fsb_conv2d_nhwc: cuTensorMapEncodeTiled(out) -> %d", (int)r);
+    p.ostore = 1;
   }
   // instruction descriptor, kind::f16: D fp32, A/B f16|bf16, both K-major, M = 128, N = block_n
   const uint32_t fmt = dtype == FSB_F16 ? 0u : 1u;
