@@ -122,55 +122,64 @@ resize_kernel(const float* __restrict__ src, T* __restrict__ dst, int C4, int Hs
 }
 
 // ------------------------------------------------------------------ 7x7, one input channel
-// CTA = 32 consecutive pixels of one row; thread = (pixel, 8 output channels).
+// CTA = 32 (x) x kC1Rows (y) pixels; thread = (pixel column, 8 output channels) walking down the rows, so the
+// 49 x Cout weights (12.5 KB) are staged once per 256 pixels instead of once per 32 (the prologue was the kernel).
 constexpr int kC1MaxCout = 64;
+constexpr int kC1Rows = 8;
 template <typename T>
 __global__ void __launch_bounds__(256)
 conv7x7_c1_kernel(const float* __restrict__ disp, const float* __restrict__ weight, const float* __restrict__ bias,
                   T* __restrict__ out, int ld_out, int Cout, T* __restrict__ disp_out, int ld_disp, int disp_ch,
                   int H, int W) {
   pdl_launch_dependents();  // the next kernel may start its prologue
-  pdl_wait();               // inputs written by the previous kernel are complete and visible
-  __shared__ float wsm[49][kC1MaxCout];
-  __shared__ float patch[7][32 + 6];
+  __shared__ __align__(16) float wsm[49][kC1MaxCout];
+  __shared__ float patch[kC1Rows + 6][32 + 6];
   const int tid = threadIdx.x;
-  const int x0 = blockIdx.x * 32, y = blockIdx.y, b = blockIdx.z;
-  for (int i = tid; i < 49 * Cout; i += 256) {
+  const int x0 = blockIdx.x * 32, y0 = blockIdx.y * kC1Rows, b = blockIdx.z;
+  for (int i = tid; i < 49 * Cout; i += 256) {  // parameters: no kernel writes them
     const int co = i / 49, t = i - co * 49;
     wsm[t][co] = weight[i];
   }
+  pdl_wait();  // inputs written by the previous kernel are complete and visible
   const float* d = disp + (size_t)b * H * W;
-  for (int i = tid; i < 7 * 38; i += 256) {
+  for (int i = tid; i < (kC1Rows + 6) * 38; i += 256) {
     const int ry = i / 38, rx = i - ry * 38;
-    const int yy = y + ry - 3, xx = x0 + rx - 3;
+    const int yy = y0 + ry - 3, xx = x0 + rx - 3;
     patch[ry][rx] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? d[(size_t)yy * W + xx] : 0.f;
   }
   __syncthreads();
   const int px = tid & 31, cg = tid >> 5;  // 8 channel groups
   const int x = x0 + px;
   if (x >= W) return;
-  const size_t pix = ((size_t)b * H + y) * W + x;
   for (int c0 = cg * 8; c0 < Cout; c0 += 64) {
-    float acc[8];
+    float bv[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = (c0 + j < Cout) ? __ldg(bias + c0 + j) : 0.f;
+    for (int j = 0; j < 8; ++j) bv[j] = (c0 + j < Cout) ? __ldg(bias + c0 + j) : 0.f;
+    for (int r = 0; r < kC1Rows; ++r) {
+      const int y = y0 + r;
+      if (y >= H) break;
+      float acc[8];
 #pragma unroll
-    for (int ky = 0; ky < 7; ++ky)
+      for (int j = 0; j < 8; ++j) acc[j] = bv[j];
 #pragma unroll
-      for (int kx = 0; kx < 7; ++kx) {
-        const float v = patch[ky][px + kx];
-        const float4 w0 = *reinterpret_cast<const float4*>(&wsm[ky * 7 + kx][c0]);
-        const float4 w1 = *reinterpret_cast<const float4*>(&wsm[ky * 7 + kx][c0 + 4]);
-        acc[0] = fmaf(v, w0.x, acc[0]); acc[1] = fmaf(v, w0.y, acc[1]);
-        acc[2] = fmaf(v, w0.z, acc[2]); acc[3] = fmaf(v, w0.w, acc[3]);
-        acc[4] = fmaf(v, w1.x, acc[4]); acc[5] = fmaf(v, w1.y, acc[5]);
-        acc[6] = fmaf(v, w1.z, acc[6]); acc[7] = fmaf(v, w1.w, acc[7]);
-      }
-    T* o = out + pix * ld_out + c0;
-    Quad<T>::store(o, fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f), fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
-    Quad<T>::store(o + 4, fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f), fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
+      for (int ky = 0; ky < 7; ++ky)
+#pragma unroll
+        for (int kx = 0; kx < 7; ++kx) {
+          const float v = patch[r + ky][px + kx];
+          const float4 w0 = *reinterpret_cast<const float4*>(&wsm[ky * 7 + kx][c0]);
+          const float4 w1 = *reinterpret_cast<const float4*>(&wsm[ky * 7 + kx][c0 + 4]);
+          acc[0] = fmaf(v, w0.x, acc[0]); acc[1] = fmaf(v, w0.y, acc[1]);
+          acc[2] = fmaf(v, w0.z, acc[2]); acc[3] = fmaf(v, w0.w, acc[3]);
+          acc[4] = fmaf(v, w1.x, acc[4]); acc[5] = fmaf(v, w1.y, acc[5]);
+          acc[6] = fmaf(v, w1.z, acc[6]); acc[7] = fmaf(v, w1.w, acc[7]);
+        }
+      const size_t pix = ((size_t)b * H + y) * W + x;
+      T* o = out + pix * ld_out + c0;
+      Quad<T>::store(o, fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f), fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
+      Quad<T>::store(o + 4, fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f), fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
+      if (disp_out != nullptr && cg == 0 && c0 == 0) disp_out[pix * ld_disp + disp_ch] = from_f32<T>(patch[r + 3][px + 3]);
+    }
   }
-  if (disp_out != nullptr && cg == 0) disp_out[pix * ld_disp + disp_ch] = from_f32<T>(patch[3][px + 3]);
 }
 
 // ------------------------------------------------------------------ depthwise 7x7
@@ -372,7 +381,7 @@ extern "C" int fsb_conv7x7_c1(const float* disp, const float* weight, const floa
               "fsb_conv7x7_c1: Cout=%d (multiple of 8, <= %d), ld_out=%d", Cout, kC1MaxCout, ld_out);
   FSB_REQUIRE(!disp_out || (disp_ch >= 0 && disp_ch < ld_disp), FSB_ERR_ARG, "fsb_conv7x7_c1: disp_ch=%d ld_disp=%d", disp_ch, ld_disp);
   FSB_REQUIRE(H < 65536 && B < 65536, FSB_ERR_SHAPE, "fsb_conv7x7_c1: grid too large");
-  dim3 grid(ceil_div(W, 32), H, B);
+  dim3 grid(ceil_div(W, 32), ceil_div(H, kC1Rows), B);
   FSB_DISPATCH16(dtype, (launch_kernel(conv7x7_c1_kernel<T>, dim3(grid), dim3(256), 0, (cudaStream_t)stream, disp, weight, bias, (T*)out, ld_out, Cout,
                                                                                        (T*)disp_out, ld_disp, disp_ch, H, W)));
   FSB_CHECK_LAUNCH("fsb_conv7x7_c1");
