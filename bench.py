@@ -460,7 +460,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--pairs", type=int, default=4, help="stereo pairs per GPU per step (one batch through the hot path)")
+    ap.add_argument("--pairs", type=int, default=8, help="stereo pairs per GPU per step (one batch through the hot path)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     args = ap.parse_args()
     if int(os.environ.get("WORLD_SIZE", "1")) > 1 or args.gpus == 1:
