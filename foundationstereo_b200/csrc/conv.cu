@@ -55,13 +55,14 @@ __host__ __device__ inline uint32_t make_step(int src, int dy, int dx, int acc, 
 struct alignas(64) ConvParams {
   CUtensorMap amap[FSB_MAX_SRC];
   CUtensorMap wmap;
+  CUtensorMap wmap_half;  // pair mode: box (64, block_n / 2), each CTA of a pair holds half of the weight tile
   CUtensorMap omap;  // 16-bit NHWC output, box (32 channels, bw, 32/bw, 1): the TMA-store epilogue of the tap kernel
   int ostore;        // 1: plain epilogues leave through shared memory + cp.async.bulk.tensor stores
   uint32_t steps[kMaxSteps];
   int nsteps;
   int H, W, tiles_x, tiles_y, tw_log2;
   int BN, nacc, tmem_cols, stages, kper;
-  int nbuf, ntiles, ntiles_n;  // persistent tap kernel: TMEM accumulator buffers, work items, N tiles per pixel tile
+  int nbuf, ntiles, ntiles_n, nbatch;  // persistent tap kernel: TMEM accumulator buffers, work items, N tiles per pixel tile
   int SA, SB;  // halo kernel: activation / weight ring depths
   uint32_t idesc;
   int rows, Cout;
@@ -292,7 +293,59 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* 
 // a CTA that lives for one small-K tile spends ~15k cycles on launch, TMEM allocation, pipeline fill and
 // a serial epilogue around 512 cycles of MMA, and the GRU q gate lost 45 % of its time to an epilogue
 // nothing overlapped.
-template <typename T, int EPI>
+// CL == 2 ("pair mode"): a cluster of two CTAs on two adjacent pixel tiles and the SAME N tile runs ONE
+// tcgen05.mma.cta_group::2 stream (M = 256): each CTA stages its own 128-pixel activation tile and HALF of the
+// weight tile (rows [r*bn/2, (r+1)*bn/2)), the leader CTA (rank 0) issues the MMAs for both, each CTA's
+// accumulators live in its own TMEM and each CTA runs its own epilogue.  What this buys is bytes: a tap-layout CTA
+// is bound by what an SM can ingest from L2 (~67 B/cycle, section 6 of DESIGN.md) and in pair mode an SM takes in
+// 16 KB + bn*64 B per K step instead of 16 KB + bn*128 B.  (Multicasting the weight tile to two independent
+// CTAs does not help: each SM still ingests the whole tile.)
+// Barriers: full[s] lives in the leader (its two producers arrive with the bytes of BOTH CTAs; every TMA load of
+// either CTA completes on it: .cta_group::2 loads with the peer bit of the barrier address cleared); empty[s],
+// tfull[b] are signalled in both CTAs by multicast commits of the leader; tempty[b] of the leader collects the
+// epilogue warps of both CTAs (the peer arrives remotely).
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // shared::cluster address of the same object in the even CTA of a pair
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_4d_2sm(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar & kPeerBitMask), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_f16_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint32_t bar) {  // arrives on `bar` in BOTH CTAs of the pair
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {  // arrive on the leader CTA's copy of `bar`
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, 0;\n\t"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n\t}"
+      ::"r"(bar) : "memory");
+}
+
+template <typename T, int EPI, int CL>
 __global__ void __launch_bounds__(kConvThreads, 1)
 conv_umma_kernel(const __grid_constant__ ConvParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -304,7 +357,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
   const int lane = threadIdx.x & 31;
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int kper = p.kper;
-  const uint32_t b_tile_bytes = (uint32_t)p.BN * (kBK * 2);
+  const uint32_t b_tile_bytes = (uint32_t)(p.BN / CL) * (kBK * 2);  // this CTA's part of a weight tile
   const uint32_t a_stage_bytes = (uint32_t)kper * kATileBytes;
   const uint32_t stage_bytes = a_stage_bytes + (uint32_t)kper * b_tile_bytes;
   const int S = p.stages;
@@ -315,7 +368,15 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
   const int nbuf = p.nbuf;
   const uint32_t buf_cols = (uint32_t)(p.nacc * p.BN);
   const int TW = 1 << p.tw_log2, TH = kBM >> p.tw_log2;
-  const int ntn = p.ntiles_n, ntiles = p.ntiles;
+  const int ntn = p.ntiles_n;
+  // work list: CL == 1: (pixel tile, N tile); CL == 2: (PAIR of pixel tiles, N tile), CTA r of the cluster takes pixel
+  // tile 2*pair + r (one past the end for an odd count: all-zero operands, nothing stored)
+  const int crank = CL == 2 ? (int)cluster_ctarank() : 0;
+  const bool leader = crank == 0;
+  const int wfirst = CL == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int wstep = CL == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int nwork = p.ntiles;
+  const int mtiles = p.tiles_x * p.tiles_y * p.nbatch;
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < S; ++s) {
@@ -324,23 +385,31 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar_tfull + 8 * i, 1);
-      mbar_init(bar_tempty + 8 * i, 8);  // one arrival per epilogue warp
+      mbar_init(bar_tempty + 8 * i, 8 * CL);  // one arrival per epilogue warp (of both CTAs in pair mode)
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     tma_prefetch_desc(&p.amap[0]);
   }
   if (warp == kWarpB && lane == 0) tma_prefetch_desc(&p.wmap);
   if (warp == 1) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
-                 "r"((uint32_t)p.tmem_cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (CL == 2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
+                   "r"((uint32_t)p.tmem_cols)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
+                   "r"((uint32_t)p.tmem_cols)
+                   : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   if (warp >= 2 && warp < kWarpB) {
     for (int i = threadIdx.x - 64; i < p.nacc * p.rows; i += 256) bias_s[i] = __ldg(p.bias + i);
   }
   tc_fence_before();
   __syncthreads();
+  if (CL == 2) cluster_sync_all();  // both CTAs' barriers and TMEM exist before either touches the other
   tc_fence_after();
   const uint32_t tmem_base = tmem_slot;
   // PDL: the prologue above (and the weight producer below, which only reads parameters that no kernel
@@ -353,10 +422,10 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
     int s = 0;
     uint32_t ph = 0;
     bool first_round = true;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const int mtile = tile / ntn;
+    for (int wt = wfirst; wt < nwork; wt += wstep) {
+      const int mtile = CL == 2 ? 2 * (wt / ntn) + crank : wt / ntn;
       const int txi = mtile % p.tiles_x, r1 = mtile / p.tiles_x;
-      const int tyi = r1 % p.tiles_y, b = r1 / p.tiles_y;
+      const int tyi = r1 % p.tiles_y, b = r1 / p.tiles_y;  // b == nbatch for the pad tile of an odd count: zero fill
       const int x0 = txi * TW, y0 = tyi * TH;
       for (int i = 0; i < p.nsteps; i += kper) {
         const int n = min(kper, p.nsteps - i);
@@ -365,11 +434,12 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
         if (elect_one()) {
           const uint32_t full = bar_full + 8 * s;
           uint32_t dst = smem_base + s * stage_bytes;
-          mbar_expect_tx(full, (uint32_t)n * kATileBytes);
+          if (leader) mbar_expect_tx(full, (uint32_t)(CL * n) * kATileBytes);  // pair mode: the peer's tiles complete here too
           for (int j = 0; j < n; ++j) {
             const uint32_t st = p.steps[i + j];
             const int src = st & 3, dy = (int)((st >> 2) & 3) - 1, dx = (int)((st >> 4) & 3) - 1, chunk = (st >> 8) & 0xff;
-            tma_load_4d(dst, &p.amap[src], full, chunk * kBK, x0 + dx, y0 + dy, b);
+            if (CL == 2) tma_load_4d_2sm(dst, &p.amap[src], full, chunk * kBK, x0 + dx, y0 + dy, b);
+            else         tma_load_4d(dst, &p.amap[src], full, chunk * kBK, x0 + dx, y0 + dy, b);
             dst += kATileBytes;
           }
         }
@@ -381,8 +451,8 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
     int s = 0;
     uint32_t ph = 0;
     bool first_round = true;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-      const int n0 = (tile % ntn) * p.BN;
+    for (int wt = wfirst; wt < nwork; wt += wstep) {
+      const int n0 = (wt % ntn) * p.BN;
       for (int i = 0; i < p.nsteps; i += kper) {
         const int n = min(kper, p.nsteps - i);
         if (!first_round) mbar_wait(bar_empty + 8 * s, ph ^ 1);
@@ -390,22 +460,23 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
         if (elect_one()) {
           const uint32_t full = bar_full + 8 * s;
           uint32_t dst = smem_base + s * stage_bytes + a_stage_bytes;
-          mbar_expect_tx(full, (uint32_t)n * b_tile_bytes);
+          if (leader) mbar_expect_tx(full, (uint32_t)(CL * n) * b_tile_bytes);
           for (int j = 0; j < n; ++j) {
-            tma_load_2d(dst, &p.wmap, full, (i + j) * kBK, n0);
+            if (CL == 2) tma_load_2d_2sm(dst, &p.wmap_half, full, (i + j) * kBK, n0 + crank * (p.BN >> 1));
+            else         tma_load_2d(dst, &p.wmap, full, (i + j) * kBK, n0);
             dst += b_tile_bytes;
           }
         }
         if (++s == S) { s = 0; ph ^= 1; first_round = false; }
       }
     }
-  } else if (warp == 1) {
-    // ====================================================================== MMA issuer
+  } else if (warp == 1 && leader) {
+    // ====================================================================== MMA issuer (pair mode: the leader CTA only)
     int s = 0;
     uint32_t ph = 0;
     const uint32_t idesc = p.idesc;
     int it = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+    for (int wt = wfirst; wt < nwork; wt += wstep, ++it) {
       const int buf = nbuf == 2 ? (it & 1) : 0;
       const uint32_t use = (uint32_t)(nbuf == 2 ? (it >> 1) : it);  // how often this buffer was used before
       mbar_wait(bar_tempty + 8 * buf, (use & 1) ^ 1);                // drained by the epilogue (passes at first use)
@@ -426,21 +497,34 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
           const uint32_t first = (started >> acc) & 1;
           if (elect_one()) {
             // +32 B along K inside the swizzle atom = +2 in the (addr >> 4) field
-            umma_f16(d, adesc, bdesc, idesc, first);
-            umma_f16(d, adesc + 2, bdesc + 2, idesc, 1);
-            umma_f16(d, adesc + 4, bdesc + 4, idesc, 1);
-            umma_f16(d, adesc + 6, bdesc + 6, idesc, 1);
+            if (CL == 2) {
+              umma_f16_2sm(d, adesc, bdesc, idesc, first);
+              umma_f16_2sm(d, adesc + 2, bdesc + 2, idesc, 1);
+              umma_f16_2sm(d, adesc + 4, bdesc + 4, idesc, 1);
+              umma_f16_2sm(d, adesc + 6, bdesc + 6, idesc, 1);
+            } else {
+              umma_f16(d, adesc, bdesc, idesc, first);
+              umma_f16(d, adesc + 2, bdesc + 2, idesc, 1);
+              umma_f16(d, adesc + 4, bdesc + 4, idesc, 1);
+              umma_f16(d, adesc + 6, bdesc + 6, idesc, 1);
+            }
           }
           started |= 1u << acc;
           adesc += kATileBytes >> 4;
           bdesc += b_tile_bytes >> 4;
         }
-        if (elect_one()) umma_commit(bar_empty + 8 * s);  // frees the stage when these MMAs have read it
+        if (elect_one()) {  // frees the stage (of both CTAs) when these MMAs have read it
+          if (CL == 2) umma_commit_2sm(bar_empty + 8 * s);
+          else         umma_commit(bar_empty + 8 * s);
+        }
         if (++s == S) { s = 0; ph ^= 1; }
       }
-      if (elect_one()) umma_commit(bar_tfull + 8 * buf);  // all MMAs of the tile done -> accumulators complete
+      if (elect_one()) {  // all MMAs of the tile done -> accumulators complete (in both CTAs)
+        if (CL == 2) umma_commit_2sm(bar_tfull + 8 * buf);
+        else         umma_commit(bar_tfull + 8 * buf);
+      }
     }
-  } else if (warp < kWarpB) {
+  } else if (warp >= 2 && warp < kWarpB) {
     // ======================================================================== epilogue
     // 8 warps: warp w reads TMEM lane quarter (w & 3); the two warps of a quarter split the
     // 32-column chunks between them (grp 0: even chunks, grp 1: odd chunks), which halves the
@@ -453,12 +537,13 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
     uint8_t* stage = p.ostore ? smem_raw + (smem_base - smem_u32(smem_raw)) + (size_t)S * stage_bytes + (size_t)(warp - 2) * 2048
                               : nullptr;
     int it = 0;
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-      const int mtile = tile / ntn, nt = tile - mtile * ntn;
+    for (int wt = wfirst; wt < nwork; wt += wstep, ++it) {
+      const int nt = wt % ntn;
+      const int mtile = CL == 2 ? 2 * (wt / ntn) + crank : wt / ntn;
       const int txi = mtile % p.tiles_x, r1 = mtile / p.tiles_x;
       const int tyi = r1 % p.tiles_y, b = r1 / p.tiles_y;
       const int y = tyi * TH + ty, x = txi * TW + tx;
-      const bool valid = (y < p.H) && (x < p.W);
+      const bool valid = (y < p.H) && (x < p.W) && (mtile < mtiles);
       const size_t pix = valid ? ((size_t)b * p.H + y) * p.W + x : 0;
       const int buf = nbuf == 2 ? (it & 1) : 0;
       const uint32_t use = (uint32_t)(nbuf == 2 ? (it >> 1) : it);
@@ -469,16 +554,22 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
                             stage);
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+      if (lane == 0) {
+        if (CL == 2) mbar_arrive_leader(bar_tempty + 8 * buf);
+        else         mbar_arrive(bar_tempty + 8 * buf);
+      }
     }
     if (p.ostore && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // stores done before smem goes away
   }
   __syncwarp();
   __syncthreads();
+  if (CL == 2) cluster_sync_all();  // no CTA leaves (or frees TMEM) while its peer may still use it
   if (warp == 1) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.tmem_cols)
-                 : "memory");
+    if (CL == 2)
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.tmem_cols) : "memory");
+    else
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.tmem_cols) : "memory");
   }
 }
 
@@ -669,17 +760,21 @@ static int pick_tile(int H, int W, int* tw_log2) {
   return (int)best;
 }
 
-template <typename T>
-static auto kernel_for(int epi) -> void (*)(const ConvParams) {
+template <typename T, int CL>
+static auto kernel_for_cl(int epi) -> void (*)(const ConvParams) {
   switch (epi) {
-    case FSB_EPI_BIAS: return conv_umma_kernel<T, FSB_EPI_BIAS>;
-    case FSB_EPI_RELU: return conv_umma_kernel<T, FSB_EPI_RELU>;
-    case FSB_EPI_GATE_ZR: return conv_umma_kernel<T, FSB_EPI_GATE_ZR>;
-    case FSB_EPI_GATE_Q: return conv_umma_kernel<T, FSB_EPI_GATE_Q>;
-    case FSB_EPI_GELU: return conv_umma_kernel<T, FSB_EPI_GELU>;
-    case FSB_EPI_SCALE_RES: return conv_umma_kernel<T, FSB_EPI_SCALE_RES>;
+    case FSB_EPI_BIAS: return conv_umma_kernel<T, FSB_EPI_BIAS, CL>;
+    case FSB_EPI_RELU: return conv_umma_kernel<T, FSB_EPI_RELU, CL>;
+    case FSB_EPI_GATE_ZR: return conv_umma_kernel<T, FSB_EPI_GATE_ZR, CL>;
+    case FSB_EPI_GATE_Q: return conv_umma_kernel<T, FSB_EPI_GATE_Q, CL>;
+    case FSB_EPI_GELU: return conv_umma_kernel<T, FSB_EPI_GELU, CL>;
+    case FSB_EPI_SCALE_RES: return conv_umma_kernel<T, FSB_EPI_SCALE_RES, CL>;
     default: return nullptr;
   }
+}
+template <typename T>
+static auto kernel_for(int epi, int cl) -> void (*)(const ConvParams) {
+  return cl == 2 ? kernel_for_cl<T, 2>(epi) : kernel_for_cl<T, 1>(epi);
 }
 
 template <typename T>
@@ -810,8 +905,23 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
 
   // Pipeline shape of the persistent tap kernel: one CTA per SM owns ~200 KB of shared memory; a stage holds
   // two K steps for N tiles up to 128 (each producer pays one mbarrier round per two loads), one above.
-  const size_t step_bytes = (size_t)kATileBytes + (size_t)BN * kBK * 2;
-  int kper = BN <= 128 ? 2 : 1, stages = a->stages;
+  // pair mode (tcgen05.mma.cta_group::2 over two pixel tiles, half a weight tile per CTA): at least two pixel tiles
+  // and halves that are whole 8-row swizzle atoms; FSB_CONV_PAIR=0 switches it off (A/B measurements)
+  const long long mtiles0 = (long long)p.tiles_x * p.tiles_y * a->B;
+  static const int pair_env = [] { const char* e = getenv("FSB_CONV_PAIR"); return e ? atoi(e) : 1; }();
+  // (short K loops lose: 1x1 128->512 30 -> 43 us, while 3x3 512->256 gains 177 -> 135 us; tools/conv_sweep.py)
+  int nsteps_all = 0;
+  for (int sgi = 0; sgi < a->nseg; ++sgi) {
+    int ch = 0;
+    for (int k = 0; k < a->seg[sgi].nsrc; ++k) {
+      const int si = a->seg[sgi].src[k];
+      if (si >= 0 && si < a->nsrc) ch += a->src[si].C / kBK;
+    }
+    nsteps_all += a->seg[sgi].ksize * a->seg[sgi].ksize * ch;
+  }
+  const int cl = (!halo && pair_env != 0 && mtiles0 >= 2 && BN % 16 == 0 && BN >= 32 && nsteps_all >= 24) ? 2 : 1;
+  const size_t step_bytes = (size_t)kATileBytes + (size_t)(BN / cl) * kBK * 2;
+  int kper = (BN / cl) <= 128 ? 2 : 1, stages = a->stages;
   if (kper > n) kper = n;
   // the TMA-store epilogue (plain epilogues with a 16-bit output, decided below with the same condition) keeps
   // 16 KB of store tiles behind the ring
@@ -874,9 +984,18 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
     FSB_REQUIRE(r == CUDA_SUCCESS, FSB_ERR_CUDA, "fsb_conv2d_nhwc: cuTensorMapEncodeTiled(out) -> %d", (int)r);
     p.ostore = 1;
   }
-  // instruction descriptor, kind::f16: D fp32, A/B f16|bf16, both K-major, M = 128, N = block_n
+  if (cl == 2) {
+    cuuint64_t dims[2] = {(cuuint64_t)Ktot, (cuuint64_t)a->rows};
+    cuuint64_t strides[1] = {(cuuint64_t)Ktot * 2};
+    cuuint32_t box[2] = {(cuuint32_t)kBK, (cuuint32_t)(BN / 2)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&p.wmap_half, dt, 2, const_cast<void*>(a->weight), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    FSB_REQUIRE(r == CUDA_SUCCESS, FSB_ERR_CUDA, "fsb_conv2d_nhwc: cuTensorMapEncodeTiled(weight half) -> %d", (int)r);
+  }
+  // instruction descriptor, kind::f16: D fp32, A/B f16|bf16, both K-major, M = 128 (256 over a CTA pair), N = block_n
   const uint32_t fmt = dtype == FSB_F16 ? 0u : 1u;
-  p.idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+  p.idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((cl * kBM) >> 4) << 24);
   p.rows = a->rows;
   p.Cout = a->Cout;
   p.bias = a->bias;
@@ -899,16 +1018,58 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   p.hidden = a->hidden;
 
   auto kern = halo ? (dtype == FSB_F16 ? halo_kernel_for<__half>(epi) : halo_kernel_for<__nv_bfloat16>(epi))
-                   : (dtype == FSB_F16 ? kernel_for<__half>(epi) : kernel_for<__nv_bfloat16>(epi));
+                   : (dtype == FSB_F16 ? kernel_for<__half>(epi, cl) : kernel_for<__nv_bfloat16>(epi, cl));
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return cuda_fail(e, "fsb_conv2d_nhwc: cudaFuncSetAttribute");
   const long long mtiles = (long long)p.tiles_x * p.tiles_y * a->B;
   FSB_REQUIRE(mtiles * (a->rows / BN) < (1ll << 31) && a->rows / BN < 65536, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: grid too large");
   p.ntiles_n = a->rows / BN;
-  p.ntiles = (int)(mtiles * p.ntiles_n);
+  p.nbatch = a->B;
+  p.ntiles = (int)((cl == 2 ? (mtiles + 1) / 2 : mtiles) * p.ntiles_n);  // work items: (pixel tile | pair of them, N tile)
   dim3 grid((unsigned)mtiles, (unsigned)(a->rows / BN));
-  if (!halo) grid = dim3((unsigned)(p.ntiles < sm_count() ? p.ntiles : sm_count()), 1);
-  launch_kernel(kern, dim3(grid), dim3(kConvThreads), smem, (cudaStream_t)stream, p);
+  if (halo) {
+    launch_kernel(kern, dim3(grid), dim3(kConvThreads), smem, (cudaStream_t)stream, p);
+  } else {
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3(kConvThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (pdl_enabled()) {
+      attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[na].val.programmaticStreamSerializationAllowed = 1;
+      ++na;
+    }
+    int nctas = p.ntiles < sm_count() ? p.ntiles : sm_count();
+    if (cl == 2) {
+      attr[na].id = cudaLaunchAttributeClusterDimension;
+      attr[na].val.clusterDim.x = 2;
+      attr[na].val.clusterDim.y = 1;
+      attr[na].val.clusterDim.z = 1;
+      ++na;
+      // how many pairs the machine holds at one CTA per SM (queried once per shared-memory size)
+      static int max_clusters[64] = {0};
+      const int slot = (int)((smem >> 12) & 63);
+      int nc = max_clusters[slot];
+      if (nc == 0) {
+        cfg.gridDim = dim3(2 * sm_count());
+        cfg.attrs = attr;
+        cfg.numAttrs = na;
+        if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) != cudaSuccess || nc <= 0) {
+          cudaGetLastError();
+          nc = sm_count() / 2;
+        }
+        max_clusters[slot] = nc;
+      }
+      nctas = 2 * (p.ntiles < nc ? p.ntiles : nc);
+    }
+    cfg.gridDim = dim3((unsigned)nctas);
+    cfg.attrs = attr;
+    cfg.numAttrs = na;
+    cudaError_t le = cudaLaunchKernelEx(&cfg, kern, p);
+    if (le != cudaSuccess) return cuda_fail(le, "fsb_conv2d_nhwc: cudaLaunchKernelEx");
+  }
   FSB_CHECK_LAUNCH("fsb_conv2d_nhwc");
   return FSB_OK;
 }

@@ -239,7 +239,8 @@ class SelectiveUpdateBlock:
                 continue
             if epilogue == _lib.FSB_EPI_SCALE_RES and cout % 32:
                 continue
-            tile = nsteps * max(2 * bn, (16384 + 128 * bn) / 80.0) + 3000
+            pair = nsteps >= 24 and mt >= 2 and bn % 16 == 0  # csrc/conv.cu pair mode: half a weight tile per SM
+            tile = nsteps * max(2 * bn, (16384 + (64 if pair else 128) * bn) / 70.0) + 3000
             if nacc * bn > 256:          # accumulators not double-buffered: the epilogue is exposed
                 tile += 60 * bn
             t = -(-mt * (rows // bn) // sms) * tile
