@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""profiles/traffic.json from two `ncu --set full` captures (4 pairs per launch, as bench.py's default):
+"""profiles/traffic.json from two `ncu --set full` captures (8 pairs per launch, as bench.py's default):
     python tools/make_traffic.py <update-step capture .ncu-rep> <kernels 1-3 capture .ncu-rep>
 DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per launch; for the update block the sum over the
 tensor-core launches of ONE step (what bench.py's roofline.achieved is defined over)."""
@@ -37,7 +37,7 @@ for n, b, _ in k123:
     for k, v in names.items():
         if k in n:
             t[v] = b  # last launch of each kernel
-t["note"] = "bytes per launch at 4 pairs (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum); conv_umma_kernel = " \
+t["note"] = "bytes per launch at 8 pairs (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum); conv_umma_kernel = " \
             "sum over the tensor-core launches of one update step"
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 with open(os.path.join(root, "profiles", "traffic.json"), "w") as fh:
