@@ -96,8 +96,10 @@ class SelectiveUpdateBlock:
             raise RuntimeError("SelectiveUpdateBlock runs on CUDA only (no CPU path)")
         _lib.lib()  # fail loudly if the library is missing
         assert dtype in (torch.float16, torch.bfloat16)
+        import os as _os
         self.dtype = dtype
-        self.use_graph = use_graph
+        self.use_graph = use_graph and _os.environ.get("FSB_GRAPH", "1") != "0"
+        self.two_lanes = _os.environ.get("FSB_TWO_LANES", "1") != "0"  # side stream for encoder / mask head
         self.fused_mlp = fused_mlp  # False: pwconv1 / pwconv2 of the disparity head as two convolution launches
         self.bn = dict(DEFAULT_BLOCK_N)
         if block_n:
@@ -405,7 +407,12 @@ class SelectiveUpdateBlock:
         main = torch.cuda.current_stream()
         if lookup:
             plan.lookup()
+        single = not self.two_lanes
         for fn, lane in zip(plan.steps, plan.lanes):
+            if single:
+                if fn is not FORK and fn is not JOIN:
+                    fn()
+                continue
             if fn is FORK:
                 plan.side.wait_stream(main)
             elif fn is JOIN:
