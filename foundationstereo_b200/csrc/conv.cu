@@ -57,7 +57,8 @@ struct alignas(64) ConvParams {
   CUtensorMap wmap;
   CUtensorMap wmap_half;  // pair mode: box (64, block_n / 2), each CTA of a pair holds half of the weight tile
   CUtensorMap omap;  // 16-bit NHWC output, box (32 channels, bw, 32/bw, 1): the TMA-store epilogue of the tap kernel
-  int ostore;        // 1: plain epilogues leave through shared memory + cp.async.bulk.tensor stores
+  int ostore;        // 1: the epilogue leaves through shared memory + cp.async.bulk.tensor stores
+  CUtensorMap gmap[4];  // gate outputs: GATE_ZR z_l, z_s, rh_l, rh_s (32-channel boxes); GATE_Q [0] h16_out (16 ch), [1] h32_out (16 fp32)
   uint32_t steps[kMaxSteps];
   int nsteps;
   int H, W, tiles_x, tiles_y, tw_log2;
@@ -86,6 +87,32 @@ struct alignas(64) ConvParams {
 };
 
 // ------------------------------------------------------------------------------------ epilogue
+// One warp-level tensor store of a staged tile: rows = the warp's 32 pixels (lane = row), NU 16-byte units per row
+// (4: SWIZZLE_64B, unit u of row r at u ^ ((r >> 1) & 3); 2: no swizzle).  Rows outside the image are clipped by
+// the TMA unit.
+template <int NU>
+__device__ __forceinline__ void stage_and_store(uint8_t* stage, const uint4 (&units)[NU], const CUtensorMap* map, int c0,
+                                                int wx0, int wy0, int b) {
+  const int lane = threadIdx.x & 31;
+  uint8_t* row = stage + lane * (NU * 16);
+  const int sw = NU == 4 ? ((lane >> 1) & 3) : 0;
+#pragma unroll
+  for (int u = 0; u < NU; ++u) *reinterpret_cast<uint4*>(row + ((u ^ sw) << 4)) = units[u];
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  __syncwarp();
+  if (lane == 0) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+                 ::"l"(map), "r"(smem_u32(stage)), "r"(c0), "r"(wx0), "r"(wy0), "r"(b)
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  }
+}
+// before a warp rewrites its store tiles: the tensor stores issued so far have read them
+__device__ __forceinline__ void store_tiles_free() {
+  if ((threadIdx.x & 31) == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+  __syncwarp();
+}
+
 // One thread = one pixel (TMEM lane); `taddr` = lane quarter + first column of the pixel tile's
 // accumulators; the thread handles the 32-column (16 for GATE_Q) chunks c_first, c_first + c_stride, ...
 template <typename T, int EPI>
@@ -113,19 +140,30 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* 
         uint32_t v[32];
         tmem_ld32(taddr + a * p.BN + c, v);
         tmem_ld_wait();
-        if (!valid) continue;
+        const bool gstore = stage != nullptr && p.ostore;
+        if (!valid && !gstore) continue;
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = sigmoid_f(__uint_as_float(v[j]) + bias[c + j]);
-        if (c < half) {
-          store32<T>(zb + pix * p.hidden + nt * half + c, f);
-        } else {
-          const int ch = nt * half + (c - half);
+        const bool is_z = c < half;
+        const int ch = nt * half + (is_z ? c : c - half);
+        if (!is_z) {
           float h[32];
-          load32f(p.h32 + pix * p.hidden + ch, h);
+          load32f(p.h32 + pix * p.hidden + ch, h);  // pix = 0 for rows outside the image: a valid address, result clipped
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] *= h[j];
-          store32<T>(rb + pix * p.hidden + ch, f);
+        }
+        if (gstore) {
+          store_tiles_free();
+          uint4 units[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            units[u] = make_uint4(pack2<T>(f[8 * u], f[8 * u + 1]), pack2<T>(f[8 * u + 2], f[8 * u + 3]),
+                                  pack2<T>(f[8 * u + 4], f[8 * u + 5]), pack2<T>(f[8 * u + 6], f[8 * u + 7]));
+          const int wx0 = __shfl_sync(0xffffffffu, x, 0), wy0 = __shfl_sync(0xffffffffu, y, 0);
+          stage_and_store<4>(stage, units, &p.gmap[(is_z ? 0 : 2) + a], ch, wx0, wy0, b);
+        } else {
+          store32<T>((is_z ? zb : rb) + pix * p.hidden + ch, f);
         }
       }
     }
@@ -171,7 +209,8 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* 
       }
       if (c + 16 * c_stride < p.BN) load_step(c + 16 * c_stride);  // next step's operands, in flight during this one
       tmem_ld_wait();
-      if (!valid) continue;
+      const bool gstore = stage != nullptr && p.ostore;
+      if (!valid && !gstore) continue;
       const int ch = n0 + c;
       float* ho = p.h32_out + pix * p.hidden + ch;
       uint4* h16o = reinterpret_cast<uint4*>(reinterpret_cast<T*>(p.h16_out) + pix * p.hidden + ch);
@@ -184,6 +223,22 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* 
         const float hl = (1.f - zl) * h[j] + zl * ql;
         const float hs = (1.f - zs) * h[j] + zs * qs;
         h[j] = hs * att + hl * (1.f - att);
+      }
+      if (gstore) {
+        store_tiles_free();
+        uint4 u16[2], u32[4];
+#pragma unroll
+        for (int o = 0; o < 2; ++o)
+          u16[o] = make_uint4(pack2<T>(h[8 * o], h[8 * o + 1]), pack2<T>(h[8 * o + 2], h[8 * o + 3]),
+                              pack2<T>(h[8 * o + 4], h[8 * o + 5]), pack2<T>(h[8 * o + 6], h[8 * o + 7]));
+#pragma unroll
+        for (int o = 0; o < 4; ++o)
+          u32[o] = make_uint4(__float_as_uint(h[4 * o]), __float_as_uint(h[4 * o + 1]), __float_as_uint(h[4 * o + 2]),
+                              __float_as_uint(h[4 * o + 3]));
+        const int wx0 = __shfl_sync(0xffffffffu, x, 0), wy0 = __shfl_sync(0xffffffffu, y, 0);
+        stage_and_store<4>(stage, u32, &p.gmap[1], ch, wx0, wy0, b);
+        stage_and_store<2>(stage + 2048, u16, &p.gmap[0], ch, wx0, wy0, b);
+        continue;
       }
 #pragma unroll
       for (int o = 0; o < 2; ++o) {
@@ -208,32 +263,23 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, const float* 
         // u of row r at u ^ ((r >> 1) & 3), conflict free) and leave as ONE tensor store; rows outside the image
         // are clipped by the TMA unit.  Per-lane stores of 64 B at pixel stride touched 32 lines per instruction
         // and sustained ~1.6 TB/s (tools/conv_sweep.py: time of the 1x1 layers ~ 0.6 us per MB of output).
-        const int lane = threadIdx.x & 31;
-        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // previous store has read the tile
-        __syncwarp();
-        uint32_t pk[16];
+        store_tiles_free();
+        uint4 units[4];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          float a0 = __uint_as_float(v[2 * j]) + bias_s[c + 2 * j], a1 = __uint_as_float(v[2 * j + 1]) + bias_s[c + 2 * j + 1];
-          if constexpr (EPI == FSB_EPI_RELU) { a0 = fmaxf(a0, 0.f); a1 = fmaxf(a1, 0.f); }
-          if constexpr (EPI == FSB_EPI_GELU) { a0 = gelu_f(a0); a1 = gelu_f(a1); }
-          pk[j] = pack2<T>(a0, a1);
+        for (int u = 0; u < 4; ++u) {
+          uint32_t w[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int e = 8 * u + 2 * j;
+            float a0 = __uint_as_float(v[e]) + bias_s[c + e], a1 = __uint_as_float(v[e + 1]) + bias_s[c + e + 1];
+            if constexpr (EPI == FSB_EPI_RELU) { a0 = fmaxf(a0, 0.f); a1 = fmaxf(a1, 0.f); }
+            if constexpr (EPI == FSB_EPI_GELU) { a0 = gelu_f(a0); a1 = gelu_f(a1); }
+            w[j] = pack2<T>(a0, a1);
+          }
+          units[u] = make_uint4(w[0], w[1], w[2], w[3]);
         }
-        uint8_t* row = stage + lane * 64;
-        const int sw = (lane >> 1) & 3;
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-          *reinterpret_cast<uint4*>(row + ((u ^ sw) << 4)) = make_uint4(pk[4 * u], pk[4 * u + 1], pk[4 * u + 2], pk[4 * u + 3]);
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         const int wx0 = __shfl_sync(0xffffffffu, x, 0), wy0 = __shfl_sync(0xffffffffu, y, 0);  // lane 0 = the warp's first pixel
-        __syncwarp();
-        if (lane == 0) {
-          asm volatile(
-              "cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
-              ::"l"(&p.omap), "r"(smem_u32(stage)), "r"(p.ch_off + n), "r"(wx0), "r"(wy0), "r"(b)
-              : "memory");
-          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-        }
+        stage_and_store<4>(stage, units, &p.omap, p.ch_off + n, wx0, wy0, b);
         continue;
       }
       if (!valid || n >= p.Cout) continue;
@@ -534,7 +580,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
     const int r = q * 32 + lane;
     const int ty = r >> p.tw_log2, tx = r & (TW - 1);
     // 2 KB store tile of this warp, behind the operand ring
-    uint8_t* stage = p.ostore ? smem_raw + (smem_base - smem_u32(smem_raw)) + (size_t)S * stage_bytes + (size_t)(warp - 2) * 2048
+    uint8_t* stage = p.ostore ? smem_raw + (smem_base - smem_u32(smem_raw)) + (size_t)S * stage_bytes + (size_t)(warp - 2) * 3072
                               : nullptr;
     int it = 0;
     for (int wt = wfirst; wt < nwork; wt += wstep, ++it) {
@@ -925,11 +971,16 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   if (kper > n) kper = n;
   // the TMA-store epilogue (plain epilogues with a 16-bit output, decided below with the same condition) keeps
   // 16 KB of store tiles behind the ring
-  const bool ostore = !halo && a->out != nullptr && a->out_f32 == nullptr &&
-                      (epi == FSB_EPI_BIAS || epi == FSB_EPI_RELU || epi == FSB_EPI_GELU) && a->Cout >= 32;
+  const bool ostore_plain = !halo && a->out != nullptr && a->out_f32 == nullptr &&
+                            (epi == FSB_EPI_BIAS || epi == FSB_EPI_RELU || epi == FSB_EPI_GELU) && a->Cout >= 32;
+  // gate epilogues: only in pair mode, where a stage is small enough that the 24 KB of tiles do not cost a ring stage
+  static const int gate_store_env = [] { const char* e = getenv("FSB_GATE_STORE"); return e ? atoi(e) : 1; }();
+  const bool ostore_gate = !halo && cl == 2 && gate_store_env != 0 && (epi == FSB_EPI_GATE_ZR || epi == FSB_EPI_GATE_Q) &&
+                           a->hidden % 32 == 0;
+  const bool ostore = ostore_plain || ostore_gate;
   // Bytes in flight are what the operand feed runs on (a 144 KB ring was 10-25 % slower than a 192 KB one on the
   // same layer): 227 KB per SM - ~5 KB static - 1 KB alignment slack - 16 KB of store tiles leave 204 KB
-  const size_t ring_budget = (ostore ? 204 : 220) * 1024;
+  const size_t ring_budget = (ostore ? 196 : 220) * 1024;  // 24 KB of store tiles
   if (kper == 2 && ring_budget / (2 * step_bytes) < 3) kper = 1;  // at least three stages in flight
   if (stages <= 0) stages = (int)(ring_budget / (kper * step_bytes));
   if (stages > 8) stages = 8;
@@ -937,7 +988,7 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   if (stages < 1) stages = 1;
   p.stages = stages;
   p.kper = kper;
-  size_t smem = (size_t)stages * kper * step_bytes + 1024 + (ostore ? 8 * 2048 : 0);
+  size_t smem = (size_t)stages * kper * step_bytes + 1024 + (ostore ? 8 * 3072 : 0);
   if (halo) {
     // activation ring: 3 boxes of 34 KB; weight ring: what is left of 220 KB (2..8 tiles)
     const size_t b_bytes = (size_t)BN * kBK * 2;
@@ -975,13 +1026,31 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   p.ostore = 0;
   if (ostore) {
     const int bw = TW < 32 ? TW : 32, bh = 32 / bw;
-    cuuint64_t dims[4] = {(cuuint64_t)a->ld_out, (cuuint64_t)a->W, (cuuint64_t)a->H, (cuuint64_t)a->B};
-    cuuint64_t strides[3] = {(cuuint64_t)a->ld_out * 2, (cuuint64_t)a->ld_out * 2 * a->W, (cuuint64_t)a->ld_out * 2 * a->W * a->H};
-    cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, 1};
-    cuuint32_t estr[4] = {1, 1, 1, 1};
-    CUresult r = enc(&p.omap, dt, 4, a->out, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B,
-                     CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    FSB_REQUIRE(r == CUDA_SUCCESS, FSB_ERR_CUDA, "fsb_conv2d_nhwc: cuTensorMapEncodeTiled(out) -> %d", (int)r);
+    // (C, W, H, B) map of an NHWC output with a (cbox channels, bw, bh, 1) box = the 32 pixels of one epilogue warp
+    auto out_map = [&](CUtensorMap* m, void* ptr, int ld, int cbox, CUtensorMapDataType type, int esz, CUtensorMapSwizzle sw,
+                       const char* what) -> int {
+      cuuint64_t dims[4] = {(cuuint64_t)ld, (cuuint64_t)a->W, (cuuint64_t)a->H, (cuuint64_t)a->B};
+      cuuint64_t strides[3] = {(cuuint64_t)ld * esz, (cuuint64_t)ld * esz * a->W, (cuuint64_t)ld * esz * a->W * a->H};
+      cuuint32_t box[4] = {(cuuint32_t)cbox, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+      cuuint32_t estr[4] = {1, 1, 1, 1};
+      CUresult r = enc(m, type, 4, ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                       CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+      FSB_REQUIRE(r == CUDA_SUCCESS, FSB_ERR_CUDA, "fsb_conv2d_nhwc: cuTensorMapEncodeTiled(%s) -> %d", what, (int)r);
+      return FSB_OK;
+    };
+    int rc = FSB_OK;
+    if (ostore_plain) {
+      rc = out_map(&p.omap, a->out, a->ld_out, 32, dt, 2, CU_TENSOR_MAP_SWIZZLE_64B, "out");
+    } else if (epi == FSB_EPI_GATE_ZR) {
+      void* ptrs[4] = {a->z_l, a->z_s, a->rh_l, a->rh_s};
+      for (int i = 0; i < 4 && rc == FSB_OK; ++i)
+        if (ptrs[i] != nullptr) rc = out_map(&p.gmap[i], ptrs[i], a->hidden, 32, dt, 2, CU_TENSOR_MAP_SWIZZLE_64B, "gate output");
+    } else {
+      rc = out_map(&p.gmap[0], a->h16_out, a->hidden, 16, dt, 2, CU_TENSOR_MAP_SWIZZLE_NONE, "h16_out");
+      if (rc == FSB_OK)
+        rc = out_map(&p.gmap[1], a->h32_out, a->hidden, 16, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, CU_TENSOR_MAP_SWIZZLE_64B, "h32_out");
+    }
+    if (rc != FSB_OK) return rc;
     p.ostore = 1;
   }
   if (cl == 2) {
