@@ -84,28 +84,41 @@ __device__ __forceinline__ void cu_tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) 
 // conflict) and item (rq, j) is the same for every chunk: ||.||^2 partials stay in registers.
 // hi = x with the 13 low mantissa bits cleared (what the TF32 datapath reads), lo = x - hi (exact
 // in fp32; the datapath truncates it to TF32 again, leaving ~2^-20 relative).
-template <int NPROD, int ITEMS, bool VEC>
-__device__ __forceinline__ void cu_stage(uint8_t* hi, uint8_t* lo, const float* __restrict__ plane, size_t HW, int w0,
-                                         int W, int rows_pad, int c0, int C, float (&ss)[ITEMS][4]) {
+// The chunk is fetched in two halves so that the loads of chunk ch+1 are in flight while the MMAs of chunk ch run:
+// cu_load (global -> registers, issued right after the MMAs of the previous chunk) and cu_store (registers ->
+// swizzled hi/lo tiles, after the buffer is free).
+template <int ITEMS, bool VEC>
+__device__ __forceinline__ void cu_load(const float* __restrict__ plane, size_t HW, int w0, int W, int rows_pad, int c0,
+                                        int C, float (&v)[ITEMS][4][4]) {
 #pragma unroll
   for (int it = 0; it < ITEMS; ++it) {
     const int idx = threadIdx.x + it * kCuThreads;
     if (idx < rows_pad * 2) {  // (rows_pad / 4) pixel quads x 8 channel quads
       const int j = idx & 7, rq = idx >> 3;
       const int w = w0 + 4 * rq;
-      float v[4][4];  // [channel][pixel]
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
+      for (int q = 0; q < 4; ++q) {  // [channel][pixel]
         const int c = c0 + 4 * j + q;
         const float* src = plane + (size_t)c * HW + w;
         if (c < C && VEC && w + 3 < W) {
           const float4 t = __ldg(reinterpret_cast<const float4*>(src));
-          v[q][0] = t.x; v[q][1] = t.y; v[q][2] = t.z; v[q][3] = t.w;
+          v[it][q][0] = t.x; v[it][q][1] = t.y; v[it][q][2] = t.z; v[it][q][3] = t.w;
         } else {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) v[q][i] = (c < C && w + i < W) ? __ldg(src + i) : 0.f;
+          for (int i = 0; i < 4; ++i) v[it][q][i] = (c < C && w + i < W) ? __ldg(src + i) : 0.f;
         }
       }
+    }
+  }
+}
+template <int NPROD, int ITEMS>
+__device__ __forceinline__ void cu_store(uint8_t* hi, uint8_t* lo, int rows_pad, const float (&v)[ITEMS][4][4],
+                                         float (&ss)[ITEMS][4]) {
+#pragma unroll
+  for (int it = 0; it < ITEMS; ++it) {
+    const int idx = threadIdx.x + it * kCuThreads;
+    if (idx < rows_pad * 2) {
+      const int j = idx & 7, rq = idx >> 3;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int r = 4 * rq + i;
@@ -113,12 +126,13 @@ __device__ __forceinline__ void cu_stage(uint8_t* hi, uint8_t* lo, const float* 
         float h[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          ss[it][i] = fmaf(v[q][i], v[q][i], ss[it][i]);
-          h[q] = NPROD == 3 ? __uint_as_float(__float_as_uint(v[q][i]) & 0xffffe000u) : v[q][i];
+          ss[it][i] = fmaf(v[it][q][i], v[it][q][i], ss[it][i]);
+          h[q] = NPROD == 3 ? __uint_as_float(__float_as_uint(v[it][q][i]) & 0xffffe000u) : v[it][q][i];
         }
         *reinterpret_cast<float4*>(hi + off) = make_float4(h[0], h[1], h[2], h[3]);
         if (NPROD == 3)
-          *reinterpret_cast<float4*>(lo + off) = make_float4(v[0][i] - h[0], v[1][i] - h[1], v[2][i] - h[2], v[3][i] - h[3]);
+          *reinterpret_cast<float4*>(lo + off) =
+              make_float4(v[it][0][i] - h[0], v[it][1][i] - h[1], v[it][2][i] - h[2], v[it][3][i] - h[3]);
       }
     }
   }
@@ -178,6 +192,14 @@ corr_umma_kernel(const float* __restrict__ f1, const float* __restrict__ f2, Lev
   const bool vecA = (W1 & 3) == 0 && (reinterpret_cast<uintptr_t>(f1) & 15) == 0;
   const bool vecB = (W2 & 3) == 0 && (reinterpret_cast<uintptr_t>(f2) & 15) == 0;
   const int nchunks = (C + kCuKC - 1) / kCuKC;
+  float va[1][4][4], vb[2][4][4];
+  auto load_chunk = [&](int ch) {
+    if (vecA) cu_load<1, true>(a_plane, HW1, m0, W1, kCuBM, ch * kCuKC, C, va);
+    else      cu_load<1, false>(a_plane, HW1, m0, W1, kCuBM, ch * kCuKC, C, va);
+    if (vecB) cu_load<2, true>(b_plane, HW2, n0, W2, Npad, ch * kCuKC, C, vb);
+    else      cu_load<2, false>(b_plane, HW2, n0, W2, Npad, ch * kCuKC, C, vb);
+  };
+  load_chunk(0);
   for (int ch = 0; ch < nchunks; ++ch) {
     // nbuf == 2: double buffered (chunk ch waits for the MMAs of chunk ch-2); nbuf == 1: one buffer, so
     // two CTAs fit an SM and overlap each other instead (chunk ch waits for the MMAs of chunk ch-1)
@@ -188,10 +210,9 @@ corr_umma_kernel(const float* __restrict__ f1, const float* __restrict__ f2, Lev
       cu_mbar_wait(bar0, (ch - 1) & 1);
     }
     uint8_t* g = gbase + (size_t)buf * buf_bytes;
-    if (vecA) cu_stage<NPROD, 1, true>(g, g + off_alo, a_plane, HW1, m0, W1, kCuBM, ch * kCuKC, C, pa);
-    else      cu_stage<NPROD, 1, false>(g, g + off_alo, a_plane, HW1, m0, W1, kCuBM, ch * kCuKC, C, pa);
-    if (vecB) cu_stage<NPROD, 2, true>(g + off_bhi, g + off_blo, b_plane, HW2, n0, W2, Npad, ch * kCuKC, C, pb);
-    else      cu_stage<NPROD, 2, false>(g + off_bhi, g + off_blo, b_plane, HW2, n0, W2, Npad, ch * kCuKC, C, pb);
+    cu_store<NPROD, 1>(g, g + off_alo, kCuBM, va, pa);
+    cu_store<NPROD, 2>(g + off_bhi, g + off_blo, Npad, vb, pb);
+    if (ch + 1 < nchunks) load_chunk(ch + 1);  // in flight across the barrier, the MMAs and the wait above
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the MMA
     __syncthreads();
     if (tid == 0) {

@@ -59,23 +59,46 @@ nhwc_to_nchw_kernel(const float* __restrict__ src, float* __restrict__ dst, int 
 }
 
 // ------------------------------------------------------------------ pool2x / interp
-// one thread = 4 channels of one output pixel (float4 loads, 8-byte store)
-template <typename T>
+// one thread = V channels of one output pixel (V = 8 when C allows it: two float4 loads per tap, one 16-byte
+// store; V = 4: one float4 load, 8-byte store)
+template <typename T, int V>
+__device__ __forceinline__ void store_vec(T* p, const float (&a)[V]) {
+  if constexpr (V == 8) {
+    __align__(16) T t[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t[i] = from_f32<T>(a[i]);
+    *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(t);
+  } else {
+    Quad<T>::store(p, a[0], a[1], a[2], a[3]);
+  }
+}
+template <int V>
+__device__ __forceinline__ void load_vec(const float* p, float (&a)[V]) {
+#pragma unroll
+  for (int q = 0; q < V / 4; ++q) {
+    const float4 t = __ldg(reinterpret_cast<const float4*>(p) + q);
+    a[4 * q] = t.x; a[4 * q + 1] = t.y; a[4 * q + 2] = t.z; a[4 * q + 3] = t.w;
+  }
+}
+
+template <typename T, int V>
 __global__ void __launch_bounds__(256)
-pool2x_kernel(const float* __restrict__ src, T* __restrict__ dst, int C4, int H, int W, int Ho, int Wo,
+pool2x_kernel(const float* __restrict__ src, T* __restrict__ dst, int CV, int H, int W, int Ho, int Wo,
               size_t total) {
   pdl_launch_dependents();  // the next kernel may start its prologue
   pdl_wait();               // inputs written by the previous kernel are complete and visible
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
-  const int c4 = (int)(i % C4);
-  size_t r = i / C4;
+  const int cv = (int)(i % CV);
+  size_t r = i / CV;
   const int xo = (int)(r % Wo);
   r /= Wo;
   const int yo = (int)(r % Ho);
   const int b = (int)(r / Ho);
-  const float4* s = reinterpret_cast<const float4*>(src) + (size_t)b * H * W * C4 + c4;
-  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+  const float* s = src + ((size_t)b * H * W * CV + cv) * V;
+  float a[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) a[j] = 0.f;
 #pragma unroll
   for (int dy = -1; dy <= 1; ++dy) {
     const int y = 2 * yo + dy;
@@ -84,24 +107,28 @@ pool2x_kernel(const float* __restrict__ src, T* __restrict__ dst, int C4, int H,
     for (int dx = -1; dx <= 1; ++dx) {
       const int x = 2 * xo + dx;
       if (x < 0 || x >= W) continue;
-      const float4 v = __ldg(s + ((size_t)y * W + x) * C4);
-      a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+      float v[V];
+      load_vec<V>(s + ((size_t)y * W + x) * CV * V, v);
+#pragma unroll
+      for (int j = 0; j < V; ++j) a[j] += v[j];
     }
   }
   const float k = 1.f / 9.f;  // count_include_pad=True: the divisor is always 9
-  Quad<T>::store(dst + i * 4, a.x * k, a.y * k, a.z * k, a.w * k);
+#pragma unroll
+  for (int j = 0; j < V; ++j) a[j] *= k;
+  store_vec<T, V>(dst + i * V, a);
 }
 
-template <typename T>
+template <typename T, int V>
 __global__ void __launch_bounds__(256)
-resize_kernel(const float* __restrict__ src, T* __restrict__ dst, int C4, int Hs, int Ws, int Hd, int Wd,
+resize_kernel(const float* __restrict__ src, T* __restrict__ dst, int CV, int Hs, int Ws, int Hd, int Wd,
               float sy, float sx, size_t total) {
   pdl_launch_dependents();  // the next kernel may start its prologue
   pdl_wait();               // inputs written by the previous kernel are complete and visible
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
-  const int c4 = (int)(i % C4);
-  size_t r = i / C4;
+  const int cv = (int)(i % CV);
+  size_t r = i / CV;
   const int xo = (int)(r % Wd);
   r /= Wd;
   const int yo = (int)(r % Hd);
@@ -111,74 +138,95 @@ resize_kernel(const float* __restrict__ src, T* __restrict__ dst, int C4, int Hs
   const int y0 = min((int)fy, Hs - 1), x0 = min((int)fx, Ws - 1);
   const int y1 = min(y0 + 1, Hs - 1), x1 = min(x0 + 1, Ws - 1);
   const float ly = fy - (float)y0, lx = fx - (float)x0;
-  const float4* s = reinterpret_cast<const float4*>(src) + (size_t)b * Hs * Ws * C4 + c4;
-  const float4 v00 = __ldg(s + ((size_t)y0 * Ws + x0) * C4), v01 = __ldg(s + ((size_t)y0 * Ws + x1) * C4);
-  const float4 v10 = __ldg(s + ((size_t)y1 * Ws + x0) * C4), v11 = __ldg(s + ((size_t)y1 * Ws + x1) * C4);
+  const float* s = src + ((size_t)b * Hs * Ws * CV + cv) * V;
+  float v00[V], v01[V], v10[V], v11[V], o[V];
+  load_vec<V>(s + ((size_t)y0 * Ws + x0) * CV * V, v00);
+  load_vec<V>(s + ((size_t)y0 * Ws + x1) * CV * V, v01);
+  load_vec<V>(s + ((size_t)y1 * Ws + x0) * CV * V, v10);
+  load_vec<V>(s + ((size_t)y1 * Ws + x1) * CV * V, v11);
   const float w00 = (1.f - ly) * (1.f - lx), w01 = (1.f - ly) * lx, w10 = ly * (1.f - lx), w11 = ly * lx;
-  Quad<T>::store(dst + i * 4, w00 * v00.x + w01 * v01.x + w10 * v10.x + w11 * v11.x,
-                 w00 * v00.y + w01 * v01.y + w10 * v10.y + w11 * v11.y,
-                 w00 * v00.z + w01 * v01.z + w10 * v10.z + w11 * v11.z,
-                 w00 * v00.w + w01 * v01.w + w10 * v10.w + w11 * v11.w);
+#pragma unroll
+  for (int j = 0; j < V; ++j) o[j] = w00 * v00[j] + w01 * v01[j] + w10 * v10[j] + w11 * v11[j];
+  store_vec<T, V>(dst + i * V, o);
 }
 
 // ------------------------------------------------------------------ 7x7, one input channel
-// CTA = 32 (x) x kC1Rows (y) pixels; thread = (pixel column, 8 output channels) walking down the rows, so the
-// 49 x Cout weights (12.5 KB) are staged once per 256 pixels instead of once per 32 (the prologue was the kernel).
+// CTA = 32 (x) x kC1Rows (y) pixels, the 49 x Cout weights (12.5 KB) staged once per 256 pixels.  warp = one row,
+// lane = one pair of output channels, walking the row in strips of 8 pixels: per kernel row a lane reads the 14
+// inputs of the strip (broadcast 16-byte loads) and 7 weight pairs for 112 FMAs, so the kernel issues FMAs, not
+// shared-memory loads (thread = pixel x 8 channels needed 3 loads per 8 FMAs and ran at a third of this).
+// A warp stores 128 contiguous bytes per pixel.
 constexpr int kC1MaxCout = 64;
 constexpr int kC1Rows = 8;
+constexpr int kC1Strip = 8;
+constexpr int kC1PatchW = 40;  // 32 + 6 columns, padded so that every strip starts 16-byte aligned
+
+template <typename T> __device__ __forceinline__ void store_pair(T* p, float a, float b);
+template <> __device__ __forceinline__ void store_pair<__half>(__half* p, float a, float b) {
+  *reinterpret_cast<__half2*>(p) = __floats2half2_rn(a, b);
+}
+template <> __device__ __forceinline__ void store_pair<__nv_bfloat16>(__nv_bfloat16* p, float a, float b) {
+  *reinterpret_cast<__nv_bfloat162*>(p) = __floats2bfloat162_rn(a, b);
+}
+
 template <typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 conv7x7_c1_kernel(const float* __restrict__ disp, const float* __restrict__ weight, const float* __restrict__ bias,
                   T* __restrict__ out, int ld_out, int Cout, T* __restrict__ disp_out, int ld_disp, int disp_ch,
                   int H, int W) {
   pdl_launch_dependents();  // the next kernel may start its prologue
   __shared__ __align__(16) float wsm[49][kC1MaxCout];
-  __shared__ float patch[kC1Rows + 6][32 + 6];
+  __shared__ __align__(16) float patch[kC1Rows + 6][kC1PatchW];
   const int tid = threadIdx.x;
   const int x0 = blockIdx.x * 32, y0 = blockIdx.y * kC1Rows, b = blockIdx.z;
-  for (int i = tid; i < 49 * Cout; i += 256) {  // parameters: no kernel writes them
+  for (int i = tid; i < 49 * kC1MaxCout; i += 256) {  // parameters: no kernel writes them
     const int co = i / 49, t = i - co * 49;
-    wsm[t][co] = weight[i];
+    wsm[t][co] = co < Cout ? weight[i] : 0.f;
   }
   pdl_wait();  // inputs written by the previous kernel are complete and visible
   const float* d = disp + (size_t)b * H * W;
-  for (int i = tid; i < (kC1Rows + 6) * 38; i += 256) {
-    const int ry = i / 38, rx = i - ry * 38;
+  for (int i = tid; i < (kC1Rows + 6) * kC1PatchW; i += 256) {
+    const int ry = i / kC1PatchW, rx = i - ry * kC1PatchW;
     const int yy = y0 + ry - 3, xx = x0 + rx - 3;
-    patch[ry][rx] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? d[(size_t)yy * W + xx] : 0.f;
+    patch[ry][rx] = (rx < 38 && yy >= 0 && yy < H && xx >= 0 && xx < W) ? d[(size_t)yy * W + xx] : 0.f;
   }
   __syncthreads();
-  const int px = tid & 31, cg = tid >> 5;  // 8 channel groups
-  const int x = x0 + px;
-  if (x >= W) return;
-  for (int c0 = cg * 8; c0 < Cout; c0 += 64) {
-    float bv[8];
+  const int lane = tid & 31, r = tid >> 5;
+  const int y = y0 + r, c = 2 * lane;
+  if (y >= H) return;
+  const bool cok = c < Cout;  // idle channel lanes still carry the disparity copy below
+  const float b0 = cok ? __ldg(bias + c) : 0.f, b1 = cok ? __ldg(bias + c + 1) : 0.f;
+#pragma unroll 1
+  for (int s0 = 0; s0 < 32; s0 += kC1Strip) {
+    if (x0 + s0 >= W) break;
+    float acc[kC1Strip][2];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) bv[j] = (c0 + j < Cout) ? __ldg(bias + c0 + j) : 0.f;
-    for (int r = 0; r < kC1Rows; ++r) {
-      const int y = y0 + r;
-      if (y >= H) break;
-      float acc[8];
+    for (int j = 0; j < kC1Strip; ++j) { acc[j][0] = b0; acc[j][1] = b1; }
+#pragma unroll 1  // unrolled, ptxas hoists all 49 weight pairs and spills; 32 warps per SM cover the load latency
+    for (int ky = 0; ky < 7; ++ky) {
+      float in[kC1Strip + 8];  // 14 used
+      const float4* prow = reinterpret_cast<const float4*>(&patch[r + ky][s0]);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) acc[j] = bv[j];
+      for (int q = 0; q < (kC1Strip + 8) / 4; ++q) {
+        const float4 t = prow[q];
+        in[4 * q] = t.x; in[4 * q + 1] = t.y; in[4 * q + 2] = t.z; in[4 * q + 3] = t.w;
+      }
 #pragma unroll
-      for (int ky = 0; ky < 7; ++ky)
+      for (int kx = 0; kx < 7; ++kx) {
+        const float2 w = *reinterpret_cast<const float2*>(&wsm[ky * 7 + kx][c]);
 #pragma unroll
-        for (int kx = 0; kx < 7; ++kx) {
-          const float v = patch[r + ky][px + kx];
-          const float4 w0 = *reinterpret_cast<const float4*>(&wsm[ky * 7 + kx][c0]);
-          const float4 w1 = *reinterpret_cast<const float4*>(&wsm[ky * 7 + kx][c0 + 4]);
-          acc[0] = fmaf(v, w0.x, acc[0]); acc[1] = fmaf(v, w0.y, acc[1]);
-          acc[2] = fmaf(v, w0.z, acc[2]); acc[3] = fmaf(v, w0.w, acc[3]);
-          acc[4] = fmaf(v, w1.x, acc[4]); acc[5] = fmaf(v, w1.y, acc[5]);
-          acc[6] = fmaf(v, w1.z, acc[6]); acc[7] = fmaf(v, w1.w, acc[7]);
+        for (int j = 0; j < kC1Strip; ++j) {
+          acc[j][0] = fmaf(in[j + kx], w.x, acc[j][0]);
+          acc[j][1] = fmaf(in[j + kx], w.y, acc[j][1]);
         }
-      const size_t pix = ((size_t)b * H + y) * W + x;
-      T* o = out + pix * ld_out + c0;
-      Quad<T>::store(o, fmaxf(acc[0], 0.f), fmaxf(acc[1], 0.f), fmaxf(acc[2], 0.f), fmaxf(acc[3], 0.f));
-      Quad<T>::store(o + 4, fmaxf(acc[4], 0.f), fmaxf(acc[5], 0.f), fmaxf(acc[6], 0.f), fmaxf(acc[7], 0.f));
-      if (disp_out != nullptr && cg == 0 && c0 == 0) disp_out[pix * ld_disp + disp_ch] = from_f32<T>(patch[r + 3][px + 3]);
+      }
     }
+    const size_t pix0 = ((size_t)b * H + y) * W + x0 + s0;
+#pragma unroll
+    for (int j = 0; j < kC1Strip; ++j)
+      if (cok && x0 + s0 + j < W) store_pair<T>(out + (pix0 + j) * ld_out + c, fmaxf(acc[j][0], 0.f), fmaxf(acc[j][1], 0.f));
+    if (disp_out != nullptr && lane < kC1Strip && x0 + s0 + lane < W)
+      disp_out[(pix0 + lane) * ld_disp + disp_ch] = from_f32<T>(patch[r + 3][s0 + lane + 3]);
   }
 }
 
@@ -269,8 +317,8 @@ dwconv7x7_kernel(const T* __restrict__ x, const float* __restrict__ weight, cons
     float acc[kDwR][4];
 #pragma unroll
     for (int j = 0; j < kDwR; ++j) { acc[j][0] = bv.x; acc[j][1] = bv.y; acc[j][2] = bv.z; acc[j][3] = bv.w; }
-#pragma unroll 1
-    for (int ky = 0; ky < 7; ++ky) {
+#pragma unroll
+    for (int ky = 0; ky < 7; ++ky) {  // unrolled: the loads of row ky+1 are scheduled under the FMAs of row ky
       float4 in[kDwR + 6];
       const T* prow = patch + ((row + ky) * kDwPX + xs * kDwR) * kDwC + cq * 4;
 #pragma unroll
@@ -348,9 +396,14 @@ extern "C" int fsb_pool2x_nhwc(const float* src, void* dst, int B, int C, int H,
   FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && is16(dtype), FSB_ERR_ARG, "fsb_pool2x_nhwc: bad size or dtype");
   FSB_REQUIRE(C % 4 == 0 && aligned16(src), FSB_ERR_SHAPE, "fsb_pool2x_nhwc: C=%d must be a multiple of 4", C);
   const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
-  const size_t total = (size_t)B * Ho * Wo * (C / 4);
+  const int V = (C % 8 == 0 && aligned16(dst)) ? 8 : 4;
+  const size_t total = (size_t)B * Ho * Wo * (C / V);
   const unsigned blocks = (unsigned)((total + 255) / 256);
-  FSB_DISPATCH16(dtype, (launch_kernel(pool2x_kernel<T>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, src, (T*)dst, C / 4, H, W, Ho, Wo, total)));
+  if (V == 8) {
+    FSB_DISPATCH16(dtype, (launch_kernel(pool2x_kernel<T, 8>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, src, (T*)dst, C / 8, H, W, Ho, Wo, total)));
+  } else {
+    FSB_DISPATCH16(dtype, (launch_kernel(pool2x_kernel<T, 4>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, src, (T*)dst, C / 4, H, W, Ho, Wo, total)));
+  }
   FSB_CHECK_LAUNCH("fsb_pool2x_nhwc");
   return FSB_OK;
 }
@@ -364,9 +417,14 @@ extern "C" int fsb_resize_nhwc(const float* src, void* dst, int B, int C, int Hs
   FSB_REQUIRE(C % 4 == 0 && aligned16(src), FSB_ERR_SHAPE, "fsb_resize_nhwc: C=%d must be a multiple of 4", C);
   const float sy = Hd > 1 ? (float)(Hs - 1) / (float)(Hd - 1) : 0.f;
   const float sx = Wd > 1 ? (float)(Ws - 1) / (float)(Wd - 1) : 0.f;
-  const size_t total = (size_t)B * Hd * Wd * (C / 4);
+  const int V = (C % 8 == 0 && aligned16(dst)) ? 8 : 4;
+  const size_t total = (size_t)B * Hd * Wd * (C / V);
   const unsigned blocks = (unsigned)((total + 255) / 256);
-  FSB_DISPATCH16(dtype, (launch_kernel(resize_kernel<T>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, src, (T*)dst, C / 4, Hs, Ws, Hd, Wd, sy, sx, total)));
+  if (V == 8) {
+    FSB_DISPATCH16(dtype, (launch_kernel(resize_kernel<T, 8>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, src, (T*)dst, C / 8, Hs, Ws, Hd, Wd, sy, sx, total)));
+  } else {
+    FSB_DISPATCH16(dtype, (launch_kernel(resize_kernel<T, 4>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, src, (T*)dst, C / 4, Hs, Ws, Hd, Wd, sy, sx, total)));
+  }
   FSB_CHECK_LAUNCH("fsb_resize_nhwc");
   return FSB_OK;
 }
