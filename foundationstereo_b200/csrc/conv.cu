@@ -40,16 +40,18 @@ namespace fsb {
 
 constexpr int kConvThreads = 352;  // 11 warps
 constexpr int kWarpB = 10;           // weight producer warp
-constexpr int kMaxSteps = 112;
+constexpr int kMaxSteps = 144;
 constexpr int kMaxRows = 512;                // output rows (padded Cout) whose bias a persistent CTA keeps in shared memory
 constexpr int kBM = 128;
 constexpr int kBK = 64;                      // 16-bit elements per K step (128 B)
 constexpr int kATileBytes = kBM * kBK * 2;   // 16 KB
 
-// K-step word: bits 0-1 source, 2-3 dy+1, 4-5 dx+1, 6 accumulator, 8-15 channel chunk of the source
-__host__ __device__ inline uint32_t make_step(int src, int dy, int dx, int acc, int chunk) {
+// K-step word: bits 0-1 source, 2-3 dy+1, 4-5 dx+1, 6 accumulator, 8-15 channel chunk of the source, 16-23 the
+// 64-wide column block of the weight matrix (= the step's position in tap order), 24 empty slot (row-reuse mode)
+constexpr uint32_t kStepNull = 1u << 24;
+__host__ __device__ inline uint32_t make_step(int src, int dy, int dx, int acc, int chunk, int wblock) {
   return (uint32_t)src | ((uint32_t)(dy + 1) << 2) | ((uint32_t)(dx + 1) << 4) | ((uint32_t)acc << 6) |
-         ((uint32_t)chunk << 8);
+         ((uint32_t)chunk << 8) | ((uint32_t)wblock << 16);
 }
 
 struct alignas(64) ConvParams {
@@ -63,6 +65,7 @@ struct alignas(64) ConvParams {
   int nsteps;
   int H, W, tiles_x, tiles_y, tw_log2;
   int BN, nacc, tmem_cols, stages, kper;
+  int vr;  // row-reuse mode: a stage = ONE activation box of TH+2 rows serving the three vertical taps (+ the 1x1 segment)
   int nbuf, ntiles, ntiles_n, nbatch;  // persistent tap kernel: TMEM accumulator buffers, work items, N tiles per pixel tile
   int SA, SB;  // halo kernel: activation / weight ring depths
   uint32_t idesc;
@@ -404,7 +407,8 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const int kper = p.kper;
   const uint32_t b_tile_bytes = (uint32_t)(p.BN / CL) * (kBK * 2);  // this CTA's part of a weight tile
-  const uint32_t a_stage_bytes = (uint32_t)kper * kATileBytes;
+  const uint32_t a_row_bytes = (uint32_t)(kBK * 2) << p.tw_log2;  // one image row of the pixel tile
+  const uint32_t a_stage_bytes = p.vr ? a_row_bytes * (uint32_t)((kBM >> p.tw_log2) + 2) : (uint32_t)kper * kATileBytes;
   const uint32_t stage_bytes = a_stage_bytes + (uint32_t)kper * b_tile_bytes;
   const int S = p.stages;
   const uint32_t bar_full = smem_u32(&bars[0]);
@@ -480,6 +484,14 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
         if (elect_one()) {
           const uint32_t full = bar_full + 8 * s;
           uint32_t dst = smem_base + s * stage_bytes;
+          if (p.vr) {
+            // one box of TH + 2 image rows: the K steps of this stage are its three vertical taps
+            if (leader) mbar_expect_tx(full, (uint32_t)CL * a_stage_bytes);
+            const uint32_t st = p.steps[i];
+            const int src = st & 3, dx = (int)((st >> 4) & 3) - 1, chunk = (st >> 8) & 0xff;
+            if (CL == 2) tma_load_4d_2sm(dst, &p.amap[src], full, chunk * kBK, x0 + dx, y0 - 1, b);
+            else         tma_load_4d(dst, &p.amap[src], full, chunk * kBK, x0 + dx, y0 - 1, b);
+          } else {
           if (leader) mbar_expect_tx(full, (uint32_t)(CL * n) * kATileBytes);  // pair mode: the peer's tiles complete here too
           for (int j = 0; j < n; ++j) {
             const uint32_t st = p.steps[i + j];
@@ -487,6 +499,7 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
             if (CL == 2) tma_load_4d_2sm(dst, &p.amap[src], full, chunk * kBK, x0 + dx, y0 + dy, b);
             else         tma_load_4d(dst, &p.amap[src], full, chunk * kBK, x0 + dx, y0 + dy, b);
             dst += kATileBytes;
+          }
           }
         }
         if (++s == S) { s = 0; ph ^= 1; first_round = false; }
@@ -506,10 +519,16 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
         if (elect_one()) {
           const uint32_t full = bar_full + 8 * s;
           uint32_t dst = smem_base + s * stage_bytes + a_stage_bytes;
-          if (leader) mbar_expect_tx(full, (uint32_t)(CL * n) * b_tile_bytes);
+          int nload = 0;
+          for (int j = 0; j < n; ++j) nload += (p.steps[i + j] & kStepNull) ? 0 : 1;
+          if (leader) mbar_expect_tx(full, (uint32_t)(CL * nload) * b_tile_bytes);
           for (int j = 0; j < n; ++j) {
-            if (CL == 2) tma_load_2d_2sm(dst, &p.wmap_half, full, (i + j) * kBK, n0 + crank * (p.BN >> 1));
-            else         tma_load_2d(dst, &p.wmap, full, (i + j) * kBK, n0);
+            const uint32_t st = p.steps[i + j];
+            if (!(st & kStepNull)) {
+              const int k0 = (int)((st >> 16) & 0xff) * kBK;
+              if (CL == 2) tma_load_2d_2sm(dst, &p.wmap_half, full, k0, n0 + crank * (p.BN >> 1));
+              else         tma_load_2d(dst, &p.wmap, full, k0, n0);
+            }
             dst += b_tile_bytes;
           }
         }
@@ -537,8 +556,15 @@ conv_umma_kernel(const __grid_constant__ ConvParams p) {
         const uint32_t a_addr = smem_base + s * stage_bytes;
         uint64_t adesc = umma_desc_k128(a_addr);
         uint64_t bdesc = umma_desc_k128(a_addr + a_stage_bytes);
+        const uint64_t adesc0 = adesc;
         for (int j = 0; j < n; ++j) {
-          const int acc = (p.steps[i + j] >> 6) & 1;
+          const uint32_t st = p.steps[i + j];
+          if (st & kStepNull) {  // row-reuse mode: slot without a K step
+            bdesc += b_tile_bytes >> 4;
+            continue;
+          }
+          if (p.vr) adesc = adesc0 + (uint64_t)((((st >> 2) & 3) * a_row_bytes) >> 4);  // the tap's window of the box
+          const int acc = (st >> 6) & 1;
           const uint32_t d = d_base + (uint32_t)(acc * p.BN);
           const uint32_t first = (started >> acc) & 1;
           if (elect_one()) {
@@ -942,7 +968,8 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
           FSB_REQUIRE(si >= 0 && si < a->nsrc, FSB_ERR_ARG, "fsb_conv2d_nhwc: segment %d source index %d", s, si);
           for (int c = 0; c < a->src[si].C / kBK; ++c) {
             FSB_REQUIRE(n < kMaxSteps, FSB_ERR_SHAPE, "fsb_conv2d_nhwc: more than %d K steps", kMaxSteps);
-            p.steps[n++] = make_step(si, dy, dx, s, c);
+            p.steps[n] = make_step(si, dy, dx, s, c, n);
+            ++n;
           }
         }
   }
@@ -986,9 +1013,75 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
   if (stages > 8) stages = 8;
   while (stages > 1 && stages * kper * step_bytes > ring_budget) --stages;
   if (stages < 1) stages = 1;
+  size_t smem = (size_t)stages * kper * step_bytes + 1024 + (ostore ? 8 * 3072 : 0);
+  // Row-reuse mode (pair mode, 3x3 segment [+ a 1x1 segment over the same sources]): a stage holds ONE activation
+  // box of TH + 2 image rows per (dx, source, chunk) -- its three vertical taps are windows of that box, the 1x1
+  // segment reads the centre window of the dx = 0 box -- and the 3 (4) weight tiles that go with it.  An SM then
+  // ingests (TH+2)/(3 TH) of the activation bytes (20 KB instead of 48 KB per three K steps for 8 x 16 tiles), which
+  // takes the block_n = 128 layers from the L2-ingest bound to the MMA bound.
+  static const int vr_env = [] { const char* e = getenv("FSB_CONV_VR"); return e ? atoi(e) : 1; }();
+  bool vr = !halo && cl == 2 && vr_env != 0 && tw_log2 >= 3 && a->seg[0].ksize == 3 && (a->nseg == 1 || a->seg[1].ksize == 1);
+  if (vr) {
+    const int nslots = a->nseg == 2 ? 4 : 3;
+    const size_t vr_stage = (size_t)(TH + 2) * TW * kBK * 2 + (size_t)nslots * (BN / cl) * kBK * 2;
+    int chs = 0;
+    for (int k = 0; k < a->seg[0].nsrc; ++k) chs += a->src[a->seg[0].src[k]].C / kBK;
+    // 1x1 segment: a (source, chunk) that the 3x3 segment reads too rides in the fourth slot of that dx = 0 group;
+    // one it does not read (the GRU q gate: r_small * h) gets a group of its own
+    int ride[FSB_MAX_SRC], own_chunks = 0;  // ride[i] = weight column block of source i in the 1x1 segment, -1: none
+    for (int i = 0; i < FSB_MAX_SRC; ++i) ride[i] = -1;
+    if (a->nseg == 2) {
+      int off = 9 * chs;
+      for (int k = 0; k < a->seg[1].nsrc; ++k) {
+        const int si = a->seg[1].src[k];
+        ride[si] = off;
+        off += a->src[si].C / kBK;
+        bool shared = false;
+        for (int k0 = 0; k0 < a->seg[0].nsrc; ++k0) shared = shared || a->seg[0].src[k0] == si;
+        if (!shared) own_chunks += a->src[si].C / kBK;
+      }
+    }
+    const int vr_steps = (3 * chs + own_chunks) * nslots;
+    if (ring_budget / vr_stage < 3 || vr_steps > kMaxSteps) {
+      vr = false;
+    } else {
+      int m = 0;
+      bool in_seg0[FSB_MAX_SRC] = {false, false, false, false};
+      for (int dx = -1; dx <= 1; ++dx) {
+        int choff = 0;
+        for (int k = 0; k < a->seg[0].nsrc; ++k) {
+          const int si = a->seg[0].src[k], nch = a->src[si].C / kBK;
+          in_seg0[si] = true;
+          for (int c = 0; c < nch; ++c) {
+            for (int dy = -1; dy <= 1; ++dy)  // weight column block = the step's position in tap order
+              p.steps[m++] = make_step(si, dy, dx, 0, c, ((dy + 1) * 3 + (dx + 1)) * chs + choff + c);
+            if (nslots == 4)
+              p.steps[m++] = (dx == 0 && ride[si] >= 0) ? make_step(si, 0, 0, 1, c, ride[si] + c)
+                                                        : (make_step(si, 0, dx, 0, c, 0) | kStepNull);
+          }
+          choff += nch;
+        }
+      }
+      if (a->nseg == 2)
+        for (int k = 0; k < a->seg[1].nsrc; ++k) {
+          const int si = a->seg[1].src[k];
+          if (in_seg0[si]) continue;
+          for (int c = 0; c < a->src[si].C / kBK; ++c) {
+            p.steps[m++] = make_step(si, 0, 0, 1, c, ride[si] + c);  // the centre window of its own box
+            for (int j = 1; j < nslots; ++j) p.steps[m++] = make_step(si, 0, 0, 1, c, 0) | kStepNull;
+          }
+        }
+      p.nsteps = m;
+      kper = nslots;
+      stages = a->stages > 0 ? a->stages : (int)(ring_budget / vr_stage);
+      if (stages > 8) stages = 8;
+      while (stages > 1 && stages * vr_stage > ring_budget) --stages;
+      smem = (size_t)stages * vr_stage + 1024 + (ostore ? 8 * 3072 : 0);
+    }
+  }
+  p.vr = vr ? 1 : 0;
   p.stages = stages;
   p.kper = kper;
-  size_t smem = (size_t)stages * kper * step_bytes + 1024 + (ostore ? 8 * 3072 : 0);
   if (halo) {
     // activation ring: 3 boxes of 34 KB; weight ring: what is left of 220 KB (2..8 tiles)
     const size_t b_bytes = (size_t)BN * kBK * 2;
@@ -1006,7 +1099,7 @@ extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t s
     const cuuint64_t C = (cuuint64_t)a->src[i].C;
     cuuint64_t dims[4] = {C, (cuuint64_t)a->W, (cuuint64_t)a->H, (cuuint64_t)a->B};
     cuuint64_t strides[3] = {C * 2, C * 2 * a->W, C * 2 * a->W * a->H};
-    cuuint32_t box[4] = {(cuuint32_t)kBK, (cuuint32_t)TW, (cuuint32_t)(halo ? kHaloRows : TH), 1};
+    cuuint32_t box[4] = {(cuuint32_t)kBK, (cuuint32_t)TW, (cuuint32_t)(halo ? kHaloRows : (vr ? TH + 2 : TH)), 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = enc(&p.amap[i], dt, 4, const_cast<void*>(a->src[i].ptr), dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
