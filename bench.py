@@ -317,9 +317,18 @@ def run_b200(args):
             "geo_lookup": time_kernel(torch, lambda: ops.geo_lookup_nhwc16(geo.geo_levels, geo.corr_levels, dev["disp"], coords, r, plan_b.corr16), 20, flush),
             "geo_lookup_fp32_nchw": time_kernel(torch, lambda: geo(dev["disp"], coords), 20, flush),
         }
+        # the steps either side of the loop: not part of the timed step, reported beside it
+        cls_logits = torch.randn(c["B"], D, c["H"], c["W"], device=device)
+        spx_logits = torch.randn(c["B"], 9, 4 * c["H"], 4 * c["W"], device=device)
+        kern_ms["softmax_disparity_regression"] = time_kernel(torch, lambda: ops.disparity_regression(cls_logits, True), 20, flush)
+        kern_ms["softmax_context_upsample"] = time_kernel(torch, lambda: ops.context_upsample(dev["disp"], spx_logits, True, 4.0), 20, flush)
         per_step = {"volume_gwc_concat": 1, "corr_pyramid": 1, "corr_pyramid_fp32_cuda_cores": 0, "geo_pyramid": 1,
-                    "geo_lookup": c["iters"], "geo_lookup_fp32_nchw": 0}
+                    "geo_lookup": c["iters"], "geo_lookup_fp32_nchw": 0, "softmax_disparity_regression": 0,
+                    "softmax_context_upsample": 0}
         alg = algorithmic_bytes(c)
+        px_ = c["B"] * c["H"] * c["W"]
+        alg["softmax_disparity_regression"] = px_ * (D + 1) * 4
+        alg["softmax_context_upsample"] = px_ * (4 + 16 * (9 + 1) * 4)
         alg["corr_pyramid_fp32_cuda_cores"] = alg["corr_pyramid"]
         alg["geo_lookup_fp32_nchw"] = alg["geo_lookup"]
         # the fused lookup writes 16-bit NHWC rows of Cpad channels instead of fp32 NCHW

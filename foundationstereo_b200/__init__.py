@@ -9,6 +9,8 @@ eager fallback: importing the ops without the built library raises.
 """
 from ._lib import FsbError, launch_count, lib  # noqa: F401
 from .submodule import build_gwc_volume, build_concat_volume, build_combined_volume  # noqa: F401
+from .submodule import (disparity_regression, softmax_disparity_regression, context_upsample,  # noqa: F401
+                        softmax_context_upsample)
 from .geometry import Combined_Geo_Encoding_Volume  # noqa: F401
 from .update import SelectiveUpdateBlock  # noqa: F401
 from .hotpath import StereoHotPath  # noqa: F401
@@ -18,5 +20,6 @@ from .patch import install, install_update_block, uninstall  # noqa: F401
 __all__ = [
     "build_gwc_volume", "build_concat_volume", "build_combined_volume", "Combined_Geo_Encoding_Volume",
     "SelectiveUpdateBlock", "StereoHotPath", "install", "install_update_block", "uninstall", "FsbError",
-    "launch_count", "lib",
+    "launch_count", "lib", "disparity_regression", "softmax_disparity_regression", "context_upsample",
+    "softmax_context_upsample",
 ]

@@ -205,3 +205,47 @@ def geo_pyramid_into(volume: torch.Tensor, levels: List[torch.Tensor]) -> None:
     for l, t in enumerate(levels):
         assert t.shape == (B * H * W, D >> l, Cg) and t.dtype == torch.float32 and t.is_contiguous()
     check(lib().fsb_geo_pyramid(volume.data_ptr(), level_array(levels), B, Cg, D, H, W, len(levels), _stream()))
+
+
+# ----------------------------------------------------------------------------------------
+# the steps either side of the refinement loop (csrc/post.cu)
+# ----------------------------------------------------------------------------------------
+@torch.library.custom_op("fsb200::disparity_regression", mutates_args=(), device_types="cuda")
+def disparity_regression(x: torch.Tensor, logits: bool) -> torch.Tensor:
+    """(B,D,H,W) -> (B,1,H,W): sum_d x*d (core/submodule.py:431-435); ``logits`` fuses the
+    softmax over D of core/foundation_stereo.py:218 (result fp32)."""
+    _need_cuda(x)
+    assert x.dim() == 4
+    x = x.contiguous()
+    B, D, H, W = x.shape
+    out = torch.empty((B, 1, H, W), dtype=torch.float32 if logits else x.dtype, device=x.device)
+    check(lib().fsb_disparity_regression(x.data_ptr(), out.data_ptr(), B, D, H, W, int(logits), _DTYPE[x.dtype],
+                                         _stream()))
+    return out
+
+
+@disparity_regression.register_fake
+def _(x, logits):
+    B, D, H, W = x.shape
+    return x.new_empty((B, 1, H, W), dtype=torch.float32 if logits else x.dtype)
+
+
+@torch.library.custom_op("fsb200::context_upsample", mutates_args=(), device_types="cuda")
+def context_upsample(disp_low: torch.Tensor, weights: torch.Tensor, logits: bool, scale: float) -> torch.Tensor:
+    """(B,1,h,w) fp32 x (B,9,4h,4w) -> (B,4h,4w) fp32 (core/submodule.py:456-468); ``logits`` fuses
+    the softmax over the 9 weights, ``scale`` multiplies the disparity (core/foundation_stereo.py:188-189)."""
+    _need_cuda(disp_low, weights)
+    B, c, h, w = disp_low.shape
+    assert c == 1 and weights.shape == (B, 9, 4 * h, 4 * w), (disp_low.shape, weights.shape)
+    disp_low = disp_low.float().contiguous()
+    weights = weights.contiguous()
+    out = torch.empty((B, 4 * h, 4 * w), dtype=torch.float32, device=disp_low.device)
+    check(lib().fsb_context_upsample(disp_low.data_ptr(), weights.data_ptr(), out.data_ptr(), B, h, w, int(logits),
+                                     float(scale), _DTYPE[weights.dtype], _stream()))
+    return out
+
+
+@context_upsample.register_fake
+def _(disp_low, weights, logits, scale):
+    B, _, h, w = disp_low.shape
+    return disp_low.new_empty((B, 4 * h, 4 * w), dtype=torch.float32)

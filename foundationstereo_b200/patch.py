@@ -5,7 +5,9 @@ The reference has no plugin API; its seam is Python name binding:
     :18 imports Combined_Geo_Encoding_Volume by name -> the names live in that module's
     globals and are looked up at call time (:207, :210, :229);
   * the update block is the attribute ``model.update_block`` (:137), called at :240; its
-    parameters must stay where they are so checkpoints load (scripts/run_demo.py:125).
+    parameters must stay where they are so checkpoints load (scripts/run_demo.py:125);
+  * the steps either side of the loop, disparity_regression (:220) and context_upsample (:189),
+    come in through the same star import.
 """
 from __future__ import annotations
 
@@ -14,13 +16,15 @@ import types
 from typing import Optional
 
 from .geometry import Combined_Geo_Encoding_Volume
-from .submodule import build_concat_volume, build_gwc_volume
+from .submodule import (build_concat_volume, build_gwc_volume, context_upsample, disparity_regression,
+                        softmax_context_upsample)
 from .update import SelectiveUpdateBlock
 
 _SAVED = {}
 
 
-def install(model=None, modules: Optional[list] = None, fused_lookup: bool = True) -> None:
+def install(model=None, modules: Optional[list] = None, fused_lookup: bool = True,
+            fused_upsample: bool = False) -> None:
     """Rebind the three names in every loaded reference module that holds them and, if a
     FoundationStereo ``model`` is given, route ``model.update_block.forward`` through
     SelectiveUpdateBlock built from the module's own parameters.
@@ -29,7 +33,11 @@ def install(model=None, modules: Optional[list] = None, fused_lookup: bool = Tru
     straight into the update block's 16-bit NHWC input buffer and returns a channels-last
     view of it -- the unchanged caller (core/foundation_stereo.py:238-240) only hands that
     tensor on to ``update_block``.  ``fused_lookup=False`` returns the reference's fp32
-    (B, L*K*(Cg+1), H, W) tensor."""
+    (B, L*K*(Cg+1), H, W) tensor.
+
+    ``fused_upsample`` (opt-in, needs a model) swaps ``model.upsample_disp``
+    (core/foundation_stereo.py:183-191) for a method that runs the two spx networks as before and
+    then ONE kernel for softmax over the 9 weights + ``disp*4`` + convex upsampling."""
     geo_cls = Combined_Geo_Encoding_Volume
     if model is not None:
         engine_of = install_update_block(model.update_block)
@@ -40,10 +48,14 @@ def install(model=None, modules: Optional[list] = None, fused_lookup: bool = Tru
                                      nhwc16_out=lambda B, H, W: engine_of().corr_buffer(B, H, W))
             FusedGeoEncodingVolume.__name__ = "Combined_Geo_Encoding_Volume"
             geo_cls = FusedGeoEncodingVolume
+        if fused_upsample:
+            install_upsample(model)
     names = {
         "build_gwc_volume": build_gwc_volume,
         "build_concat_volume": build_concat_volume,
         "Combined_Geo_Encoding_Volume": geo_cls,
+        "disparity_regression": disparity_regression,
+        "context_upsample": context_upsample,
     }
     if modules is None:
         modules = [m for n, m in list(sys.modules.items())
@@ -77,14 +89,33 @@ def install_update_block(update_block):
     return engine
 
 
+def install_upsample(model) -> None:
+    """``model.upsample_disp`` (core/foundation_stereo.py:183-191) with its tail fused: the spx
+    networks stay the model's own modules, softmax + ``disp*4.`` + context_upsample are one launch."""
+    import torch
+
+    def fast_upsample_disp(self, disp, mask_feat_4, stem_2x):
+        with torch.autocast("cuda", enabled=bool(self.args.mixed_precision)):
+            xspx = self.spx_2_gru(mask_feat_4, stem_2x)
+            spx_pred = self.spx_gru(xspx)
+        return softmax_context_upsample(disp.float(), spx_pred, 4.0)
+
+    _SAVED.setdefault(("upsample_disp", id(model)), model.upsample_disp)
+    model.upsample_disp = types.MethodType(fast_upsample_disp, model)
+
+
 def uninstall(model=None) -> None:
     for (modname, name), fn in list(_SAVED.items()):
-        if modname == "update_block":
+        if modname in ("update_block", "upsample_disp"):
             continue
         mod = sys.modules.get(modname)
         if mod is not None:
             setattr(mod, name, fn)
     if model is not None:
-        key = ("update_block", id(model.update_block))
+        ub = getattr(model, "update_block", None)
+        key = ("update_block", id(ub))
+        if ub is not None and key in _SAVED:
+            ub.forward = _SAVED.pop(key)
+        key = ("upsample_disp", id(model))
         if key in _SAVED:
-            model.update_block.forward = _SAVED.pop(key)
+            model.upsample_disp = _SAVED.pop(key)

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define FSB_VERSION 110 /* major*100 + minor */
+#define FSB_VERSION 120 /* major*100 + minor */
 #define FSB_MAX_LEVELS 6
 
 typedef void* fsb_stream_t; /* cudaStream_t */
@@ -246,6 +246,22 @@ int fsb_edgenext_mlp(const void* x, const void* w1, const float* b1, const void*
                      fsb_stream_t stream);
 /* y += x (fp32, n elements): the disparity update of core/foundation_stereo.py:242 */
 int fsb_axpy_f32(float* y, const float* x, size_t n, fsb_stream_t stream);
+
+
+/* ---- the steps either side of the refinement loop (HBM-bound streams) ------------ */
+/* disparity_regression (core/submodule.py:431-435): out[b,0,h,w] = sum_d x[b,d,h,w] * d.
+ *   x (B,D,H,W) of `dtype`; logits = 0: x are probabilities, out has the dtype of x (the reference's result dtype);
+ *   logits = 1: x are the classifier's logits and the softmax over D of core/foundation_stereo.py:218 is fused in
+ *   (one pass, running max / sum), out is fp32 (softmax runs in fp32 under autocast).                           */
+int fsb_disparity_regression(const void* x, void* out, int B, int D, int H, int W, int logits, int dtype,
+                             fsb_stream_t stream);
+/* context_upsample (core/submodule.py:456-468): convex 4x upsampling,
+ *   out[b,Y,X] = sum_{k=ky*3+kx} scale * disp_low[b, Y/4+ky-1, X/4+kx-1] * weights[b,k,Y,X]   (zero outside the image).
+ *   disp_low (B,1,h,w) fp32; weights (B,9,4h,4w) of `dtype`; out (B,4h,4w) fp32.
+ *   logits = 1: weights are the logits of spx_gru and the softmax over the 9 of core/foundation_stereo.py:188 is
+ *   fused in; scale = 4 folds the `disp*4.` of :189 (pass 1 for the reference's call).  weights/out 16-byte aligned. */
+int fsb_context_upsample(const float* disp_low, const void* weights, float* out, int B, int h, int w, int logits,
+                         float scale, int dtype, fsb_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -32,6 +32,10 @@ from .hotpath import (  # noqa: F401
     pool2x,
     resize_like,
     refine,
+    disparity_regression,
+    softmax_disparity_regression,
+    context_upsample,
+    upsample_disp_tail,
 )
 from .params import make_update_block_params, update_block_param_shapes  # noqa: F401
 from .inputs import make_inputs  # noqa: F401

@@ -297,3 +297,43 @@ def refine(
         net, mask, delta = update_block(p, net, inp, feat, disp, att)
         disp = disp + delta.float()
     return disp, mask, net
+
+
+# --------------------------------------------------------------------------
+# the steps either side of the loop  (core/submodule.py:431-435, 456-468;
+# core/foundation_stereo.py:183-191, 218-220)
+# --------------------------------------------------------------------------
+def disparity_regression(prob: Tensor) -> Tensor:
+    """Expected disparity (core/submodule.py:431-435): (B,D,H,W) -> (B,1,H,W),
+    out = sum_d prob[:,d] * d in the dtype of ``prob``."""
+    D = prob.shape[1]
+    d = torch.arange(D, dtype=prob.dtype).reshape(1, D, 1, 1)
+    return (prob * d).sum(1, keepdim=True)
+
+
+def softmax_disparity_regression(logits: Tensor) -> Tensor:
+    """core/foundation_stereo.py:218-220: softmax over the disparity axis, then
+    the expected disparity; fp32 (softmax runs in fp32 under autocast)."""
+    return disparity_regression(torch.softmax(logits.float(), 1))
+
+
+def context_upsample(disp_low: Tensor, weights: Tensor) -> Tensor:
+    """Convex 4x upsampling (core/submodule.py:456-468): every full-resolution
+    pixel (Y,X) is a weighted sum of the 3x3 neighbourhood (zero padded, row-major
+    k = ky*3+kx) of its low-resolution pixel (Y//4, X//4).  (b,1,h,w),(b,9,4h,4w)
+    -> (b,4h,4w)."""
+    b, _, h, w = disp_low.shape
+    pad = F.pad(disp_low[:, 0], (1, 1, 1, 1))
+    out = torch.zeros((b, 4 * h, 4 * w), dtype=torch.result_type(disp_low, weights))
+    for ky in range(3):
+        for kx in range(3):
+            nb = pad[:, ky : ky + h, kx : kx + w]
+            nb = nb.repeat_interleave(4, 1).repeat_interleave(4, 2)
+            out = out + nb * weights[:, ky * 3 + kx]
+    return out
+
+
+def upsample_disp_tail(disp: Tensor, spx_logits: Tensor) -> Tensor:
+    """Tail of FoundationStereo.upsample_disp (core/foundation_stereo.py:188-191):
+    softmax over the 9 weights, disparity scaled by 4, convex upsampling -> (b,1,4h,4w) fp32."""
+    return context_upsample(disp.float() * 4.0, torch.softmax(spx_logits.float(), 1)).unsqueeze(1).float()

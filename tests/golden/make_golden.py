@@ -133,6 +133,28 @@ def main():
         save("refine_3it", seed_params=3, seed_inputs=5, disp1=trace[0], disp2=trace[1], disp3=trace[2],
              mask=mask, net0=net[0])
 
+    # ---- the steps either side of the loop: disparity_regression, context_upsample (+ their softmaxes)
+    import torch.nn.functional as F
+    from core.submodule import disparity_regression, context_upsample
+    g = torch.Generator().manual_seed(23)
+    B, D, H, W = 2, 13, 5, 7          # odd H*W: the scalar path
+    logits = 3.0 * torch.randn(B, D, H, W, generator=g)
+    logits[0, :, 0, 0] = 0.0          # uniform distribution
+    logits[0, 5, 0, 1] = 60.0         # one-hot
+    prob = F.softmax(logits, 1)
+    B2, D2, H2, W2 = 1, 24, 4, 8      # H*W % 4 == 0: the vector path
+    logits2 = 2.0 * torch.randn(B2, D2, H2, W2, generator=g)
+    prob2 = F.softmax(logits2, 1)
+    h, w = 3, 5
+    disp = 20.0 * torch.rand(B, 1, h, w, generator=g)
+    spx = 2.0 * torch.randn(B, 9, 4 * h, 4 * w, generator=g)
+    wts = F.softmax(spx, 1)
+    save("post", logits=logits, prob=prob, reg=disparity_regression(prob, D),
+         logits2=logits2, prob2=prob2, reg2=disparity_regression(prob2, D2),
+         reg2_f16=disparity_regression(prob2.half(), D2),
+         disp=disp, spx=spx, wts=wts, up=context_upsample(disp, wts),
+         up_tail=context_upsample(disp * 4., wts).unsqueeze(1))
+
 
 if __name__ == "__main__":
     main()

@@ -38,6 +38,8 @@ def test_version_and_error_channel(lib):
     assert b"NULL" in lib.fsb_last_error()
     rc = lib.fsb_geo_lookup(None, None, None, None, None, 1, 28, 8, 2, 2, 2, 2, 4, 0, None)
     assert rc == -1
+    assert lib.fsb_disparity_regression(None, None, 1, 8, 2, 2, 0, 0, None) == -1
+    assert lib.fsb_context_upsample(None, None, None, 1, 2, 2, 0, 1.0, 0, None) == -1
 
 
 def test_python_ops_refuse_cpu_tensors():
@@ -58,7 +60,10 @@ def test_patch_rebinds_reference_names():
     mod = types.ModuleType("core.foundation_stereo")
     sentinel = object()
     mod.build_gwc_volume = mod.build_concat_volume = mod.Combined_Geo_Encoding_Volume = sentinel
+    mod.disparity_regression = mod.context_upsample = sentinel
     fsb.install(modules=[mod])
     assert mod.build_gwc_volume is fsb.build_gwc_volume
     assert mod.build_concat_volume is fsb.build_concat_volume
     assert mod.Combined_Geo_Encoding_Volume is fsb.Combined_Geo_Encoding_Volume
+    assert mod.disparity_regression is fsb.disparity_regression
+    assert mod.context_upsample is fsb.context_upsample

@@ -67,3 +67,18 @@ def test_param_shapes_match_reference_listing():
     shapes = oracle.update_block_param_shapes(2, 4, 128, 28)
     n = sum(int(torch.tensor(s).prod()) for s in shapes.values())
     assert n == 16_348_640
+
+
+def test_post_steps():
+    """disparity_regression / context_upsample and their fused-softmax forms against the reference's
+    outputs (core/submodule.py:431-435, 456-468; core/foundation_stereo.py:188-189, 218-220)."""
+    g = load_golden("post")
+    assert torch.equal(oracle.disparity_regression(g["prob"]), g["reg"])
+    assert torch.equal(oracle.disparity_regression(g["prob2"]), g["reg2"])
+    r16 = oracle.disparity_regression(g["prob2"].half())
+    assert r16.dtype == torch.float16 and rel_err(r16, g["reg2_f16"]) <= 2e-3
+    assert rel_err(oracle.softmax_disparity_regression(g["logits"]), g["reg"]) <= 1e-6
+    up = oracle.context_upsample(g["disp"], g["wts"])
+    assert up.shape == g["up"].shape and rel_err(up, g["up"]) <= 1e-6
+    tail = oracle.upsample_disp_tail(g["disp"], g["spx"])
+    assert tail.shape == g["up_tail"].shape and rel_err(tail, g["up_tail"]) <= 1e-6

@@ -20,7 +20,11 @@ coords = torch.arange(W, dtype=torch.float32, device="cuda").reshape(1, 1, W, 1)
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
 Cpad = (L * (2 * r + 1) * 29 + 63) // 64 * 64
 out16 = torch.zeros(B, H, W, Cpad, dtype=torch.float16, device="cuda")
+cls_logits = torch.randn(B, D, H, W, device="cuda")
+spx_logits = torch.randn(B, 9, 4 * H, 4 * W, device="cuda")
 for _ in range(reps):
+    ops.disparity_regression(cls_logits, True)
+    ops.context_upsample(d["disp"], spx_logits, True, 4.0)
     ops.combined_volume(d["fl"], d["fr"], d["pl"], d["pr"], D, 8)
     geo = fsb.Combined_Geo_Encoding_Volume(d["fl"], d["fr"], d["volume"], num_levels=L, dx=dx)
     out = geo(d["disp"], coords)
