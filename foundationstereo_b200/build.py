@@ -49,19 +49,59 @@ def is_stale() -> bool:
         return fh.read().strip() != _fingerprint()
 
 
+def _compile_one(nvcc: str, src: str, obj: str, deps_hash: str):
+    """One .cu -> .o (cached by the hash of the source, the shared headers and the flags)."""
+    tag = obj + ".hash"
+    h = hashlib.sha256(deps_hash.encode())
+    with open(src, "rb") as fh:
+        h.update(fh.read())
+    digest = h.hexdigest()
+    if os.path.exists(obj) and os.path.exists(tag):
+        with open(tag) as fh:
+            if fh.read().strip() == digest:
+                return 0, f"[cached] {os.path.basename(src)}\n"
+    flags = [f for f in NVCC_FLAGS if f != "-shared"]
+    cmd = [nvcc] + flags + ["-c", "-o", obj, src]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode == 0:
+        with open(tag, "w") as fh:
+            fh.write(digest)
+    return res.returncode, " ".join(cmd) + "\n" + res.stdout + res.stderr
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile csrc/*.cu into libfsb200.so; returns the library path."""
+    """Compile csrc/*.cu (one object per file, in parallel, cached under csrc/build/) and link
+    libfsb200.so; returns the library path."""
     if not force and not is_stale():
         return LIB
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(nvcc):
         raise RuntimeError("nvcc not found: libfsb200.so cannot be built")
-    cmd = [nvcc] + NVCC_FLAGS + ["-o", LIB] + _sources()
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    log = res.stdout + res.stderr
+    objdir = os.path.join(CSRC, "build")
+    os.makedirs(objdir, exist_ok=True)
+    if force:
+        for f in glob.glob(os.path.join(objdir, "*.hash")):
+            os.remove(f)
+    h = hashlib.sha256(" ".join(NVCC_FLAGS).encode())
+    for f in sorted(glob.glob(os.path.join(CSRC, "*.cuh"))) + [os.path.join(os.path.dirname(PKG), "include", "fsb200.h")]:
+        with open(f, "rb") as fh:
+            h.update(fh.read())
+    deps_hash = h.hexdigest()
+    from concurrent.futures import ThreadPoolExecutor
+    srcs = _sources()
+    objs = [os.path.join(objdir, os.path.basename(s)[:-3] + ".o") for s in srcs]
+    with ThreadPoolExecutor(max_workers=min(len(srcs), os.cpu_count() or 1)) as pool:
+        results = list(pool.map(lambda so: _compile_one(nvcc, so[0], so[1], deps_hash), zip(srcs, objs)))
+    log = "".join(r[1] for r in results)
+    failed = any(r[0] != 0 for r in results)
+    if not failed:
+        cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-cudart", "static", "-o", LIB] + objs
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        log += " ".join(cmd) + "\n" + res.stdout + res.stderr
+        failed = res.returncode != 0
     with open(os.path.join(CSRC, ".build_log.txt"), "w") as fh:
-        fh.write(" ".join(cmd) + "\n" + log)
-    if res.returncode != 0:
+        fh.write(log)
+    if failed:
         raise RuntimeError("nvcc failed:\n" + log[-8000:])
     if verbose:
         print(log)

@@ -141,7 +141,7 @@ __device__ __forceinline__ void cu_store(uint8_t* hi, uint8_t* lo, int rows_pad,
 template <int NPROD>
 __global__ void __launch_bounds__(kCuThreads)
 corr_umma_kernel(const float* __restrict__ f1, const float* __restrict__ f2, LevelPtrs lv, int C, int H, int W1,
-                 int W2, int L, int nbuf) {
+                 int W2, int L, int nbuf, int rows_m) {
   pdl_launch_dependents();  // the next kernel may start its prologue
   pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ __align__(1024) uint8_t cu_smem[];
@@ -151,7 +151,10 @@ corr_umma_kernel(const float* __restrict__ f1, const float* __restrict__ f2, Lev
   __shared__ float nA[kCuBM], nB[256];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int m0 = blockIdx.x * kCuBM, n0 = blockIdx.y * 256;
+  // rows_m <= 128 rows of w1 per CTA (W1 split evenly over the m tiles, a multiple of 4): only those rows of the
+  // 128-row A tile are staged and stored; the MMA still runs M = 128, the other accumulator rows are never read
+  const int m0 = blockIdx.x * rows_m, n0 = blockIdx.y * 256;
+  const int rowsA = min(rows_m, (W1 - m0 + 3) & ~3);
   const int bh = blockIdx.z, b = bh / H, h = bh - b * H;
   const int Nv = min(256, W2 - n0);         // valid columns of this tile
   const int Npad = (Nv + 15) & ~15;         // MMA N
@@ -194,8 +197,8 @@ corr_umma_kernel(const float* __restrict__ f1, const float* __restrict__ f2, Lev
   const int nchunks = (C + kCuKC - 1) / kCuKC;
   float va[1][4][4], vb[2][4][4];
   auto load_chunk = [&](int ch) {
-    if (vecA) cu_load<1, true>(a_plane, HW1, m0, W1, kCuBM, ch * kCuKC, C, va);
-    else      cu_load<1, false>(a_plane, HW1, m0, W1, kCuBM, ch * kCuKC, C, va);
+    if (vecA) cu_load<1, true>(a_plane, HW1, m0, W1, rowsA, ch * kCuKC, C, va);
+    else      cu_load<1, false>(a_plane, HW1, m0, W1, rowsA, ch * kCuKC, C, va);
     if (vecB) cu_load<2, true>(b_plane, HW2, n0, W2, Npad, ch * kCuKC, C, vb);
     else      cu_load<2, false>(b_plane, HW2, n0, W2, Npad, ch * kCuKC, C, vb);
   };
@@ -210,7 +213,7 @@ corr_umma_kernel(const float* __restrict__ f1, const float* __restrict__ f2, Lev
       cu_mbar_wait(bar0, (ch - 1) & 1);
     }
     uint8_t* g = gbase + (size_t)buf * buf_bytes;
-    cu_store<NPROD, 1>(g, g + off_alo, kCuBM, va, pa);
+    cu_store<NPROD, 1>(g, g + off_alo, rowsA, va, pa);
     cu_store<NPROD, 2>(g + off_bhi, g + off_blo, Npad, vb, pb);
     if (ch + 1 < nchunks) load_chunk(ch + 1);  // in flight across the barrier, the MMAs and the wait above
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the MMA
@@ -269,7 +272,7 @@ corr_umma_kernel(const float* __restrict__ f1, const float* __restrict__ f2, Lev
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const int q = warp & 3;
     const int r = q * 32 + lane, w1 = m0 + r;
-    const bool valid = w1 < W1;
+    const bool valid = r < rowsA && w1 < W1;
     const float ia = 1.f / nA[r];
     const size_t p = (size_t)bh * W1 + (valid ? w1 : 0);
     const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
@@ -330,11 +333,13 @@ int launch_corr_umma(const float* f1, const float* f2, const LevelPtrs& lv, int 
   const int nbuf = (2 * buf + 1024 <= 96 * 1024) ? 2 : 1;
   const size_t smem = nbuf * buf + 1024;
   FSB_REQUIRE(smem <= 227 * 1024 - 16 * 1024, FSB_ERR_SHAPE, "fsb_corr_pyramid: %zu B shared memory", smem);
-  dim3 grid(ceil_div(W1, kCuBM), ceil_div(W2, 256), B * H);
+  const int mtiles = ceil_div(W1, kCuBM);
+  const int rows_m = round_up(ceil_div(W1, mtiles), 4);  // e.g. W1 = 160: two CTAs of 80 rows instead of 128 + 32
+  dim3 grid(mtiles, ceil_div(W2, 256), B * H);
   auto kern = nprod == 3 ? corr_umma_kernel<3> : corr_umma_kernel<1>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return cuda_fail(e, "fsb_corr_pyramid: cudaFuncSetAttribute");
-  launch_kernel(kern, dim3(grid), dim3(kCuThreads), smem, stream, f1, f2, lv, C, H, W1, W2, L, nbuf);
+  launch_kernel(kern, dim3(grid), dim3(kCuThreads), smem, stream, f1, f2, lv, C, H, W1, W2, L, nbuf, rows_m);
   FSB_CHECK_LAUNCH("fsb_corr_pyramid");
   return FSB_OK;
 }
