@@ -111,4 +111,9 @@ struct LevelPtrs {
 int launch_corr_umma(const float* f1, const float* f2, const LevelPtrs& lv, int B, int C, int H, int W1, int W2, int L,
                      int nprod, cudaStream_t stream);
 
+// corr_tma.cu: the same with the NCHW planes fed by TMA as MN-major operands (needs W % 4 == 0, 16-byte aligned bases)
+bool corr_tma_eligible(const float* f1, const float* f2, int W1, int W2);
+int launch_corr_tma(const float* f1, const float* f2, const LevelPtrs& lv, int B, int C, int H, int W1, int W2, int L,
+                    int nprod, cudaStream_t stream);
+
 }  // namespace fsb

@@ -481,6 +481,8 @@ extern "C" int fsb_corr_pyramid(const float* f1, const float* f2, float* const* 
     FSB_REQUIRE(aligned16(corr_levels[l]), FSB_ERR_ALIGN, "fsb_corr_pyramid: level %d not 16-byte aligned", l);
     lv.p[l] = corr_levels[l];
   }
+  if (precision != FSB_PREC_FP32 && corr_tma_eligible(f1, f2, W1, W2))
+    return launch_corr_tma(f1, f2, lv, B, C, H, W1, W2, L, precision == FSB_PREC_TF32X3 ? 3 : 1, (cudaStream_t)stream);
   if (precision != FSB_PREC_FP32)
     return launch_corr_umma(f1, f2, lv, B, C, H, W1, W2, L, precision == FSB_PREC_TF32X3 ? 3 : 1, (cudaStream_t)stream);
   dim3 grid(ceil_div(W2, 128), ceil_div(W1, 64), B * H);
