@@ -31,8 +31,9 @@ t = {}
 tensor = [(n, b) for n, b, _ in step if "conv_umma" in n or "conv_halo" in n or "edgenext_mlp" in n]
 t["conv_umma_kernel"] = sum(b for _, b in tensor)
 t["conv_umma_kernel_launches"] = len(tensor)
-names = {"volume_kernel": "volume_gwc_concat", "corr_umma": "corr_pyramid", "geo_pyramid": "geo_pyramid",
-         "lookup_nhwc": "geo_lookup", "lookup_nchw": "geo_lookup_fp32_nchw"}
+names = {"volume_kernel": "volume_gwc_concat", "corr_umma": "corr_pyramid", "corr_tma": "corr_pyramid",
+         "geo_pyramid": "geo_pyramid", "lookup_nhwc": "geo_lookup", "lookup_nchw": "geo_lookup_fp32_nchw",
+         "disp_regression": "softmax_disparity_regression", "context_upsample": "softmax_context_upsample"}
 for n, b, _ in k123:
     for k, v in names.items():
         if k in n:
