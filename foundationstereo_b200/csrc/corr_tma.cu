@@ -38,6 +38,7 @@ struct CorrTmaParams {
   int rows_m;   // rows of w1 per m tile
   int boxes_a;  // boxes of the A region of a stage = ceil(rows_m / 32)
   int boxes_b;  // boxes of the B region = ceil(min(W2, 256) padded to 16 / 32)
+  int stage0, stage1;  // level 0 / level 1 leave through shared memory as fully coalesced 16-byte stores
 };
 
 // MN-major SWIZZLE_128B_BASE32B operand: atom = 32 pixels (128 B) x 4 channels (rows of 128 B, 512 B per atom);
@@ -215,6 +216,11 @@ corr_tma_kernel(const __grid_constant__ CorrTmaParams p) {
   }
   __syncthreads();
 
+  // output staging (all MMAs are done once bar_acc has fired, the operand stages are free): level 0 over the two raw
+  // stages, level 1 in the lo stage
+  float* const out0s = reinterpret_cast<float*>(gbase);
+  float* const out1s = reinterpret_cast<float*>(gbase + 2 * (size_t)stage_bytes);
+  const int stride0s = W2 + 4, stride1s = (W2 >> 1) + 4;
   {
     // epilogue on all 8 warps: warp w reads TMEM lane quarter (w & 3); warps 0-3 take the even 16-column chunks,
     // warps 4-7 the odd ones
@@ -226,6 +232,9 @@ corr_tma_kernel(const __grid_constant__ CorrTmaParams p) {
     const float ia = 1.f / nA[r];
     const size_t px = (size_t)bh * W1 + (valid ? w1 : 0);
     const uint32_t taddr = tmem + ((uint32_t)(q * 32) << 16);
+    float* out0 = out0s;
+    float* out1 = out1s;
+    const int stride0 = stride0s, stride1 = stride1s;
     for (int c0 = (warp >> 2) * 16; c0 < Npad; c0 += 32) {
       uint32_t raw[16];
       tmem_ld16(taddr + c0, raw);
@@ -235,15 +244,28 @@ corr_tma_kernel(const __grid_constant__ CorrTmaParams p) {
 #pragma unroll
       for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(raw[i]) * ia * nB[c0 + i];  // nB holds 1/max(|f2|, eps)
       const int col = n0 + c0;
-      float* row = p.lv.p[0] + px * W2 + col;
-      if (col + 16 <= W2) {
+      if (p.stage0) {  // n0 == 0: row r of the staged tile, stride W2 + 4 floats (conflict-free 16-byte stores)
+        float* srow = out0 + r * stride0 + c0;
+        if (c0 + 16 <= W2) {
 #pragma unroll
-        for (int q4 = 0; q4 < 4; ++q4)
-          *reinterpret_cast<float4*>(row + 4 * q4) = make_float4(v[4 * q4], v[4 * q4 + 1], v[4 * q4 + 2], v[4 * q4 + 3]);
+          for (int q4 = 0; q4 < 4; ++q4)
+            *reinterpret_cast<float4*>(srow + 4 * q4) = make_float4(v[4 * q4], v[4 * q4 + 1], v[4 * q4 + 2], v[4 * q4 + 3]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (c0 + i < W2) srow[i] = v[i];
+        }
       } else {
+        float* row = p.lv.p[0] + px * W2 + col;
+        if (col + 16 <= W2) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i)
-          if (col + i < W2) row[i] = v[i];
+          for (int q4 = 0; q4 < 4; ++q4)
+            *reinterpret_cast<float4*>(row + 4 * q4) = make_float4(v[4 * q4], v[4 * q4 + 1], v[4 * q4 + 2], v[4 * q4 + 3]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (col + i < W2) row[i] = v[i];
+        }
       }
       // pooled levels: mean of adjacent pairs of the previous level, floor length
       int n = 16, len = W2, cl = col;
@@ -253,6 +275,18 @@ corr_tma_kernel(const __grid_constant__ CorrTmaParams p) {
 #pragma unroll
         for (int i = 0; i < 8; ++i)
           if (i < n) v[i] = (v[2 * i] + v[2 * i + 1]) * 0.5f;
+        if (l == 1 && p.stage1) {
+          float* srow = out1 + r * stride1 + cl;
+          if (cl + 8 <= len) {
+            *reinterpret_cast<float4*>(srow) = make_float4(v[0], v[1], v[2], v[3]);
+            *reinterpret_cast<float4*>(srow + 4) = make_float4(v[4], v[5], v[6], v[7]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              if (cl + i < len) srow[i] = v[i];
+          }
+          continue;
+        }
         float* rl = p.lv.p[l] + px * len + cl;
         if (n >= 4 && (len & 3) == 0 && cl + n <= len) {
           *reinterpret_cast<float4*>(rl) = make_float4(v[0], v[1], v[2], v[3]);
@@ -265,6 +299,28 @@ corr_tma_kernel(const __grid_constant__ CorrTmaParams p) {
       }
     }
     tc_fence_before();
+  }
+  if (p.stage0 || p.stage1) {
+    // The staged tile leaves as ONE contiguous run per level (rows of a tile are consecutive in the output): every warp
+    // instruction writes 512 contiguous bytes = 16 full sectors, instead of 32 half sectors in 32 different rows.
+    __syncthreads();
+    const size_t prow0 = (size_t)bh * W1 + m0;
+    if (p.stage0) {
+      const int per_row = W2 >> 2, total = rowsA * per_row;
+      float4* dst = reinterpret_cast<float4*>(p.lv.p[0] + prow0 * W2);
+      for (int i = tid; i < total; i += kCtThreads) {
+        const int rr = i / per_row, c4 = i - rr * per_row;
+        dst[i] = *reinterpret_cast<const float4*>(out0s + rr * stride0s + 4 * c4);
+      }
+    }
+    if (p.stage1) {
+      const int per_row = W2 >> 3, total = rowsA * per_row;
+      float4* dst = reinterpret_cast<float4*>(p.lv.p[1] + prow0 * (W2 >> 1));
+      for (int i = tid; i < total; i += kCtThreads) {
+        const int rr = i / per_row, c4 = i - rr * per_row;
+        dst[i] = *reinterpret_cast<const float4*>(out1s + rr * stride1s + 4 * c4);
+      }
+    }
   }
   __syncthreads();
   if (warp == 0) {
@@ -315,7 +371,11 @@ int launch_corr_tma(const float* f1, const float* f2, const LevelPtrs& lv, int B
   // the MMA reads M = 128 rows = 4 pixel blocks from the A region: blocks past boxes_a fall into the B region (their
   // accumulator rows are never read), so a stage must hold at least 4 boxes
   if (p.boxes_a + p.boxes_b < 4) p.boxes_b = 4 - p.boxes_a;
-  const size_t smem = 3 * (size_t)(p.boxes_a + p.boxes_b) * kCtBox + 1024;
+  const size_t stage = (size_t)(p.boxes_a + p.boxes_b) * kCtBox;
+  // staged epilogue: one n tile, rows of 16-byte multiples, the staged tile fits the freed operand stages
+  p.stage0 = W2 <= 256 && aligned16(lv.p[0]) && (size_t)p.rows_m * (W2 + 4) * 4 <= 2 * stage;
+  p.stage1 = L >= 2 && W2 <= 256 && (W2 & 7) == 0 && aligned16(lv.p[1]) && (size_t)p.rows_m * ((W2 >> 1) + 4) * 4 <= stage;
+  const size_t smem = 3 * stage + 1024;
   FSB_REQUIRE(smem <= 220 * 1024, FSB_ERR_SHAPE, "fsb_corr_pyramid: %zu B shared memory", smem);
   dim3 grid(mtiles, ceil_div(W2, 256), B * H);
   auto kern = nprod == 3 ? corr_tma_kernel<3> : corr_tma_kernel<1>;
