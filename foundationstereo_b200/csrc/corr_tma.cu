@@ -96,19 +96,9 @@ corr_tma_kernel(const __grid_constant__ CorrTmaParams p) {
     mbar_init(bar_mma, 1);
     mbar_init(bar_acc, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    tma_prefetch_desc(&p.map1);
-    tma_prefetch_desc(&p.map2);
   }
-  if (warp == 0) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
-                 "r"((uint32_t)tcols) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem = tmem_slot;
-
+  // the first two chunks are requested before TMEM allocation and the set-up barrier (thread 0 initialised the barriers
+  // it posts to; everyone else meets them after the __syncthreads below)
   auto issue_tma = [&](int ch) {  // thread 0: chunk ch -> raw stage ch & 1
     const uint32_t s = ch & 1, dst = base + s * stage_bytes, bar = bar_full + 8 * s;
     mbar_expect_tx(bar, (uint32_t)(ldA + ldB) * kCtBox);
@@ -119,6 +109,16 @@ corr_tma_kernel(const __grid_constant__ CorrTmaParams p) {
     issue_tma(0);
     if (nchunks > 1) issue_tma(1);
   }
+
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_slot)),
+                 "r"((uint32_t)tcols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
 
   // instruction descriptor, kind::tf32: D fp32, A/B tf32, both MN-major (bits 15, 16), M = 128, N = Npad
   const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(Npad >> 3) << 17) |
@@ -140,6 +140,15 @@ corr_tma_kernel(const __grid_constant__ CorrTmaParams p) {
       if (tid == 0 && ch + 1 < nchunks) issue_tma(ch + 1);
     }
     mbar_wait(bar_full + 8 * s, (ch >> 1) & 1);
+    if (NPROD == 3 && tid == 0) {
+      // hi * hi needs only the raw tiles: it runs on the tensor pipe while the threads write the lo tiles
+      tc_fence_after();
+      const uint32_t sa = base + s * stage_bytes;
+#pragma unroll
+      for (int kg = 0; kg < 4; ++kg)
+        ct_mma_tf32(tmem, ct_desc_mn128(sa + kg * 1024, kCtBox), ct_desc_mn128(sa + off_b + kg * 1024, kCtBox), idesc,
+                    (ch > 0 || kg > 0) ? 1u : 0u);
+    }
     uint8_t* raw = gbase + (size_t)s * stage_bytes;
     uint8_t* lo = gbase + 2 * (size_t)stage_bytes;
 #pragma unroll
@@ -174,7 +183,7 @@ corr_tma_kernel(const __grid_constant__ CorrTmaParams p) {
       for (int kg = 0; kg < 4; ++kg) {  // 8 channels (one atom row group, 1024 B) per MMA
         const uint64_t ahi = ct_desc_mn128(sa + kg * 1024, kCtBox);
         const uint64_t bhi = ct_desc_mn128(sa + off_b + kg * 1024, kCtBox);
-        ct_mma_tf32(tmem, ahi, bhi, idesc, (ch > 0 || kg > 0) ? 1u : 0u);
+        if (NPROD == 1) ct_mma_tf32(tmem, ahi, bhi, idesc, (ch > 0 || kg > 0) ? 1u : 0u);
         if (NPROD == 3) {
           const uint64_t alo = ct_desc_mn128(lo_base + kg * 1024, kCtBox);
           const uint64_t blo = ct_desc_mn128(lo_base + off_b + kg * 1024, kCtBox);
