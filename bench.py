@@ -358,10 +358,14 @@ def run_b200(args):
 
         # ---- CPU baseline (oracle port) on the host cores, bounded sample --------------------
         threads = os.cpu_count() or 1
-        best = min(cpu_sample(60, 2, threads)[0] for _ in range(2))
-        cpu = {"value": 1.0 / best, "unit": UNIT, "cores": threads, "kind": "port",
-               "sample": "rows 0..59 of 120 (full width, D=104): volumes + geo init + 2 of 32 iterations, best of 2, "
-                         "extrapolated linearly to one pair; torch fp32 CPU oracle (oracle/hotpath.py)"}
+        if world == 1:
+            best = min(cpu_sample(60, 2, threads)[0] for _ in range(2))
+            cpu = {"value": 1.0 / best, "unit": UNIT, "cores": threads, "kind": "port",
+                   "sample": "rows 0..59 of 120 (full width, D=104): volumes + geo init + 2 of 32 iterations, best of 2, "
+                             "extrapolated linearly to one pair; torch fp32 CPU oracle (oracle/hotpath.py)"}
+        else:
+            cpu = {"value": None, "unit": UNIT, "cores": threads, "kind": "port",
+                   "sample": "timed at N=1 only (python bench.py --gpus 1)"}
 
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
