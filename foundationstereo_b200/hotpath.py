@@ -36,6 +36,9 @@ class StereoHotPath:
         self.update_block = SelectiveUpdateBlock(state_dict, self.device)
         self.dx = torch.linspace(-corr_radius, corr_radius, 2 * corr_radius + 1).reshape(1, 1, -1, 1)
         self._ws = {}
+        # bench.py: CUDA events around the refinement loop of every run() (the loop's share of a timed step)
+        self.record_loop = False
+        self.loop_events: List[Tuple[torch.cuda.Event, torch.cuda.Event]] = []
 
     @torch.no_grad()
     def run(self, fl: Tensor, fr: Tensor, pl: Tensor, pr: Tensor, volume: Tensor, disp: Tensor,
@@ -51,7 +54,13 @@ class StereoHotPath:
             ws = self._ws[key] = Combined_Geo_Encoding_Volume.make_workspace(B, volume.shape[1], volume.shape[2], H, W,
                                                                            fr.shape[3], self.L, fl.device)
         geo = Combined_Geo_Encoding_Volume(fl.float(), fr.float(), volume, num_levels=self.L, dx=self.dx, workspace=ws)
+        if self.record_loop:
+            ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+            ev[0].record()
         disp, mask, _ = self.update_block.refine(geo, net, inp, att, disp, iters)
+        if self.record_loop:
+            ev[1].record()
+            self.loop_events.append(ev)
         return disp, mask, comb
 
     # ---- host-resident inputs: double-buffered upload -----------------------------------------------

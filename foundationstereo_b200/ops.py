@@ -23,9 +23,18 @@ def _stream() -> int:
 
 
 def _need_cuda(*ts: torch.Tensor) -> None:
+    """All tensors on one CUDA device."""
     for t in ts:
         if not t.is_cuda:
             raise _lib.FsbError("foundationstereo_b200 ops run on CUDA tensors only (no CPU path)")
+        if t.device != ts[0].device:
+            raise _lib.FsbError(f"tensors on different devices: {ts[0].device} and {t.device}")
+
+
+def _call(t: torch.Tensor, name: str, *args) -> None:
+    """One C-ABI launch on the current stream of ``t``'s device (which need not be the caller's current device)."""
+    with torch.cuda.device(t.device):
+        check(getattr(lib(), name)(*args, torch.cuda.current_stream().cuda_stream))
 
 
 # ----------------------------------------------------------------------------------------
@@ -38,8 +47,8 @@ def gwc_volume(fl: torch.Tensor, fr: torch.Tensor, maxdisp: int, num_groups: int
     fl, fr = fl.contiguous(), fr.contiguous()
     B, C, H, W = fl.shape
     out = torch.empty((B, num_groups, maxdisp, H, W), dtype=fl.dtype, device=fl.device)
-    check(lib().fsb_volume_gwc_concat(fl.data_ptr(), fr.data_ptr(), None, None, out.data_ptr(), None,
-                                      B, C, 0, num_groups, H, W, maxdisp, _DTYPE[fl.dtype], _stream()))
+    _call(fl, "fsb_volume_gwc_concat", fl.data_ptr(), fr.data_ptr(), None, None, out.data_ptr(), None,
+                                      B, C, 0, num_groups, H, W, maxdisp, _DTYPE[fl.dtype])
     return out
 
 
@@ -56,8 +65,8 @@ def concat_volume(pl: torch.Tensor, pr: torch.Tensor, maxdisp: int) -> torch.Ten
     pl, pr = pl.contiguous(), pr.contiguous()
     B, Cp, H, W = pl.shape
     out = torch.empty((B, 2 * Cp, maxdisp, H, W), dtype=pl.dtype, device=pl.device)
-    check(lib().fsb_volume_gwc_concat(None, None, pl.data_ptr(), pr.data_ptr(), None, out.data_ptr(),
-                                      B, 0, Cp, 0, H, W, maxdisp, _DTYPE[pl.dtype], _stream()))
+    _call(pl, "fsb_volume_gwc_concat", None, None, pl.data_ptr(), pr.data_ptr(), None, out.data_ptr(),
+                                      B, 0, Cp, 0, H, W, maxdisp, _DTYPE[pl.dtype])
     return out
 
 
@@ -78,8 +87,8 @@ def combined_volume(fl: torch.Tensor, fr: torch.Tensor, pl: torch.Tensor, pr: to
     B, C, H, W = fl.shape
     Cp = pl.shape[1]
     out = torch.empty((B, num_groups + 2 * Cp, maxdisp, H, W), dtype=fl.dtype, device=fl.device)
-    check(lib().fsb_volume_combined(fl.data_ptr(), fr.data_ptr(), pl.data_ptr(), pr.data_ptr(), out.data_ptr(),
-                                    B, C, Cp, num_groups, H, W, maxdisp, _DTYPE[fl.dtype], _stream()))
+    _call(fl, "fsb_volume_combined", fl.data_ptr(), fr.data_ptr(), pl.data_ptr(), pr.data_ptr(), out.data_ptr(),
+                                    B, C, Cp, num_groups, H, W, maxdisp, _DTYPE[fl.dtype])
     return out
 
 
@@ -102,8 +111,8 @@ def corr_pyramid(f1: torch.Tensor, f2: torch.Tensor, num_levels: int, precision:
     W2 = f2.shape[3]
     assert f2.shape[:3] == (B, C, H)
     levels = [torch.empty((B * H * W1, W2 >> l), dtype=torch.float32, device=f1.device) for l in range(num_levels)]
-    check(lib().fsb_corr_pyramid(f1.data_ptr(), f2.data_ptr(), level_array(levels), B, C, H, W1, W2,
-                                 num_levels, precision, _stream()))
+    _call(f1, "fsb_corr_pyramid", f1.data_ptr(), f2.data_ptr(), level_array(levels), B, C, H, W1, W2,
+                                 num_levels, precision)
     return levels
 
 
@@ -122,7 +131,7 @@ def geo_pyramid(volume: torch.Tensor, num_levels: int) -> List[torch.Tensor]:
     B, Cg, D, H, W = volume.shape
     levels = [torch.empty((B * H * W, D >> l, Cg), dtype=torch.float32, device=volume.device)
               for l in range(num_levels)]
-    check(lib().fsb_geo_pyramid(volume.data_ptr(), level_array(levels), B, Cg, D, H, W, num_levels, _stream()))
+    _call(volume, "fsb_geo_pyramid", volume.data_ptr(), level_array(levels), B, Cg, D, H, W, num_levels)
     return levels
 
 
@@ -149,8 +158,8 @@ def geo_lookup(geo_levels: List[torch.Tensor], corr_levels: List[torch.Tensor], 
     assert N == B * H * W and coords.numel() == N
     K = 2 * radius + 1
     out = torch.empty((B, L * K * (Cg + 1), H, W), dtype=torch.float32, device=disp.device)
-    check(lib().fsb_geo_lookup(level_array(geo_levels), level_array(corr_levels), disp.data_ptr(),
-                               coords.data_ptr(), out.data_ptr(), B, Cg, D, H, W, W2, L, radius, 0, _stream()))
+    _call(disp, "fsb_geo_lookup", level_array(geo_levels), level_array(corr_levels), disp.data_ptr(),
+                               coords.data_ptr(), out.data_ptr(), B, Cg, D, H, W, W2, L, radius, 0)
     return out
 
 
@@ -179,8 +188,8 @@ def geo_lookup_nhwc16(geo_levels: List[torch.Tensor], corr_levels: List[torch.Te
     assert disp.dtype == torch.float32 and disp.is_contiguous() and coords.dtype == torch.float32 \
         and coords.is_contiguous() and coords.numel() == N == B * H * W
     layout = 1 if out.dtype == torch.float16 else 2
-    check(lib().fsb_geo_lookup(level_array(geo_levels), level_array(corr_levels), disp.data_ptr(),
-                               coords.data_ptr(), out.data_ptr(), B, Cg, D, H, W, W2, L, radius, layout, _stream()))
+    _call(disp, "fsb_geo_lookup", level_array(geo_levels), level_array(corr_levels), disp.data_ptr(),
+                               coords.data_ptr(), out.data_ptr(), B, Cg, D, H, W, W2, L, radius, layout)
     return out
 
 
@@ -193,8 +202,8 @@ def corr_pyramid_into(f1: torch.Tensor, f2: torch.Tensor, levels: List[torch.Ten
     W2 = f2.shape[3]
     for l, t in enumerate(levels):
         assert t.shape == (B * H * W1, W2 >> l) and t.dtype == torch.float32 and t.is_contiguous()
-    check(lib().fsb_corr_pyramid(f1.data_ptr(), f2.data_ptr(), level_array(levels), B, C, H, W1, W2,
-                                 len(levels), precision, _stream()))
+    _call(f1, "fsb_corr_pyramid", f1.data_ptr(), f2.data_ptr(), level_array(levels), B, C, H, W1, W2,
+                                 len(levels), precision)
 
 
 def geo_pyramid_into(volume: torch.Tensor, levels: List[torch.Tensor]) -> None:
@@ -204,7 +213,7 @@ def geo_pyramid_into(volume: torch.Tensor, levels: List[torch.Tensor]) -> None:
     B, Cg, D, H, W = volume.shape
     for l, t in enumerate(levels):
         assert t.shape == (B * H * W, D >> l, Cg) and t.dtype == torch.float32 and t.is_contiguous()
-    check(lib().fsb_geo_pyramid(volume.data_ptr(), level_array(levels), B, Cg, D, H, W, len(levels), _stream()))
+    _call(volume, "fsb_geo_pyramid", volume.data_ptr(), level_array(levels), B, Cg, D, H, W, len(levels))
 
 
 # ----------------------------------------------------------------------------------------
@@ -219,8 +228,7 @@ def disparity_regression(x: torch.Tensor, logits: bool) -> torch.Tensor:
     x = x.contiguous()
     B, D, H, W = x.shape
     out = torch.empty((B, 1, H, W), dtype=torch.float32 if logits else x.dtype, device=x.device)
-    check(lib().fsb_disparity_regression(x.data_ptr(), out.data_ptr(), B, D, H, W, int(logits), _DTYPE[x.dtype],
-                                         _stream()))
+    _call(x, "fsb_disparity_regression", x.data_ptr(), out.data_ptr(), B, D, H, W, int(logits), _DTYPE[x.dtype])
     return out
 
 
@@ -240,8 +248,8 @@ def context_upsample(disp_low: torch.Tensor, weights: torch.Tensor, logits: bool
     disp_low = disp_low.float().contiguous()
     weights = weights.contiguous()
     out = torch.empty((B, 4 * h, 4 * w), dtype=torch.float32, device=disp_low.device)
-    check(lib().fsb_context_upsample(disp_low.data_ptr(), weights.data_ptr(), out.data_ptr(), B, h, w, int(logits),
-                                     float(scale), _DTYPE[weights.dtype], _stream()))
+    _call(disp_low, "fsb_context_upsample", disp_low.data_ptr(), weights.data_ptr(), out.data_ptr(), B, h, w, int(logits),
+                                     float(scale), _DTYPE[weights.dtype])
     return out
 
 

@@ -74,14 +74,23 @@ def install_update_block(update_block):
     state = {"engine": None, "versions": None}
 
     def engine():
-        versions = tuple(p._version for p in update_block.parameters())
+        # in-place updates bump `_version`; `.to()` / `.half()` / `.cuda()` swap `param.data` without bumping it, so the
+        # storage address, device and dtype are part of the key as well
+        versions = tuple((p._version, p.data_ptr(), p.device, p.dtype) for p in update_block.parameters())
         if state["engine"] is None or versions != state["versions"]:
             dev = next(update_block.parameters()).device
+            state["engine"] = None  # drop the old engine (packed weights, plans, captured graphs) first
             state["engine"] = SelectiveUpdateBlock(update_block.state_dict(), dev)
             state["versions"] = versions
         return state["engine"]
 
     def fast_forward(self, net, inp, corr, disp, att):
+        import torch
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            from ._lib import FsbError
+            raise FsbError("the B200 update block is inference-only: with gradients enabled its weights would silently "
+                           "stop training.  Run under torch.no_grad() / torch.inference_mode() (scripts/run_demo.py:102 "
+                           "does), or fsb.uninstall(model) before training")
         return engine()(net, inp, corr, disp, att)
 
     _SAVED.setdefault(("update_block", id(update_block)), update_block.forward)

@@ -56,11 +56,14 @@ class _Plan:
     (:155-158), and the coarse GRU levels have too few pixel tiles to fill 148 SMs, so the
     two chains run concurrently between FORK / JOIN markers (also inside the CUDA graph)."""
 
-    def __init__(self):
+    def __init__(self, device: torch.device):
         self.steps: List[Callable[[], None]] = []
         self.names: List[str] = []
         self.lanes: List[int] = []
+        self.tags: List[Optional[str]] = []
         self.lane = 0
+        self.tag: Optional[str] = None
+        self.keep: list = []
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.iter_graph: Optional[torch.cuda.CUDAGraph] = None
         self.iter_key = None
@@ -68,12 +71,13 @@ class _Plan:
         self.calls = 0
         self.iter_calls = 0
         self.flops = 0.0
-        self.side = torch.cuda.Stream()
+        self.side = torch.cuda.Stream(device)
 
     def add(self, name: str, fn) -> None:
         self.steps.append(fn)
         self.names.append(name)
         self.lanes.append(self.lane)
+        self.tags.append(self.tag)
 
 
 class SelectiveUpdateBlock:
@@ -90,7 +94,7 @@ class SelectiveUpdateBlock:
     def __init__(self, state_dict: Dict[str, Tensor], device: torch.device | str = "cuda",
                  dtype: torch.dtype = torch.float16, use_graph: bool = True,
                  block_n: Optional[Dict[str, int]] = None, halo: Optional[Sequence[str]] = None,
-                 fused_mlp: bool = True):
+                 fused_mlp: bool = True, copy_outputs: bool = False):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("SelectiveUpdateBlock runs on CUDA only (no CPU path)")
@@ -100,6 +104,7 @@ class SelectiveUpdateBlock:
         self.dtype = dtype
         self.use_graph = use_graph and _os.environ.get("FSB_GRAPH", "1") != "0"
         self.two_lanes = _os.environ.get("FSB_TWO_LANES", "1") != "0"  # side stream for encoder / mask head
+        self.copy_outputs = copy_outputs  # forward returns fresh tensors instead of views of the plan's buffers
         self.fused_mlp = fused_mlp  # False: pwconv1 / pwconv2 of the disparity head as two convolution launches
         self.bn = dict(DEFAULT_BLOCK_N)
         if block_n:
@@ -108,10 +113,13 @@ class SelectiveUpdateBlock:
         self.replayed_kernels = 0  # libfsb200 kernels launched through CUDA-graph replays (not seen by fsb_launch_count)
         self.fixed_tiles = block_n is not None or halo is not None  # explicit tuning tables switch the heuristics off
         sd = {k: v.detach().to(self.device, torch.float32) for k, v in state_dict.items()}
-        assert "gru16.conv0.0.weight" in sd and "gru08.conv0.0.weight" in sd, \
-            "only the n_gru_layers == 3 configuration of the reference is supported"
+        # n_gru_layers of the reference module (core/update.py:128-132) = which GRUs its state_dict holds
+        self.n_layers = 3 if "gru16.conv0.0.weight" in sd else 2 if "gru08.conv0.0.weight" in sd else 1
+        if "gru04.small_gru.convz.weight" not in sd:
+            raise _lib.FsbError("state_dict is not a BasicSelectiveMultiUpdateBlock's (no gru04.* keys, core/update.py:132)")
         self.hidden = sd["gru04.small_gru.convz.weight"].shape[0]
-        assert self.hidden == 128, "hidden_dim 128 (core/foundation_stereo.py:137)"
+        if self.hidden != 128:
+            raise _lib.FsbError(f"hidden_dim {self.hidden}: the kernels are built for 128 (core/foundation_stereo.py:137)")
         self.planes = sd["encoder.convc1.weight"].shape[1]
         self.planes_pad = pad64(self.planes)
         self.spec: Dict[str, tuple] = {}                    # weight key -> (launch name, segments, biases, Cout, block_n)
@@ -155,7 +163,13 @@ class SelectiveUpdateBlock:
     def _pack(self, sd: Dict[str, Tensor]) -> None:
         hd = self.hidden
         bn = self.bn
-        for g, cin in (("gru16", 2 * hd), ("gru08", 3 * hd), ("gru04", 3 * hd)):
+        n = self.n_layers
+        grus = [("gru04", (2 + (n > 1)) * hd)]                  # input widths: core/update.py:129-132
+        if n >= 2:
+            grus.append(("gru08", (2 + (n == 3)) * hd))
+        if n == 3:
+            grus.append(("gru16", 2 * hd))
+        for g, cin in grus:
             nx = cin // hd
             self._put(f"{g}.conv0", f"{g}.conv0", [(sd[f"{g}.conv0.0.weight"], [(hd, hd)] * nx)],
                       [sd[f"{g}.conv0.0.bias"]], cin, self._bn("conv0", g))
@@ -270,7 +284,7 @@ class SelectiveUpdateBlock:
 
     def _build_plan(self, B: int, H: int, W: int) -> _Plan:
         hd, dev, dt = self.hidden, self.device, self.dtype
-        plan = _Plan()
+        plan = _Plan(dev)
         # tile shape per launch: explicit entries here override the cost model of _pick_block_n (used for every
         # tap-layout launch).  Since the tap kernel became persistent it matches or beats the halo variant on every
         # layer shape of the block (tools/conv_sweep.py: 3x3 512->512 288 vs 295 us, 384->384 182 vs 184 us), so
@@ -289,33 +303,49 @@ class SelectiveUpdateBlock:
         plan.coords = torch.arange(W, dtype=torch.float32, device=dev).reshape(1, 1, W, 1).repeat(B, H, 1, 1)
         plan.src_key = [None] * 3  # (tensor, version) of the inp/att tensors last converted
         add = plan.add
-
-        # encoder (core/update.py:62-70): motion = [conv(cat[cor, d]) (127) | disp (1)]  -- side lane
-        add(FORK, FORK)
-        plan.lane = 1
-        c1, c2, d1, d2, motion = new(0, 256), new(0, 256), new(0, 64), new(0, 64), new(0, hd)
-        self._conv(plan, "encoder.convc1", "convc1", [plan.corr16], [(1, [0])], "convc1", _lib.FSB_EPI_RELU, out=c1)
-        self._conv(plan, "encoder.convc2", "convc2", [c1], [(3, [0])], "convc2", _lib.FSB_EPI_RELU, out=c2)
-        add("encoder.convd1", lambda: C.conv7x7_c1(plan.disp, self.f["convd1.w"], self.f["convd1.b"], d1, 64, motion,
-                                                    hd - 1))
-        self._conv(plan, "encoder.convd2", "convd2", [d1], [(3, [0])], "convd2", _lib.FSB_EPI_RELU, out=d2)
-        self._conv(plan, "encoder.conv", "enc_conv", [c2, d2], [(3, [0, 1])], "enc_conv", _lib.FSB_EPI_RELU, out=motion)
-        plan.lane = 0
-        # gru16: x = [inp[2], pool2x(net[1])]                                   (core/update.py:143)
-        p1 = new(2, hd)
-        add("pool2x(net1)", lambda: C.pool2x(plan.h32[1], p1))
-        self._gru(plan, "gru16", 2, [plan.inp16[2], p1])
-        # gru08: x = [inp[1], pool2x(net[0]), interp(net[2])]                   (:146)
-        p0, u2 = new(1, hd), new(1, hd)
-        add("pool2x(net0)", lambda: C.pool2x(plan.h32[0], p0))
-        add("interp(net2)", lambda: C.resize(plan.h32[2], u2))
-        self._gru(plan, "gru08", 1, [plan.inp16[1], p0, u2])
-        add(JOIN, JOIN)
-        # gru04: x = [inp[0], motion, interp(net[1])]                           (:151-153)
-        u1 = new(0, hd)
-        add("interp(net1)", lambda: C.resize(plan.h32[1], u1))
-        self._gru(plan, "gru04", 0, [plan.inp16[0], motion, u1])
-        # mask head (core/update.py:134-139,158) -- side lane
+        n = self.n_layers
+        if n == 1:
+            # core/update.py:152: with n_gru_layers == 1 the reference's forward never calls gru04 -- net passes through
+            # unchanged and the motion encoder's result is unused; only the two heads run.
+            pass
+        else:
+            # encoder (core/update.py:62-70): motion = [conv(cat[cor, d]) (127) | disp (1)]  -- side lane
+            add(FORK, FORK)
+            plan.lane = 1
+            c1, c2, d1, d2, motion = new(0, 256), new(0, 256), new(0, 64), new(0, 64), new(0, hd)
+            self._conv(plan, "encoder.convc1", "convc1", [plan.corr16], [(1, [0])], "convc1", _lib.FSB_EPI_RELU, out=c1)
+            self._conv(plan, "encoder.convc2", "convc2", [c1], [(3, [0])], "convc2", _lib.FSB_EPI_RELU, out=c2)
+            add("encoder.convd1", lambda: C.conv7x7_c1(plan.disp, self.f["convd1.w"], self.f["convd1.b"], d1, 64, motion,
+                                                        hd - 1))
+            self._conv(plan, "encoder.convd2", "convd2", [d1], [(3, [0])], "convd2", _lib.FSB_EPI_RELU, out=d2)
+            self._conv(plan, "encoder.conv", "enc_conv", [c2, d2], [(3, [0, 1])], "enc_conv", _lib.FSB_EPI_RELU, out=motion)
+            plan.lane = 0
+            plan.keep += [c1, c2, d1, d2, motion]
+            if n == 3:
+                # gru16: x = [inp[2], pool2x(net[1])]                               (core/update.py:143)
+                p1 = new(2, hd)
+                add("pool2x(net1)", lambda: C.pool2x(plan.h32[1], p1))
+                self._gru(plan, "gru16", 2, [plan.inp16[2], p1])
+                plan.keep.append(p1)
+            # gru08: x = [inp[1], pool2x(net[0]) (, interp(net[2]) with three levels)]  (:145-148)
+            p0 = new(1, hd)
+            add("pool2x(net0)", lambda: C.pool2x(plan.h32[0], p0))
+            xs08 = [plan.inp16[1], p0]
+            if n == 3:
+                u2 = new(1, hd)
+                add("interp(net2)", lambda: C.resize(plan.h32[2], u2))
+                xs08.append(u2)
+            self._gru(plan, "gru08", 1, xs08)
+            add(JOIN, JOIN)
+            # gru04: x = [inp[0], motion, interp(net[1])]                           (:150-153)
+            u1 = new(0, hd)
+            add("interp(net1)", lambda: C.resize(plan.h32[1], u1))
+            self._gru(plan, "gru04", 0, [plan.inp16[0], motion, u1])
+            plan.keep += xs08 + [u1]
+        # mask head (core/update.py:134-139,158) -- side lane; tagged so `refine` can leave it out of the iteration
+        # graph and run it once after the last iteration (only that one's mask is consumed in test_mode,
+        # core/foundation_stereo.py:243-247)
+        plan.tag = "mask"
         add(FORK, FORK)
         plan.lane = 1
         m0 = new(0, 64)
@@ -323,6 +353,7 @@ class SelectiveUpdateBlock:
         self._conv(plan, "mask.2", "mask2", [m0], [(3, [0])], "mask2", _lib.FSB_EPI_RELU, out_f32=plan.mask,
                    out_scale=0.25)
         plan.lane = 0
+        plan.tag = None
         # disp head (core/update.py:20-32) with EdgeNextConvEncoder (core/submodule.py:565-591)
         y = [new(0, hd) for _ in range(3)]
         t, u = new(0, hd), new(0, 4 * hd)
@@ -346,7 +377,7 @@ class SelectiveUpdateBlock:
         self._conv(plan, "disp_head.conv.4", "head4", [y[2]], [(3, [0])], "head4", _lib.FSB_EPI_BIAS,
                    out_f32=plan.delta)
         add(JOIN, JOIN)
-        plan.keep = [p1, p0, u2, c1, c2, d1, d2, motion, u1, y, t, u, m0]
+        plan.keep += [y, t, u, m0]
         return plan
 
     # ---- ingest ---------------------------------------------------------------------------
@@ -366,16 +397,27 @@ class SelectiveUpdateBlock:
         return None
 
     def _ingest(self, plan: _Plan, net, inp, att, corr: Optional[Tensor], disp: Tensor) -> None:
-        for l in range(3):
+        nl = self.n_layers
+        if len(net) < nl or len(inp) < nl or len(att) < nl:
+            raise _lib.FsbError(f"net / inp / att must hold {nl} pyramid levels (n_gru_layers of this update block), got "
+                                f"{len(net)} / {len(inp)} / {len(att)}")
+        for l in range(nl):
             n = net[l]
+            if tuple(n.shape) != (plan.shape[l][0], self.hidden) + tuple(plan.shape[l][1:]):
+                raise _lib.FsbError(f"net[{l}] has shape {tuple(n.shape)}, expected "
+                                    f"{(plan.shape[l][0], self.hidden) + tuple(plan.shape[l][1:])}")
             if not self._is_view_of(n, plan.h32[l]):
                 C.nchw_to_nhwc(n.float().contiguous(), plan.h16[l], plan.h32[l])
             # the context tensors are converted once and reused while the caller passes the SAME tensor objects,
             # unmodified (the reference loop does).  The key holds the tensors themselves: an address alone can be
             # recycled by the caching allocator for another batch's data.
-            key = (inp[l], inp[l]._version, att[l], att[l]._version)
+            # Inference tensors (torch.inference_mode, scripts/train.py:515) keep no version counter: None = never
+            # trusted, reconvert every call.
+            ver = lambda t: None if t.is_inference() else t._version
+            key = (inp[l], ver(inp[l]), att[l], ver(att[l]))
             old = plan.src_key[l]
-            if old is None or old[0] is not key[0] or old[2] is not key[2] or old[1] != key[1] or old[3] != key[3]:
+            if (old is None or key[1] is None or key[3] is None or old[0] is not key[0] or old[2] is not key[2]
+                    or old[1] != key[1] or old[3] != key[3]):
                 C.nchw_to_nhwc(inp[l].float().contiguous(), plan.inp16[l], None)
                 plan.att[l].copy_(att[l].reshape(plan.att[l].shape))
                 plan.src_key[l] = key
@@ -385,14 +427,26 @@ class SelectiveUpdateBlock:
             view = self._corr_view(corr)
             if view is None or view.data_ptr() != plan.corr16.data_ptr():
                 # the reference's fp32 (B, L*K*(Cg+1), H, W) tensor (or a foreign 16-bit one)
+                if corr.shape[1] != self.planes:
+                    raise _lib.FsbError(f"corr has {corr.shape[1]} channels, encoder.convc1 takes {self.planes} "
+                                        "(corr_levels * (2*corr_radius+1) * (volume_dim+1), core/update.py:55)")
                 C.nchw_to_nhwc(corr.float().contiguous(), plan.corr16, None)
+
+    @staticmethod
+    def _no_autograd(*tensors) -> None:
+        """The engine is inference-only: its outputs carry no graph.  Raise rather than hand detached
+        tensors to a caller that is recording one (scripts/train.py:333 differentiates through the block)."""
+        if torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in tensors):
+            raise _lib.FsbError("the B200 update block is inference-only (no autograd formula): call it under "
+                                "torch.no_grad() / torch.inference_mode(), or uninstall() it for training")
 
     # ---- one step -------------------------------------------------------------------------
     def plan_for(self, B: int, H: int, W: int) -> _Plan:
         key = (B, H, W)
         plan = self._plans.get(key)
         if plan is None:
-            plan = self._plans[key] = self._build_plan(B, H, W)
+            with torch.cuda.device(self.device):
+                plan = self._plans[key] = self._build_plan(B, H, W)
         return plan
 
     def corr_buffer(self, B: int, H: int, W: int) -> Tensor:
@@ -400,16 +454,19 @@ class SelectiveUpdateBlock:
         output writes here and convc1 reads it in place."""
         return self.plan_for(B, H, W).corr16
 
-    def run_steps(self, plan: _Plan, lookup: bool = False) -> None:
+    def run_steps(self, plan: _Plan, lookup: bool = False, mask: bool = True, only_mask: bool = False) -> None:
         """The launches of one refinement step, issued on the current stream and the plan's
         side stream (no graph).  With ``lookup`` the bound geometry lookup runs first and the
-        disparity update (core/foundation_stereo.py:242) last: one whole loop iteration."""
+        disparity update (core/foundation_stereo.py:242) last: one whole loop iteration.
+        ``mask=False`` leaves the mask head out; ``only_mask`` runs nothing else."""
         main = torch.cuda.current_stream()
         if lookup:
             plan.lookup()
         single = not self.two_lanes
-        for fn, lane in zip(plan.steps, plan.lanes):
-            if single:
+        for fn, lane, tag in zip(plan.steps, plan.lanes, plan.tags):
+            if (tag == "mask") != only_mask and (only_mask or not mask):
+                continue
+            if single or only_mask:
                 if fn is not FORK and fn is not JOIN:
                     fn()
                 continue
@@ -425,12 +482,12 @@ class SelectiveUpdateBlock:
         if lookup:
             C.axpy(plan.disp, plan.delta)
 
-    def _capture(self, plan: _Plan, lookup: bool) -> torch.cuda.CUDAGraph:
+    def _capture(self, plan: _Plan, lookup: bool, mask: bool = True) -> torch.cuda.CUDAGraph:
         g = torch.cuda.CUDAGraph()
         torch.cuda.synchronize()
         n0 = _lib.launch_count()
         with torch.cuda.graph(g):
-            self.run_steps(plan, lookup)
+            self.run_steps(plan, lookup, mask)
         g.fsb_kernels = _lib.launch_count() - n0  # libfsb200 kernels one replay launches
         return g
 
@@ -452,15 +509,23 @@ class SelectiveUpdateBlock:
     def forward(self, net: List[Tensor], inp: Sequence[Tensor], corr: Tensor, disp: Tensor,
                 att: Sequence[Tensor]) -> Tuple[List[Tensor], Tensor, Tensor]:
         """Same contract as core/update.py:141-159: mutates and returns ``net``; returns
-        (net, mask, delta_disp) as fp32 tensors."""
+        (net, mask, delta_disp) as fp32 tensors.  The results are views of the engine's own buffers,
+        valid until the next call on the same (B,H,W) (the reference loop consumes them at once,
+        core/foundation_stereo.py:240-247); ``copy_outputs=True`` at construction returns fresh tensors."""
         if not disp.is_cuda:
             raise _lib.FsbError("SelectiveUpdateBlock runs on CUDA tensors only (no CPU path)")
+        self._no_autograd(*net, *inp, corr, disp, *att)
         B, _, H, W = disp.shape
-        plan = self.plan_for(B, H, W)
-        self._ingest(plan, net, inp, att, corr, disp)
-        self._execute(plan)
-        for l in range(3):
-            net[l] = plan.h32[l].permute(0, 3, 1, 2)
+        with torch.cuda.device(self.device):
+            plan = self.plan_for(B, H, W)
+            self._ingest(plan, net, inp, att, corr, disp)
+            self._execute(plan)
+            for l in range(self.n_layers):
+                net[l] = plan.h32[l].permute(0, 3, 1, 2)
+            if self.copy_outputs:
+                for l in range(self.n_layers):
+                    net[l] = net[l].clone()
+                return net, plan.mask.clone(), plan.delta.clone()
         return net, plan.mask, plan.delta
 
     __call__ = forward
@@ -468,31 +533,41 @@ class SelectiveUpdateBlock:
     # ---- the whole refinement loop (core/foundation_stereo.py:236-242) -----------------------
     @torch.no_grad()
     def refine(self, geo, net: Sequence[Tensor], inp: Sequence[Tensor], att: Sequence[Tensor], disp: Tensor,
-               iters: int) -> Tuple[Tensor, Tensor, List[Tensor]]:
+               iters: int, mask_every_iter: bool = False) -> Tuple[Tensor, Tensor, List[Tensor]]:
         """``iters`` x [geo lookup -> update block -> disp += delta] with every iteration ONE
         CUDA-graph replay: the lookup writes the 16-bit NHWC tensor convc1 reads, the update
         runs on the plan's static buffers and the disparity is updated in place, so there is no
         host work or host sync between iterations.  ``geo`` is a Combined_Geo_Encoding_Volume
         (its level buffers should have stable addresses -- ``workspace=`` -- or the graph is
-        re-captured).  Returns (disparity (B,1,H,W) fp32, mask features of the last step, net)."""
+        re-captured).  Returns (disparity (B,1,H,W) fp32, mask features of the last step, net).
+
+        The mask head (core/update.py:134-139,158) depends on net[0] only and, in test_mode, only the
+        last iteration's result is consumed (core/foundation_stereo.py:243-247).  This method owns the
+        loop, so by default it runs the mask head ONCE, after the last iteration -- the same values the
+        reference's last call returns; ``mask_every_iter=True`` keeps it inside every iteration like the
+        drop-in ``forward`` does."""
+        self._no_autograd(*net, *inp, disp, *att)
         B, _, H, W = disp.shape
-        plan = self.plan_for(B, H, W)
-        self._ingest(plan, list(net), inp, att, None, disp.float())
-        key = tuple(t.data_ptr() for t in list(geo.geo_levels) + list(geo.corr_levels)) + (geo.radius,)
-        if plan.iter_key != key:
-            levels = (list(geo.geo_levels), list(geo.corr_levels), geo.radius)
-            from . import ops
-            plan.lookup = lambda: ops.geo_lookup_nhwc16(levels[0], levels[1], plan.disp, plan.coords, levels[2],
-                                                        plan.corr16)
-            plan.iter_key = key
-            plan.iter_graph = None
-            plan.iter_calls = 0
-        for _ in range(iters):
-            plan.iter_calls += 1
-            if not self.use_graph or plan.iter_calls == 1:
-                self.run_steps(plan, True)
-                continue
-            if plan.iter_graph is None:
-                plan.iter_graph = self._capture(plan, True)
-            self._replay(plan.iter_graph)
-        return plan.disp.clone(), plan.mask, [plan.h32[l].permute(0, 3, 1, 2) for l in range(3)]
+        with torch.cuda.device(self.device):
+            plan = self.plan_for(B, H, W)
+            self._ingest(plan, list(net), inp, att, None, disp.float())
+            key = tuple(t.data_ptr() for t in list(geo.geo_levels) + list(geo.corr_levels)) + (geo.radius, mask_every_iter)
+            if plan.iter_key != key:
+                levels = (list(geo.geo_levels), list(geo.corr_levels), geo.radius)
+                from . import ops
+                plan.lookup = lambda: ops.geo_lookup_nhwc16(levels[0], levels[1], plan.disp, plan.coords, levels[2],
+                                                            plan.corr16)
+                plan.iter_key = key
+                plan.iter_graph = None
+                plan.iter_calls = 0
+            for _ in range(iters):
+                plan.iter_calls += 1
+                if not self.use_graph or plan.iter_calls == 1:
+                    self.run_steps(plan, True, mask_every_iter)
+                    continue
+                if plan.iter_graph is None:
+                    plan.iter_graph = self._capture(plan, True, mask_every_iter)
+                self._replay(plan.iter_graph)
+            if not mask_every_iter:
+                self.run_steps(plan, only_mask=True)
+            return plan.disp.clone(), plan.mask, [plan.h32[l].permute(0, 3, 1, 2) for l in range(self.n_layers)]

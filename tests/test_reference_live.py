@@ -1,0 +1,55 @@
+"""CPU tests that run the UNMODIFIED reference (oracle/_ref, or /root/reference in the build container) beside the
+oracle restatement on fresh seeded inputs -- the live counterpart of the committed golden vectors -- and check the
+harness pieces the GPU end-to-end test relies on (stand-ins, recorder, the restated hot loop)."""
+import pytest
+import torch
+
+import oracle
+from conftest import rel_err
+from oracle import refmodel as rm
+
+pytestmark = pytest.mark.skipif(not rm.available(), reason="reference not available (tools/make_ref.py makes oracle/_ref)")
+
+
+def test_volumes_and_geo_match_reference_live():
+    ns = rm.import_reference()
+    x = oracle.make_inputs(B=2, C=32, H=9, W=21, D=11, Cg=28, seed=21)
+    with torch.no_grad():
+        assert torch.equal(ns.build_gwc_volume(x["fl"], x["fr"], 11, 8), oracle.gwc_volume(x["fl"], x["fr"], 11, 8))
+        assert torch.equal(ns.build_concat_volume(x["pl"], x["pr"], 11), oracle.concat_volume(x["pl"], x["pr"], 11))
+        dx = torch.linspace(-4, 4, 9).reshape(1, 1, 9, 1)
+        ref = ns.Combined_Geo_Encoding_Volume(x["fl"], x["fr"], x["volume"], num_levels=2, dx=dx)
+        mine = oracle.GeoEncodingVolume(x["fl"], x["fr"], x["volume"], 2, 4)
+        assert rel_err(mine(x["disp"], x["coords"]), ref(x["disp"], x["coords"])) <= 1e-5
+
+
+def test_update_block_matches_reference_live():
+    p = oracle.make_update_block_params(seed=3)
+    ub = rm.make_reference_update_block(p)
+    x = oracle.make_inputs(B=1, C=16, H=16, W=24, D=12, Cg=28, seed=22)
+    with torch.no_grad():
+        geo = oracle.GeoEncodingVolume(x["fl"], x["fr"], x["volume"], 2, 4)
+        corr = geo(x["disp"], x["coords"])
+        want = ub([t.clone() for t in x["net"]], list(x["inp"]), corr, x["disp"], list(x["att"]))
+        got = oracle.update_block(p, [t.clone() for t in x["net"]], x["inp"], corr, x["disp"], x["att"])
+    for a, b in zip(got[0], want[0]):
+        assert rel_err(a, b) <= 1e-5
+    assert rel_err(got[1], want[1]) <= 1e-5 and rel_err(got[2], want[2]) <= 1e-5
+
+
+def test_full_model_runs_and_loop_restatement_matches_forward():
+    """FoundationStereo (random init, small image) through the harness on the CPU: the stock forward's
+    1/4-res trajectory equals `refmodel.reference_loop` fed with the recorded hot-path inputs, i.e. the
+    driver the GPU test uses for the noise floor IS the reference's loop."""
+    model = rm.build_model("vits", max_disp=64, mixed_precision=False, seed=0)
+    left, right = rm.make_pair(1, 64, 96, max_disp=12, seed=2)
+    fs = rm.import_model_module()
+    with rm.sdpa_instead_of_flash_attn(), torch.no_grad():
+        with rm.Recorder(model) as rec:
+            up = model(left, right, iters=3, test_mode=True)
+        assert rec.calls == 3 and up.shape == (1, 1, 64, 96)
+        disp, mask, states = rm.reference_loop(model.update_block, fs.Combined_Geo_Encoding_Volume, rec.geo_args,
+                                               rec.first, 3, autocast=False, trace=True)
+        assert len(states) == 3
+        again = model.upsample_disp(disp, mask.float(), model.stem_2(fs.normalize_image(left)).float())
+    assert torch.allclose(again, up, atol=1e-5), float((again - up).abs().max())
