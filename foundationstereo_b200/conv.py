@@ -188,6 +188,18 @@ def edgenext_mlp(x: Tensor, w1: Tensor, b1: Tensor, w2: Tensor, b2: Tensor, gamm
                                  res.data_ptr(), out.data_ptr(), x.numel() // C, C, F, _DT[x.dtype], _stream()))
 
 
+def conv3x3_cout1(x: Tensor, weight: Tensor, bias: Tensor, delta: Tensor, disp_accum: Optional[Tensor]) -> None:
+    """delta = conv3x3(x; C -> 1) + bias on CUDA cores (csrc/nhwc.cu); with ``disp_accum`` also disp_accum += delta.
+    x 16-bit NHWC (B,H,W,C); weight fp32 (9, C); delta / disp_accum fp32 (B,1,H,W)."""
+    B, H, W, C = x.shape
+    assert weight.dtype == torch.float32 and weight.shape == (9, C) and weight.is_contiguous()
+    assert delta.dtype == torch.float32 and delta.numel() == B * H * W
+    assert disp_accum is None or (disp_accum.dtype == torch.float32 and disp_accum.numel() == B * H * W)
+    check(lib().fsb_conv3x3_cout1(x.data_ptr(), weight.data_ptr(), bias.data_ptr(), delta.data_ptr(),
+                                  disp_accum.data_ptr() if disp_accum is not None else None, B, C, H, W, _DT[x.dtype],
+                                  _stream()))
+
+
 def axpy(y: Tensor, x: Tensor) -> None:
     assert y.dtype == x.dtype == torch.float32 and y.numel() == x.numel()
     check(lib().fsb_axpy_f32(y.data_ptr(), x.data_ptr(), y.numel(), _stream()))

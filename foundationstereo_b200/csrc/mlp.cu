@@ -17,7 +17,8 @@
 //   j+1 while the epilogue warps run the GELU of chunk j; both accumulators are double-buffered, so the
 //   final epilogue (+b2, *gamma, +res, 16-bit store) of tile t overlaps the GEMMs of tile t+1.
 //   W1 / W2 (256 KB) stream from L2 through a 5-stage ring of 16 KB tiles in consumption order.
-// The kernel is bound by the GELU arithmetic (512 per pixel), which is what should bound this op.
+// The kernel is bound by the GELU arithmetic (512 per pixel), which is what should bound this op; the GELU runs on
+// the packed fp32 datapath with one MUFU per element (gelu2_f, umma.cuh).
 #include "common.cuh"
 #include "umma.cuh"
 
@@ -237,7 +238,8 @@ edgenext_mlp_kernel(const __grid_constant__ MlpParams p) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           const float2 bb = *reinterpret_cast<const float2*>(bias + 2 * i);
-          pk[i] = pack2<T>(gelu_f(__uint_as_float(v[2 * i]) + bb.x), gelu_f(__uint_as_float(v[2 * i + 1]) + bb.y));
+          const float2 y = gelu2_f(__fadd2_rn(make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1])), bb));
+          pk[i] = pack2<T>(y.x, y.y);
         }
         mbar_wait(h_empty + 8 * b, (use & 1) ^ 1);  // G2 of the chunk two back has read H[b]
         uint8_t* hb = hrow + b * 2 * kMlpTile;

@@ -253,6 +253,14 @@ template <> __device__ __forceinline__ float4 load4_f32<__nv_bfloat16>(const __n
   return make_float4(a.x, a.y, b.x, b.y);
 }
 
+template <typename T> __device__ __forceinline__ float2 unpack2f(uint32_t v);
+template <> __device__ __forceinline__ float2 unpack2f<__half>(uint32_t v) {
+  return __half22float2(*reinterpret_cast<const __half2*>(&v));
+}
+template <> __device__ __forceinline__ float2 unpack2f<__nv_bfloat16>(uint32_t v) {
+  return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v));
+}
+
 // PERSISTENT: a CTA keeps the 49 x 64 weights of its channel group in shared memory and walks the pixel tiles
 // tile = blockIdx.x, blockIdx.x + gridDim.x, ...; the input patch of the NEXT tile streams in with cp.async
 // (zero fill outside the image) while the current one is computed -- as one-tile CTAs the kernel spent 40 % of
@@ -314,24 +322,30 @@ dwconv7x7_kernel(const T* __restrict__ x, const float* __restrict__ weight, cons
     const int txi = tile % tiles_x, r1 = tile / tiles_x;
     const int tx0 = txi * kDwTX, ty0 = (r1 % tiles_y) * kDwTY, b = r1 / tiles_y;
     const int y = ty0 + row, xb = tx0 + xs * kDwR;
-    float acc[kDwR][4];
+    // fp32 accumulation as PACKED pairs: on sm_100 a scalar FFMA issues every other cycle per scheduler while
+    // fma.rn.f32x2 (FFMA2) does two lanes' worth per instruction -- this FMA-bound kernel needs it to reach the
+    // 128 FMA/clk/SM the part is specified with (83 -> measured below).
+    float2 acc[kDwR][2];
 #pragma unroll
-    for (int j = 0; j < kDwR; ++j) { acc[j][0] = bv.x; acc[j][1] = bv.y; acc[j][2] = bv.z; acc[j][3] = bv.w; }
+    for (int j = 0; j < kDwR; ++j) { acc[j][0] = make_float2(bv.x, bv.y); acc[j][1] = make_float2(bv.z, bv.w); }
 #pragma unroll
     for (int ky = 0; ky < 7; ++ky) {  // unrolled: the loads of row ky+1 are scheduled under the FMAs of row ky
-      float4 in[kDwR + 6];
+      float2 in[kDwR + 6][2];
       const T* prow = patch + ((row + ky) * kDwPX + xs * kDwR) * kDwC + cq * 4;
 #pragma unroll
-      for (int j = 0; j < kDwR + 6; ++j) in[j] = load4_f32<T>(prow + j * kDwC);
+      for (int j = 0; j < kDwR + 6; ++j) {
+        const uint2 u = *reinterpret_cast<const uint2*>(prow + j * kDwC);
+        in[j][0] = unpack2f<T>(u.x);
+        in[j][1] = unpack2f<T>(u.y);
+      }
 #pragma unroll
       for (int kx = 0; kx < 7; ++kx) {
         const float4 w = *reinterpret_cast<const float4*>(wsm + (ky * 7 + kx) * kDwC + cq * 4);
+        const float2 w01 = make_float2(w.x, w.y), w23 = make_float2(w.z, w.w);
 #pragma unroll
         for (int j = 0; j < kDwR; ++j) {
-          acc[j][0] = fmaf(in[j + kx].x, w.x, acc[j][0]);
-          acc[j][1] = fmaf(in[j + kx].y, w.y, acc[j][1]);
-          acc[j][2] = fmaf(in[j + kx].z, w.z, acc[j][2]);
-          acc[j][3] = fmaf(in[j + kx].w, w.w, acc[j][3]);
+          acc[j][0] = __ffma2_rn(in[j + kx][0], w01, acc[j][0]);
+          acc[j][1] = __ffma2_rn(in[j + kx][1], w23, acc[j][1]);
         }
       }
     }
@@ -339,9 +353,84 @@ dwconv7x7_kernel(const T* __restrict__ x, const float* __restrict__ weight, cons
       T* o = out + (((size_t)b * H + y) * W + xb) * C + c0 + cq * 4;
 #pragma unroll
       for (int j = 0; j < kDwR; ++j)
-        if (xb + j < W) Quad<T>::store(o + (size_t)j * C, acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
+        if (xb + j < W) Quad<T>::store(o + (size_t)j * C, acc[j][0].x, acc[j][0].y, acc[j][1].x, acc[j][1].y);
     }
     __syncthreads();  // everyone is done with `patch` before the next iteration's prefetch overwrites it
+  }
+}
+
+// ------------------------------------------------------------------ 3x3 convolution C -> 1 (DispHead.conv[4])
+// delta[b,y,x] = bias + sum_{t=(ky,kx)} <in[b, y+ky-1, x+kx-1, :], w[t][:]>   (core/update.py:28, zero padding 1).
+// As an N = 16 tensor-core tile this layer used 6 % of the tensor pipe for 43 us; it is 1152 MACs per pixel of
+// plain dot product.  CTA = 8 x 32 output pixels.  Phase 1: for every pixel of the 10 x 34 input patch the NINE
+// dot products with the per-tap weight vectors (each input pixel is read ONCE, 4 lanes x 64 contiguous bytes per
+// pixel, packed fp32 FMAs, weights broadcast from shared memory), reduced over the 4 lanes by shuffles into a
+// shared [9][10][34] table; phase 2: an output pixel sums its 9 shifted entries.  Optionally also disp += delta
+// (core/foundation_stereo.py:242), which saves the refinement loop a launch.
+constexpr int kC1TY = 8, kC1TX = 32, kC1PY = kC1TY + 2, kC1PX = kC1TX + 2, kC1PS = kC1PX + 1;
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+conv3x3_cout1_kernel(const T* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
+                     float* __restrict__ delta, float* __restrict__ disp, int C, int H, int W) {
+  pdl_launch_dependents();
+  extern __shared__ __align__(16) float c1_sm[];
+  float* ws = c1_sm;                      // [9][C]
+  float* part = c1_sm + 9 * C;            // [9][kC1PY][kC1PS]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, sub = lane & 3;
+  for (int i = tid; i < 9 * C; i += 256) ws[i] = w[i];  // parameters: no kernel writes them
+  const int tiles_x = (W + kC1TX - 1) / kC1TX, tiles_y = (H + kC1TY - 1) / kC1TY;
+  const int txi = blockIdx.x % tiles_x, r1 = blockIdx.x / tiles_x;
+  const int tx0 = txi * kC1TX, ty0 = (r1 % tiles_y) * kC1TY, b = r1 / tiles_y;
+  pdl_wait();
+  __syncthreads();
+  // ---- phase 1: 9 partial dot products per patch pixel; a warp takes 8 consecutive patch pixels per trip
+  for (int p0 = warp * 8; p0 < kC1PY * kC1PX; p0 += 64) {
+    const int pp = p0 + (lane >> 2);
+    const int py = pp / kC1PX, px = pp - py * kC1PX;
+    const int yy = ty0 + py - 1, xx = tx0 + px - 1;
+    const bool ok = pp < kC1PY * kC1PX && yy >= 0 && yy < H && xx >= 0 && xx < W;
+    float2 acc[9];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) acc[t] = make_float2(0.f, 0.f);
+    if (ok) {
+      const T* src = x + (((size_t)b * H + yy) * W + xx) * C + sub * 8;
+      for (int c0 = 0; c0 < C; c0 += 32) {   // the 4 lanes of a pixel read 64 contiguous bytes per trip
+        const uint4 u = *reinterpret_cast<const uint4*>(src + c0);
+        const float2 v0 = unpack2f<T>(u.x), v1 = unpack2f<T>(u.y), v2 = unpack2f<T>(u.z), v3 = unpack2f<T>(u.w);
+        const float* wc = ws + c0 + sub * 8;
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+          const float4 wa = *reinterpret_cast<const float4*>(wc + t * C);
+          const float4 wb = *reinterpret_cast<const float4*>(wc + t * C + 4);
+          acc[t] = __ffma2_rn(v0, make_float2(wa.x, wa.y), acc[t]);
+          acc[t] = __ffma2_rn(v1, make_float2(wa.z, wa.w), acc[t]);
+          acc[t] = __ffma2_rn(v2, make_float2(wb.x, wb.y), acc[t]);
+          acc[t] = __ffma2_rn(v3, make_float2(wb.z, wb.w), acc[t]);
+        }
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      float v = acc[t].x + acc[t].y;
+      v += __shfl_xor_sync(0xffffffffu, v, 1);
+      v += __shfl_xor_sync(0xffffffffu, v, 2);
+      if (sub == (t & 3) && pp < kC1PY * kC1PX) part[(t * kC1PY + py) * kC1PS + px] = v;
+    }
+  }
+  __syncthreads();
+  // ---- phase 2
+  const int oy = tid >> 5, ox = tid & 31;
+  const int y = ty0 + oy, xo = tx0 + ox;
+  if (y < H && xo < W) {
+    float v = __ldg(bias);
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) v += part[((ky * 3 + kx) * kC1PY + oy + ky) * kC1PS + ox + kx];
+    const size_t o = ((size_t)b * H + y) * W + xo;
+    delta[o] = v;
+    if (disp) disp[o] += v;
   }
 }
 
@@ -475,6 +564,29 @@ extern "C" int fsb_dwconv7x7_nhwc(const void* x, const float* weight, const floa
                   (__nv_bfloat16*)out, C, H, W, (int)ntiles);
   }
   FSB_CHECK_LAUNCH("fsb_dwconv7x7_nhwc");
+  return FSB_OK;
+}
+
+extern "C" int fsb_conv3x3_cout1(const void* x, const float* weight, const float* bias, float* delta, float* disp_accum,
+                                 int B, int C, int H, int W, int dtype, fsb_stream_t stream) {
+  using namespace fsb;
+  FSB_REQUIRE(x && weight && bias && delta, FSB_ERR_ARG, "fsb_conv3x3_cout1: NULL pointer");
+  FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && is16(dtype), FSB_ERR_ARG, "fsb_conv3x3_cout1: bad size or dtype");
+  FSB_REQUIRE(C % 32 == 0 && C <= 1024 && aligned16(x) && aligned16(weight), FSB_ERR_SHAPE,
+              "fsb_conv3x3_cout1: C=%d must be a multiple of 32 (<= 1024), x and weight 16-byte aligned", C);
+  const long long tiles = (long long)B * ceil_div(H, kC1TY) * ceil_div(W, kC1TX);
+  FSB_REQUIRE(tiles < (1ll << 31), FSB_ERR_SHAPE, "fsb_conv3x3_cout1: too many tiles");
+  const size_t smem = (size_t)(9 * C + 9 * kC1PY * kC1PS) * sizeof(float);
+  if (dtype == FSB_F16) {
+    cudaError_t e = cudaFuncSetAttribute(conv3x3_cout1_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return cuda_fail(e, "fsb_conv3x3_cout1: cudaFuncSetAttribute");
+    launch_kernel(conv3x3_cout1_kernel<__half>, dim3((unsigned)tiles), dim3(256), smem, (cudaStream_t)stream, (const __half*)x, weight, bias, delta, disp_accum, C, H, W);
+  } else {
+    cudaError_t e = cudaFuncSetAttribute(conv3x3_cout1_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return cuda_fail(e, "fsb_conv3x3_cout1: cudaFuncSetAttribute");
+    launch_kernel(conv3x3_cout1_kernel<__nv_bfloat16>, dim3((unsigned)tiles), dim3(256), smem, (cudaStream_t)stream, (const __nv_bfloat16*)x, weight, bias, delta, disp_accum, C, H, W);
+  }
+  FSB_CHECK_LAUNCH("fsb_conv3x3_cout1");
   return FSB_OK;
 }
 

@@ -64,8 +64,10 @@ class _Plan:
         self.lane = 0
         self.tag: Optional[str] = None
         self.keep: list = []
+        self.accum = False
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.iter_graph: Optional[torch.cuda.CUDAGraph] = None
+        self.loop_graphs: Dict[int, torch.cuda.CUDAGraph] = {}
         self.iter_key = None
         self.lookup: Optional[Callable[[], None]] = None
         self.calls = 0
@@ -94,7 +96,7 @@ class SelectiveUpdateBlock:
     def __init__(self, state_dict: Dict[str, Tensor], device: torch.device | str = "cuda",
                  dtype: torch.dtype = torch.float16, use_graph: bool = True,
                  block_n: Optional[Dict[str, int]] = None, halo: Optional[Sequence[str]] = None,
-                 fused_mlp: bool = True, copy_outputs: bool = False):
+                 fused_mlp: bool = True, copy_outputs: bool = False, dot_head4: bool = True):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("SelectiveUpdateBlock runs on CUDA only (no CPU path)")
@@ -103,8 +105,10 @@ class SelectiveUpdateBlock:
         import os as _os
         self.dtype = dtype
         self.use_graph = use_graph and _os.environ.get("FSB_GRAPH", "1") != "0"
+        self.loop_graph = _os.environ.get("FSB_LOOP_GRAPH", "1") != "0"  # refine(): one graph for all iterations
         self.two_lanes = _os.environ.get("FSB_TWO_LANES", "1") != "0"  # side stream for encoder / mask head
         self.copy_outputs = copy_outputs  # forward returns fresh tensors instead of views of the plan's buffers
+        self.dot_head4 = dot_head4  # False: disp_head.conv.4 as a tensor-core convolution launch + a separate disp += delta
         self.fused_mlp = fused_mlp  # False: pwconv1 / pwconv2 of the disparity head as two convolution launches
         self.bn = dict(DEFAULT_BLOCK_N)
         if block_n:
@@ -215,6 +219,9 @@ class SelectiveUpdateBlock:
                       [sd[pre + ".pwconv1.bias"]], 4 * hd, bn["pw1"])
             self._put(f"pw2_{i}", pre + ".pwconv2", [(sd[pre + ".pwconv2.weight"], [(4 * hd, 4 * hd)])],
                       [sd[pre + ".pwconv2.bias"]], hd, bn["pw2"])
+        # (1, hd, 3, 3) -> [tap][channel] fp32 holding the 16-bit-rounded values the tensor-core path would multiply
+        self.f["head4.w"] = sd["disp_head.conv.4.weight"][0].permute(1, 2, 0).reshape(9, hd).to(self.dtype).float().contiguous()
+        self.f["head4.b"] = sd["disp_head.conv.4.bias"].contiguous()
         self._put("head4", "disp_head.conv.4", [(sd["disp_head.conv.4.weight"], [(hd, hd)])],
                   [sd["disp_head.conv.4.bias"]], 1, bn["head4"])
         self._put("mask0", "mask.0", [(sd["mask.0.weight"], [(hd, hd)])], [sd["mask.0.bias"]], 64, bn["mask0"])
@@ -374,8 +381,14 @@ class SelectiveUpdateBlock:
             self._conv(plan, f"disp_head.conv.{i}.pwconv1", f"pw1_{i}", [t], [(1, [0])], "pw1", _lib.FSB_EPI_GELU, out=u)
             self._conv(plan, f"disp_head.conv.{i}.pwconv2", f"pw2_{i}", [u], [(1, [0])], "pw2", _lib.FSB_EPI_SCALE_RES,
                        out=y[k + 1], res=y[k], gamma=self.f[f"gamma{i}"])
-        self._conv(plan, "disp_head.conv.4", "head4", [y[2]], [(3, [0])], "head4", _lib.FSB_EPI_BIAS,
-                   out_f32=plan.delta)
+        if self.dot_head4:
+            # 128 -> 1 channels: a dot product per pixel on CUDA cores (csrc/nhwc.cu), not an N = 16 tensor tile; in the
+            # loop (`refine`) the same launch also does disp += delta (core/foundation_stereo.py:242)
+            add("disp_head.conv.4", lambda: C.conv3x3_cout1(y[2], self.f["head4.w"], self.f["head4.b"], plan.delta,
+                                                             plan.disp if plan.accum else None))
+        else:
+            self._conv(plan, "disp_head.conv.4", "head4", [y[2]], [(3, [0])], "head4", _lib.FSB_EPI_BIAS,
+                       out_f32=plan.delta)
         add(JOIN, JOIN)
         plan.keep += [y, t, u, m0]
         return plan
@@ -460,6 +473,7 @@ class SelectiveUpdateBlock:
         disparity update (core/foundation_stereo.py:242) last: one whole loop iteration.
         ``mask=False`` leaves the mask head out; ``only_mask`` runs nothing else."""
         main = torch.cuda.current_stream()
+        plan.accum = lookup and self.dot_head4 and not only_mask  # disp += delta inside the disp_head.conv.4 launch
         if lookup:
             plan.lookup()
         single = not self.two_lanes
@@ -479,15 +493,16 @@ class SelectiveUpdateBlock:
             else:
                 with torch.cuda.stream(plan.side):
                     fn()
-        if lookup:
+        if lookup and not plan.accum:
             C.axpy(plan.disp, plan.delta)
 
-    def _capture(self, plan: _Plan, lookup: bool, mask: bool = True) -> torch.cuda.CUDAGraph:
+    def _capture(self, plan: _Plan, lookup: bool, mask: bool = True, repeat: int = 1) -> torch.cuda.CUDAGraph:
         g = torch.cuda.CUDAGraph()
         torch.cuda.synchronize()
         n0 = _lib.launch_count()
         with torch.cuda.graph(g):
-            self.run_steps(plan, lookup, mask)
+            for _ in range(repeat):
+                self.run_steps(plan, lookup, mask)
         g.fsb_kernels = _lib.launch_count() - n0  # libfsb200 kernels one replay launches
         return g
 
@@ -505,7 +520,6 @@ class SelectiveUpdateBlock:
             plan.graph = self._capture(plan, False)
         self._replay(plan.graph)
 
-    @torch.no_grad()
     def forward(self, net: List[Tensor], inp: Sequence[Tensor], corr: Tensor, disp: Tensor,
                 att: Sequence[Tensor]) -> Tuple[List[Tensor], Tensor, Tensor]:
         """Same contract as core/update.py:141-159: mutates and returns ``net``; returns
@@ -514,9 +528,9 @@ class SelectiveUpdateBlock:
         core/foundation_stereo.py:240-247); ``copy_outputs=True`` at construction returns fresh tensors."""
         if not disp.is_cuda:
             raise _lib.FsbError("SelectiveUpdateBlock runs on CUDA tensors only (no CPU path)")
-        self._no_autograd(*net, *inp, corr, disp, *att)
+        self._no_autograd(*net, *inp, corr, disp, *att)   # checked in the CALLER's grad mode
         B, _, H, W = disp.shape
-        with torch.cuda.device(self.device):
+        with torch.no_grad(), torch.cuda.device(self.device):
             plan = self.plan_for(B, H, W)
             self._ingest(plan, net, inp, att, corr, disp)
             self._execute(plan)
@@ -531,7 +545,6 @@ class SelectiveUpdateBlock:
     __call__ = forward
 
     # ---- the whole refinement loop (core/foundation_stereo.py:236-242) -----------------------
-    @torch.no_grad()
     def refine(self, geo, net: Sequence[Tensor], inp: Sequence[Tensor], att: Sequence[Tensor], disp: Tensor,
                iters: int, mask_every_iter: bool = False) -> Tuple[Tensor, Tensor, List[Tensor]]:
         """``iters`` x [geo lookup -> update block -> disp += delta] with every iteration ONE
@@ -548,7 +561,7 @@ class SelectiveUpdateBlock:
         drop-in ``forward`` does."""
         self._no_autograd(*net, *inp, disp, *att)
         B, _, H, W = disp.shape
-        with torch.cuda.device(self.device):
+        with torch.no_grad(), torch.cuda.device(self.device):
             plan = self.plan_for(B, H, W)
             self._ingest(plan, list(net), inp, att, None, disp.float())
             key = tuple(t.data_ptr() for t in list(geo.geo_levels) + list(geo.corr_levels)) + (geo.radius, mask_every_iter)
@@ -559,15 +572,25 @@ class SelectiveUpdateBlock:
                                                             plan.corr16)
                 plan.iter_key = key
                 plan.iter_graph = None
+                plan.loop_graphs = {}
                 plan.iter_calls = 0
-            for _ in range(iters):
-                plan.iter_calls += 1
-                if not self.use_graph or plan.iter_calls == 1:
-                    self.run_steps(plan, True, mask_every_iter)
-                    continue
-                if plan.iter_graph is None:
-                    plan.iter_graph = self._capture(plan, True, mask_every_iter)
-                self._replay(plan.iter_graph)
+            if self.use_graph and self.loop_graph and plan.iter_calls > 0:
+                # the WHOLE loop as one graph (iters x 30-odd kernel nodes): programmatic dependent launch keeps
+                # overlapping kernel tails across iteration boundaries and the host launches once per pair batch
+                g = plan.loop_graphs.get(iters)
+                if g is None:
+                    g = plan.loop_graphs[iters] = self._capture(plan, True, mask_every_iter, iters)
+                self._replay(g)
+                plan.iter_calls += iters
+            else:
+                for _ in range(iters):
+                    plan.iter_calls += 1
+                    if not self.use_graph or plan.iter_calls == 1:
+                        self.run_steps(plan, True, mask_every_iter)
+                        continue
+                    if plan.iter_graph is None:
+                        plan.iter_graph = self._capture(plan, True, mask_every_iter)
+                    self._replay(plan.iter_graph)
             if not mask_every_iter:
                 self.run_steps(plan, only_mask=True)
             return plan.disp.clone(), plan.mask, [plan.h32[l].permute(0, 3, 1, 2) for l in range(self.n_layers)]

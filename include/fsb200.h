@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define FSB_VERSION 120 /* major*100 + minor */
+#define FSB_VERSION 130 /* major*100 + minor */
 #define FSB_MAX_LEVELS 6
 
 typedef void* fsb_stream_t; /* cudaStream_t */
@@ -244,6 +244,13 @@ int fsb_dwconv7x7_nhwc(const void* x, const float* weight, const float* bias, vo
 int fsb_edgenext_mlp(const void* x, const void* w1, const float* b1, const void* w2, const float* b2,
                      const float* gamma, const void* res, void* out, long long npix, int C, int F, int dtype,
                      fsb_stream_t stream);
+/* DispHead's last layer (core/update.py:28): 3x3 convolution C -> 1, pad 1, + bias, on CUDA cores (1152 MACs per pixel
+ * of plain dot product; as a tensor-core tile it used 6 % of the pipe).
+ *   x 16-bit NHWC (B,H,W,C), C a multiple of 32; weight fp32 [9][C] (tap (ky,kx) row-major, then channel); bias fp32 [1];
+ *   delta fp32 (B,1,H,W) out.  If disp_accum != NULL also disp_accum += delta (the disparity update of
+ *   core/foundation_stereo.py:242 folded into the same launch). */
+int fsb_conv3x3_cout1(const void* x, const float* weight, const float* bias, float* delta, float* disp_accum, int B,
+                      int C, int H, int W, int dtype, fsb_stream_t stream);
 /* y += x (fp32, n elements): the disparity update of core/foundation_stereo.py:242 */
 int fsb_axpy_f32(float* y, const float* x, size_t n, fsb_stream_t stream);
 

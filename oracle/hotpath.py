@@ -262,12 +262,20 @@ def update_block(
     disp: Tensor,
     att: Sequence[Tensor],
 ) -> Tuple[List[Tensor], Tensor, Tensor]:
-    """BasicSelectiveMultiUpdateBlock.forward for n_gru_layers == 3
-    (core/update.py:141-159).  Mutates and returns ``net`` like the reference."""
-    net[2] = selective_gru(p, "gru16", att[2], net[2], inp[2], pool2x(net[1]))
-    net[1] = selective_gru(p, "gru08", att[1], net[1], inp[1], pool2x(net[0]), resize_like(net[2], net[1]))
-    motion = torch.cat([inp[0], motion_encoder(p, disp, corr)], 1)
-    net[0] = selective_gru(p, "gru04", att[0], net[0], motion, resize_like(net[1], net[0]))
+    """BasicSelectiveMultiUpdateBlock.forward (core/update.py:141-159).  Mutates and returns ``net`` like the
+    reference.  n_gru_layers is read off the parameter dict (which GRUs it holds, core/update.py:128-132):
+    3 = gru16 + gru08 + gru04; 2 = gru08 (two inputs) + gru04; 1 = NO GRU at all -- the reference only calls
+    gru04 under ``n_gru_layers > 1`` (:152), so net passes through and only the two heads run."""
+    n = 3 if "gru16.conv0.0.weight" in p else 2 if "gru08.conv0.0.weight" in p else 1
+    if n == 3:
+        net[2] = selective_gru(p, "gru16", att[2], net[2], inp[2], pool2x(net[1]))
+    if n >= 2:
+        if n > 2:
+            net[1] = selective_gru(p, "gru08", att[1], net[1], inp[1], pool2x(net[0]), resize_like(net[2], net[1]))
+        else:
+            net[1] = selective_gru(p, "gru08", att[1], net[1], inp[1], pool2x(net[0]))
+        motion = torch.cat([inp[0], motion_encoder(p, disp, corr)], 1)
+        net[0] = selective_gru(p, "gru04", att[0], net[0], motion, resize_like(net[1], net[0]))
     delta = disp_head(p, net[0])
     mask = mask_head(p, net[0])
     return net, mask, delta

@@ -19,9 +19,9 @@ import torch
 
 
 def update_block_param_shapes(
-    corr_levels: int = 2, corr_radius: int = 4, hidden: int = 128, volume_dim: int = 28
+    corr_levels: int = 2, corr_radius: int = 4, hidden: int = 128, volume_dim: int = 28, n_gru_layers: int = 3
 ) -> "OrderedDict[str, Tuple[int, ...]]":
-    """name -> shape for n_gru_layers == 3."""
+    """name -> shape; which GRUs exist and their input widths follow core/update.py:128-132."""
     s: "OrderedDict[str, Tuple[int, ...]]" = OrderedDict()
 
     def conv(name, cout, cin, k):
@@ -34,7 +34,10 @@ def update_block_param_shapes(
     conv("encoder.convd1", 64, 1, 7)
     conv("encoder.convd2", 64, 64, 3)
     conv("encoder.conv", hidden - 1, 64 + 256, 3)
-    for name, cin in (("gru16", 2 * hidden), ("gru08", 3 * hidden), ("gru04", 3 * hidden)):
+    grus = {3: (("gru16", 2 * hidden), ("gru08", 3 * hidden), ("gru04", 3 * hidden)),
+            2: (("gru08", 2 * hidden), ("gru04", 3 * hidden)),
+            1: (("gru04", 2 * hidden),)}[n_gru_layers]
+    for name, cin in grus:
         conv(name + ".conv0.0", cin, cin, 3)
         conv(name + ".conv1.0", cin + hidden, cin + hidden, 3)
         for gate in ("convz", "convr", "convq"):
@@ -64,6 +67,7 @@ def make_update_block_params(
     hidden: int = 128,
     volume_dim: int = 28,
     delta_scale: float = 1.0,
+    n_gru_layers: int = 3,
 ) -> Dict[str, torch.Tensor]:
     """U(-1/sqrt(fan_in), 1/sqrt(fan_in)) weights and biases (PyTorch's default
     conv/linear range), layer-scale gammas in [0.1, 0.2] so that the EdgeNeXt
@@ -73,7 +77,7 @@ def make_update_block_params(
     (SURVEY.md H10)."""
     g = torch.Generator().manual_seed(seed)
     out: Dict[str, torch.Tensor] = {}
-    shapes = update_block_param_shapes(corr_levels, corr_radius, hidden, volume_dim)
+    shapes = update_block_param_shapes(corr_levels, corr_radius, hidden, volume_dim, n_gru_layers)
     fan_in: Dict[str, int] = {}
     for name, shp in shapes.items():
         if name.endswith(".weight"):

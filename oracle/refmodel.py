@@ -332,10 +332,11 @@ def reference_loop(update_block, geo_cls, geo_args, first, iters: int, autocast:
 # ---------------------------------------------------------------------------------------------
 # the reference's hot path on the CPU (bench.py's cpu_baseline / --impl reference legs)
 # ---------------------------------------------------------------------------------------------
-def make_reference_update_block(state: Dict[str, torch.Tensor], corr_levels: int = 2, corr_radius: int = 4):
+def make_reference_update_block(state: Dict[str, torch.Tensor], corr_levels: int = 2, corr_radius: int = 4,
+                                n_gru_layers: int = 3):
     """The reference's BasicSelectiveMultiUpdateBlock (core/update.py:122-139) with `state` loaded strictly."""
     ns = import_reference()
-    ub = ns.BasicSelectiveMultiUpdateBlock(update_block_args(corr_levels, corr_radius, 3), 128, volume_dim=28)
+    ub = ns.BasicSelectiveMultiUpdateBlock(update_block_args(corr_levels, corr_radius, n_gru_layers), 128, volume_dim=28)
     ub.load_state_dict(state, strict=True)
     return ub.eval()
 

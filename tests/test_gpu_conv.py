@@ -251,3 +251,43 @@ def test_update_block_fused_mlp_equals_two_launches(fsb):
         outs.append((delta.clone(), mask.clone()))
     assert rel_err(outs[0][0].cpu(), outs[1][0].cpu()) <= 4e-3
     assert torch.equal(outs[0][1], outs[1][1])
+
+
+# ------------------------------------------------------------------ DispHead.conv[4] on CUDA cores (csrc/nhwc.cu)
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(2, 13, 37, 128), (1, 8, 32, 128), (3, 17, 70, 64), (1, 1, 1, 32)])
+def test_conv3x3_cout1_vs_torch(fsb, dtype, shape):
+    """3x3 convolution C -> 1 (core/update.py:28) against fp32 PyTorch on the same 16-bit-rounded operands: fp32
+    accumulation, fp32 output -> 1e-4 relative; with disp_accum the same launch adds delta to the disparity."""
+    from foundationstereo_b200 import conv as C
+    B, H, W, Cc = shape
+    x = _rand(B, Cc, H, W, seed=1).to(dtype)
+    w = (_rand(1, Cc, 3, 3, seed=2) / (3 * Cc ** 0.5)).to(dtype)
+    b = _rand(1, seed=3)
+    want = F.conv2d(x.float(), w.float(), b, padding=1)
+    wt = w[0].float().permute(1, 2, 0).reshape(9, Cc).contiguous().cuda()
+    xd = x.permute(0, 2, 3, 1).contiguous().cuda()
+    delta = torch.full((B, 1, H, W), 7.0, device="cuda")
+    C.conv3x3_cout1(xd, wt, b.cuda(), delta, None)
+    assert rel_err(delta.cpu(), want) <= 1e-4
+    disp = _rand(B, 1, H, W, seed=4).cuda()
+    d0 = disp.clone()
+    delta2 = torch.empty_like(delta)
+    C.conv3x3_cout1(xd, wt, b.cuda(), delta2, disp)
+    assert torch.equal(delta2, delta) and torch.equal(disp, d0 + delta)
+
+
+def test_update_block_dot_head4_equals_tensor_core_head4(fsb):
+    """disp_head.conv.4 as the CUDA-core dot kernel vs as a tensor-core convolution launch: same operands, fp32
+    accumulation in both -> delta agrees to accumulation-order noise."""
+    import oracle
+    p = oracle.make_update_block_params(seed=4)
+    x = oracle.make_inputs(B=2, C=16, H=20, W=44, D=8, Cg=28, seed=10)
+    c = lambda t: t.cuda()
+    outs = []
+    for dot in (True, False):
+        ub = fsb.SelectiveUpdateBlock(p, "cuda", use_graph=False, dot_head4=dot)
+        corr = _rand(2, ub.planes, 20, 44, seed=5).cuda()
+        net, mask, delta = ub([c(t) for t in x["net"]], [c(t) for t in x["inp"]], corr, c(x["disp"]), [c(t) for t in x["att"]])
+        outs.append(delta.clone())
+    assert rel_err(outs[0].cpu(), outs[1].cpu()) <= 1e-4

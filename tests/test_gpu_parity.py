@@ -367,3 +367,73 @@ def test_corr_tensor_core_modes(fsb, shape):
         assert rel_err(x1[l].cpu(), w) <= 2e-3, (l, rel_err(x1[l].cpu(), w))
     # pooled levels are exact means of the level below (same registers)
     assert torch.equal(x3[1], (x3[0][:, 0:2 * (W // 2):2] + x3[0][:, 1:2 * (W // 2):2]) * 0.5)
+
+
+# ------------------------------------------------------------- contract edges of the update block
+@pytest.mark.parametrize("n_layers,levels", [(2, 2), (1, 2), (3, 4)])
+def test_update_block_layers_and_levels_vs_oracle(fsb, n_layers, levels):
+    """n_gru_layers 1 and 2 (core/update.py:128-132,142-153; with ONE layer the reference never calls gru04, so
+    net passes through) and corr_levels = 4 (the in-tree training default: 1044 lookup channels -> 1088 padded)."""
+    H, W, D = 24, 40, 32
+    p = oracle.make_update_block_params(seed=6, corr_levels=levels, n_gru_layers=n_layers)
+    x = oracle.make_inputs(B=2, C=16, H=H, W=W, D=D, Cg=28, seed=13)
+    with torch.no_grad():
+        geo = oracle.GeoEncodingVolume(x["fl"], x["fr"], x["volume"], levels, 4)
+        corr = geo(x["disp"], x["coords"])
+        want_net, want_mask, want_delta = oracle.update_block(p, [t.clone() for t in x["net"][:n_layers]], x["inp"], corr,
+                                                              x["disp"], x["att"])
+    ub = fsb.SelectiveUpdateBlock(p, "cuda")
+    assert ub.n_layers == n_layers
+    c = lambda t: t.cuda()
+    nets = [c(t) for t in x["net"][:n_layers]]
+    net, mask, delta = ub(nets, [c(t) for t in x["inp"][:n_layers]], c(corr), c(x["disp"]), [c(t) for t in x["att"][:n_layers]])
+    assert net is nets and len(net) == n_layers
+    for i in range(n_layers):
+        assert rel_err(net[i].cpu(), want_net[i]) <= TOL_F16
+    assert rel_err(mask.cpu(), want_mask) <= TOL_F16
+    assert rel_err(delta.cpu(), want_delta) <= TOL_F16
+    # the fused 16-bit lookup feeds the same block (corr_levels 4: 1088-channel buffer)
+    dx = torch.linspace(-4, 4, 9).reshape(1, 1, -1, 1)
+    vol = fsb.Combined_Geo_Encoding_Volume(c(x["fl"]), c(x["fr"]), c(x["volume"]), num_levels=levels, dx=dx,
+                                           nhwc16_out=ub.corr_buffer)
+    nets2 = [c(t) for t in x["net"][:n_layers]]
+    feat16 = vol(c(x["disp"]), c(x["coords"]))
+    net2, mask2, delta2 = ub(nets2, [c(t) for t in x["inp"][:n_layers]], feat16, c(x["disp"]), [c(t) for t in x["att"][:n_layers]])
+    assert rel_err(delta2.cpu(), want_delta) <= TOL_F16
+
+
+def test_update_block_rejects_wrong_shapes(fsb):
+    p = oracle.make_update_block_params(seed=6)
+    ub = fsb.SelectiveUpdateBlock(p, "cuda")
+    x = oracle.make_inputs(B=1, C=16, H=16, W=24, D=8, Cg=28, seed=1)
+    c = lambda t: t.cuda()
+    good = ([c(t) for t in x["net"]], [c(t) for t in x["inp"]], torch.zeros(1, ub.planes, 16, 24, device="cuda"),
+            c(x["disp"]), [c(t) for t in x["att"]])
+    with pytest.raises(fsb.FsbError):     # too few pyramid levels
+        ub(good[0][:2], good[1], good[2], good[3], good[4])
+    with pytest.raises(fsb.FsbError):     # lookup tensor of another corr_levels / radius
+        ub(good[0], good[1], torch.zeros(1, ub.planes + 29, 16, 24, device="cuda"), good[3], good[4])
+    with pytest.raises(fsb.FsbError):     # autograd is not supported: raise, do not detach silently
+        with torch.enable_grad():
+            ub([t.requires_grad_() for t in good[0]], good[1], good[2], good[3], good[4])
+
+
+def test_refine_mask_once_equals_mask_every_iteration(fsb):
+    """refine() computes the mask head once after the last iteration by default; with mask_every_iter=True it runs
+    inside every iteration like the drop-in forward: the returned mask, disparity and hidden state are identical."""
+    H, W, D, iters = 24, 40, 16, 4
+    p = oracle.make_update_block_params(seed=2)
+    x = oracle.make_inputs(B=1, C=32, H=H, W=W, D=D, Cg=28, seed=4)
+    c = lambda t: t.cuda()
+    dx = torch.linspace(-4, 4, 9).reshape(1, 1, -1, 1)
+    res = []
+    for every in (False, True):
+        ub = fsb.SelectiveUpdateBlock(p, "cuda")
+        ws = fsb.Combined_Geo_Encoding_Volume.make_workspace(1, 28, D, H, W, W, 2, "cuda")
+        geo = fsb.Combined_Geo_Encoding_Volume(c(x["fl"]), c(x["fr"]), c(x["volume"]), num_levels=2, dx=dx, workspace=ws)
+        for _ in range(3):  # eager first call, per-iteration graph, whole-loop graph
+            disp, mask, net = ub.refine(geo, [c(t) for t in x["net"]], [c(t) for t in x["inp"]], [c(t) for t in x["att"]],
+                                        c(x["disp"]), iters, mask_every_iter=every)
+            res.append((disp.clone(), mask.clone(), net[0].clone()))
+    for r in res[1:]:
+        assert torch.equal(r[0], res[0][0]) and torch.equal(r[1], res[0][1]) and torch.equal(r[2], res[0][2])

@@ -23,15 +23,20 @@ def test_volumes_and_geo_match_reference_live():
         assert rel_err(mine(x["disp"], x["coords"]), ref(x["disp"], x["coords"])) <= 1e-5
 
 
-def test_update_block_matches_reference_live():
-    p = oracle.make_update_block_params(seed=3)
-    ub = rm.make_reference_update_block(p)
-    x = oracle.make_inputs(B=1, C=16, H=16, W=24, D=12, Cg=28, seed=22)
+@pytest.mark.parametrize("n_layers,levels", [(3, 2), (2, 2), (1, 2), (3, 4)])
+def test_update_block_matches_reference_live(n_layers, levels):
+    """n_gru_layers 1..3 (core/update.py:128-132,142-153; with one layer the reference never calls gru04) and the
+    in-tree training default corr_levels = 4 (configs/train/stereo_v1.json)."""
+    p = oracle.make_update_block_params(seed=3, corr_levels=levels, n_gru_layers=n_layers)
+    ub = rm.make_reference_update_block(p, corr_levels=levels, n_gru_layers=n_layers)
+    x = oracle.make_inputs(B=1, C=16, H=16, W=24, D=24, Cg=28, seed=22)
     with torch.no_grad():
-        geo = oracle.GeoEncodingVolume(x["fl"], x["fr"], x["volume"], 2, 4)
+        geo = oracle.GeoEncodingVolume(x["fl"], x["fr"], x["volume"], levels, 4)
         corr = geo(x["disp"], x["coords"])
-        want = ub([t.clone() for t in x["net"]], list(x["inp"]), corr, x["disp"], list(x["att"]))
-        got = oracle.update_block(p, [t.clone() for t in x["net"]], x["inp"], corr, x["disp"], x["att"])
+        nets = lambda: [t.clone() for t in x["net"][:n_layers]]
+        want = ub(nets(), list(x["inp"]), corr, x["disp"], list(x["att"]))
+        got = oracle.update_block(p, nets(), x["inp"], corr, x["disp"], x["att"])
+    assert len(got[0]) == len(want[0]) == n_layers
     for a, b in zip(got[0], want[0]):
         assert rel_err(a, b) <= 1e-5
     assert rel_err(got[1], want[1]) <= 1e-5 and rel_err(got[2], want[2]) <= 1e-5
