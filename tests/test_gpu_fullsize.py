@@ -27,7 +27,7 @@ def _save():
         json.dump(REPORT, fh, indent=1, sort_keys=True)
 
 
-@pytest.mark.parametrize("B,delta_scale", [(2, 0.25), (1, 1.0)])
+@pytest.mark.parametrize("B,delta_scale", [(2, 1.0), (1, 0.25)])
 def test_config1_full_size_32_iterations_vs_oracle(B, delta_scale):
     import foundationstereo_b200 as fsb
     from foundationstereo_b200 import synthetic
