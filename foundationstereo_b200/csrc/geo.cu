@@ -146,8 +146,9 @@ __device__ __forceinline__ void write_level(const float* t, float* out, int Cg, 
   }
 }
 
+template <typename TIN>
 __global__ void __launch_bounds__(256)
-geo_pyramid_kernel(const float* __restrict__ vol, LevelPtrs lv, int Cg, int D, int H, int W, int L) {
+geo_pyramid_kernel(const TIN* __restrict__ vol, LevelPtrs lv, int Cg, int D, int H, int W, int L) {
   pdl_launch_dependents();  // the next kernel may start its prologue
   pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ float t[];  // [kGeoTD*Cg][kGeoTW+1], row index = dd*Cg + c
@@ -155,14 +156,14 @@ geo_pyramid_kernel(const float* __restrict__ vol, LevelPtrs lv, int Cg, int D, i
   const int w0 = blockIdx.x * kGeoTW, d0 = blockIdx.y * kGeoTD;
   const int bh = blockIdx.z, b = bh / H, h = bh - b * H;
   const size_t HW = (size_t)H * W;
-  const float* src = vol + (size_t)b * Cg * D * HW + (size_t)h * W + w0;
+  const TIN* src = vol + (size_t)b * Cg * D * HW + (size_t)h * W + w0;
   const int n = Cg * kGeoTD * kGeoTW;
   for (int i = tid; i < n; i += 256) {
     const int w = i & (kGeoTW - 1);
     const int r = i >> 5;  // = c*kGeoTD + dd
     const int c = r >> 3, dd = r & 7;
     float v = 0.f;
-    if (d0 + dd < D && w0 + w < W) v = src[((size_t)c * D + d0 + dd) * HW + w];
+    if (d0 + dd < D && w0 + w < W) v = to_f32<TIN>(src[((size_t)c * D + d0 + dd) * HW + w]);
     t[(dd * Cg + c) * (kGeoTW + 1) + w] = v;
   }
   __syncthreads();
@@ -180,9 +181,9 @@ geo_pyramid_kernel(const float* __restrict__ vol, LevelPtrs lv, int Cg, int D, i
 // element j = dd*Cg + c of every pixel's 8*Cg-float output run (level 0) and loops over the 32
 // pixels: smem reads t[j][w] are conflict free (row stride 33), global writes are whole
 // 128-byte lines of a contiguous run, and the pooled levels reuse the same shared tile.
-template <int CG>
+template <int CG, typename TIN>
 __global__ void __launch_bounds__(256)
-geo_pyramid_fast_kernel(const float* __restrict__ vol, LevelPtrs lv, int D, int H, int W, int L) {
+geo_pyramid_fast_kernel(const TIN* __restrict__ vol, LevelPtrs lv, int D, int H, int W, int L) {
   pdl_launch_dependents();  // the next kernel may start its prologue
   pdl_wait();               // inputs written by the previous kernel are complete and visible
   constexpr int R0 = kGeoTD * CG;  // rows of the tile = floats of a level-0 run
@@ -192,7 +193,7 @@ geo_pyramid_fast_kernel(const float* __restrict__ vol, LevelPtrs lv, int D, int 
   const int w0 = blockIdx.x * kGeoTW, d0 = blockIdx.y * kGeoTD;
   const int bh = blockIdx.z, b = bh / H, h = bh - b * H;
   const size_t HW = (size_t)H * W;
-  const float* src = vol + (size_t)b * CG * D * HW + (size_t)h * W + w0;
+  const TIN* src = vol + (size_t)b * CG * D * HW + (size_t)h * W + w0;
   const bool wok = w0 + lane < W;
   // loads: warp = one (c, dd) row of 32 consecutive w (one 128-byte line), 8 rows in flight per warp
   // (all CG loads of a warp are issued before the first is used: ~14 KB in flight per CTA)
@@ -200,7 +201,7 @@ geo_pyramid_fast_kernel(const float* __restrict__ vol, LevelPtrs lv, int D, int 
   float v[CG];
   const bool dok = wok && d0 + warp < D;
 #pragma unroll
-  for (int k = 0; k < CG; ++k) v[k] = dok ? __ldg(src + ((size_t)k * D + d0 + warp) * HW + lane) : 0.f;
+  for (int k = 0; k < CG; ++k) v[k] = dok ? to_f32<TIN>(__ldg(src + ((size_t)k * D + d0 + warp) * HW + lane)) : 0.f;
 #pragma unroll
   for (int k = 0; k < CG; ++k) t[warp * CG + k][lane] = v[k];
   __syncthreads();
@@ -491,10 +492,32 @@ extern "C" int fsb_corr_pyramid(const float* f1, const float* f2, float* const* 
   return FSB_OK;
 }
 
-extern "C" int fsb_geo_pyramid(const float* vol, float* const* geo_levels, int B, int Cg, int D, int H, int W,
-                               int L, fsb_stream_t stream) {
+namespace fsb {
+template <typename TIN>
+static int launch_geo_pyramid(const TIN* vol, const LevelPtrs& lv, int B, int Cg, int D, int H, int W, int L,
+                              cudaStream_t stream) {
+  const size_t smem = (size_t)kGeoTD * Cg * (kGeoTW + 1) * sizeof(float);
+  FSB_REQUIRE(smem <= 227 * 1024, FSB_ERR_SHAPE, "fsb_geo_pyramid: Cg=%d needs %zu B shared memory", Cg, smem);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(geo_pyramid_kernel<TIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_pyramid: cudaFuncSetAttribute");
+  }
+  dim3 grid(ceil_div(W, kGeoTW), ceil_div(D, kGeoTD), B * H);
+  if (Cg == 28)
+    launch_kernel(geo_pyramid_fast_kernel<28, TIN>, dim3(grid), dim3(256), 0, stream, vol, lv, D, H, W, L);
+  else
+    launch_kernel(geo_pyramid_kernel<TIN>, dim3(grid), dim3(256), smem, stream, vol, lv, Cg, D, H, W, L);
+  FSB_CHECK_LAUNCH("fsb_geo_pyramid");
+  return FSB_OK;
+}
+}  // namespace fsb
+
+extern "C" int fsb_geo_pyramid_in(const void* vol, int vol_dtype, float* const* geo_levels, int B, int Cg, int D, int H,
+                                  int W, int L, fsb_stream_t stream) {
   using namespace fsb;
   FSB_REQUIRE(vol && geo_levels, FSB_ERR_ARG, "fsb_geo_pyramid: NULL pointer");
+  FSB_REQUIRE(vol_dtype == FSB_F32 || vol_dtype == FSB_F16 || vol_dtype == FSB_BF16, FSB_ERR_ARG,
+              "fsb_geo_pyramid: vol_dtype %d", vol_dtype);
   FSB_REQUIRE(B > 0 && Cg > 0 && D > 0 && H > 0 && W > 0, FSB_ERR_ARG, "fsb_geo_pyramid: non-positive size");
   FSB_REQUIRE(L >= 1 && L <= 4, FSB_ERR_SHAPE, "fsb_geo_pyramid: num_levels=%d outside [1,4]", L);
   FSB_REQUIRE((D >> (L - 1)) >= 1, FSB_ERR_SHAPE, "fsb_geo_pyramid: D=%d too small for %d levels", D, L);
@@ -504,19 +527,15 @@ extern "C" int fsb_geo_pyramid(const float* vol, float* const* geo_levels, int B
     FSB_REQUIRE(geo_levels[l], FSB_ERR_ARG, "fsb_geo_pyramid: level %d pointer is NULL", l);
     lv.p[l] = geo_levels[l];
   }
-  const size_t smem = (size_t)kGeoTD * Cg * (kGeoTW + 1) * sizeof(float);
-  FSB_REQUIRE(smem <= 227 * 1024, FSB_ERR_SHAPE, "fsb_geo_pyramid: Cg=%d needs %zu B shared memory", Cg, smem);
-  if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(geo_pyramid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_pyramid: cudaFuncSetAttribute");
-  }
-  dim3 grid(ceil_div(W, kGeoTW), ceil_div(D, kGeoTD), B * H);
-  if (Cg == 28)
-    launch_kernel(geo_pyramid_fast_kernel<28>, dim3(grid), dim3(256), 0, (cudaStream_t)stream, vol, lv, D, H, W, L);
-  else
-    launch_kernel(geo_pyramid_kernel, dim3(grid), dim3(256), smem, (cudaStream_t)stream, vol, lv, Cg, D, H, W, L);
-  FSB_CHECK_LAUNCH("fsb_geo_pyramid");
-  return FSB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (vol_dtype == FSB_F16) return launch_geo_pyramid((const __half*)vol, lv, B, Cg, D, H, W, L, st);
+  if (vol_dtype == FSB_BF16) return launch_geo_pyramid((const __nv_bfloat16*)vol, lv, B, Cg, D, H, W, L, st);
+  return launch_geo_pyramid((const float*)vol, lv, B, Cg, D, H, W, L, st);
+}
+
+extern "C" int fsb_geo_pyramid(const float* vol, float* const* geo_levels, int B, int Cg, int D, int H, int W,
+                               int L, fsb_stream_t stream) {
+  return fsb_geo_pyramid_in(vol, FSB_F32, geo_levels, B, Cg, D, H, W, L, stream);
 }
 
 extern "C" int fsb_geo_lookup(float* const* geo_levels, float* const* corr_levels, const float* disp,

@@ -265,9 +265,17 @@ edgenext_mlp_kernel(const __grid_constant__ MlpParams p) {
       if (pix < p.npix) {
         float f[32], rr[32];
         load32<T>(reinterpret_cast<const T*>(p.res) + pix * kMlpC + g * 32, rr);
+        // gamma / b2 of the warp's 32 columns as 16-byte broadcast loads (8 + 8 LDS.128 instead of 64 LDS.32)
+        const float4* g4 = reinterpret_cast<const float4*>(g_s + g * 32);
+        const float4* b4 = reinterpret_cast<const float4*>(b2_s + g * 32);
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          f[i] = fmaf(g_s[g * 32 + i], __uint_as_float(v[i]) + b2_s[g * 32 + i], rr[i]);
+        for (int i4 = 0; i4 < 8; ++i4) {
+          const float4 gg = g4[i4], bb = b4[i4];
+          f[4 * i4 + 0] = fmaf(gg.x, __uint_as_float(v[4 * i4 + 0]) + bb.x, rr[4 * i4 + 0]);
+          f[4 * i4 + 1] = fmaf(gg.y, __uint_as_float(v[4 * i4 + 1]) + bb.y, rr[4 * i4 + 1]);
+          f[4 * i4 + 2] = fmaf(gg.z, __uint_as_float(v[4 * i4 + 2]) + bb.z, rr[4 * i4 + 2]);
+          f[4 * i4 + 3] = fmaf(gg.w, __uint_as_float(v[4 * i4 + 3]) + bb.w, rr[4 * i4 + 3]);
+        }
         store32<T>(reinterpret_cast<T*>(p.out) + pix * kMlpC + g * 32, f);
       }
     }

@@ -384,38 +384,72 @@ conv3x3_cout1_kernel(const T* __restrict__ x, const float* __restrict__ w, const
   const int tx0 = txi * kC1TX, ty0 = (r1 % tiles_y) * kC1TY, b = r1 / tiles_y;
   pdl_wait();
   __syncthreads();
-  // ---- phase 1: 9 partial dot products per patch pixel; a warp takes 8 consecutive patch pixels per trip
-  for (int p0 = warp * 8; p0 < kC1PY * kC1PX; p0 += 64) {
-    const int pp = p0 + (lane >> 2);
-    const int py = pp / kC1PX, px = pp - py * kC1PX;
-    const int yy = ty0 + py - 1, xx = tx0 + px - 1;
-    const bool ok = pp < kC1PY * kC1PX && yy >= 0 && yy < H && xx >= 0 && xx < W;
-    float2 acc[9];
+  // ---- phase 1: 9 partial dot products per patch pixel.  A warp takes 32 consecutive patch pixels per trip: lane
+  // group g = lane >> 2 owns the FOUR pixels p0 + g + 8k (k = 0..3), so every weight vector read from shared memory
+  // (an LDS.128 costs four wavefronts however many lanes share an address) feeds four pixels' FMAs -- with one pixel
+  // per lane group the kernel was shared-memory bound (8 M wavefronts, 48 us).
+  constexpr int kPix = 4;
+  for (int p0 = warp * 32; p0 < kC1PY * kC1PX; p0 += 256) {
+    const T* src[kPix];
+    bool ok[kPix];
+    int pp[kPix];
 #pragma unroll
-    for (int t = 0; t < 9; ++t) acc[t] = make_float2(0.f, 0.f);
-    if (ok) {
-      const T* src = x + (((size_t)b * H + yy) * W + xx) * C + sub * 8;
-      for (int c0 = 0; c0 < C; c0 += 32) {   // the 4 lanes of a pixel read 64 contiguous bytes per trip
-        const uint4 u = *reinterpret_cast<const uint4*>(src + c0);
-        const float2 v0 = unpack2f<T>(u.x), v1 = unpack2f<T>(u.y), v2 = unpack2f<T>(u.z), v3 = unpack2f<T>(u.w);
-        const float* wc = ws + c0 + sub * 8;
+    for (int k = 0; k < kPix; ++k) {
+      pp[k] = p0 + (lane >> 2) + 8 * k;
+      const int py = pp[k] / kC1PX, px = pp[k] - py * kC1PX;
+      const int yy = ty0 + py - 1, xx = tx0 + px - 1;
+      ok[k] = pp[k] < kC1PY * kC1PX && yy >= 0 && yy < H && xx >= 0 && xx < W;
+      src[k] = x + (((size_t)b * H + (ok[k] ? yy : 0)) * W + (ok[k] ? xx : 0)) * C + sub * 8;
+    }
+    float2 acc[kPix][9];
 #pragma unroll
-        for (int t = 0; t < 9; ++t) {
-          const float4 wa = *reinterpret_cast<const float4*>(wc + t * C);
-          const float4 wb = *reinterpret_cast<const float4*>(wc + t * C + 4);
-          acc[t] = __ffma2_rn(v0, make_float2(wa.x, wa.y), acc[t]);
-          acc[t] = __ffma2_rn(v1, make_float2(wa.z, wa.w), acc[t]);
-          acc[t] = __ffma2_rn(v2, make_float2(wb.x, wb.y), acc[t]);
-          acc[t] = __ffma2_rn(v3, make_float2(wb.z, wb.w), acc[t]);
+    for (int k = 0; k < kPix; ++k)
+#pragma unroll
+      for (int t = 0; t < 9; ++t) acc[k][t] = make_float2(0.f, 0.f);
+    // the 4 lanes of a pixel read 64 contiguous bytes per chunk of 32 channels; the next chunk's loads are in
+    // flight while this one is multiplied
+    uint4 u[kPix], un[kPix];
+#pragma unroll
+    for (int k = 0; k < kPix; ++k) u[k] = ok[k] ? *reinterpret_cast<const uint4*>(src[k]) : make_uint4(0u, 0u, 0u, 0u);
+    for (int c0 = 0; c0 < C; c0 += 32) {
+      if (c0 + 32 < C) {
+#pragma unroll
+        for (int k = 0; k < kPix; ++k)
+          un[k] = ok[k] ? *reinterpret_cast<const uint4*>(src[k] + c0 + 32) : make_uint4(0u, 0u, 0u, 0u);
+      }
+      float2 v[kPix][4];
+#pragma unroll
+      for (int k = 0; k < kPix; ++k) {
+        v[k][0] = unpack2f<T>(u[k].x); v[k][1] = unpack2f<T>(u[k].y); v[k][2] = unpack2f<T>(u[k].z); v[k][3] = unpack2f<T>(u[k].w);
+      }
+      const float* wc = ws + c0 + sub * 8;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const float4 wa = *reinterpret_cast<const float4*>(wc + t * C);
+        const float4 wb = *reinterpret_cast<const float4*>(wc + t * C + 4);
+        const float2 w0 = make_float2(wa.x, wa.y), w1 = make_float2(wa.z, wa.w);
+        const float2 w2 = make_float2(wb.x, wb.y), w3 = make_float2(wb.z, wb.w);
+#pragma unroll
+        for (int k = 0; k < kPix; ++k) {
+          acc[k][t] = __ffma2_rn(v[k][0], w0, acc[k][t]);
+          acc[k][t] = __ffma2_rn(v[k][1], w1, acc[k][t]);
+          acc[k][t] = __ffma2_rn(v[k][2], w2, acc[k][t]);
+          acc[k][t] = __ffma2_rn(v[k][3], w3, acc[k][t]);
         }
       }
+#pragma unroll
+      for (int k = 0; k < kPix; ++k) u[k] = un[k];
     }
 #pragma unroll
-    for (int t = 0; t < 9; ++t) {
-      float v = acc[t].x + acc[t].y;
-      v += __shfl_xor_sync(0xffffffffu, v, 1);
-      v += __shfl_xor_sync(0xffffffffu, v, 2);
-      if (sub == (t & 3) && pp < kC1PY * kC1PX) part[(t * kC1PY + py) * kC1PS + px] = v;
+    for (int k = 0; k < kPix; ++k) {
+      const int py = pp[k] / kC1PX, px = pp[k] - py * kC1PX;
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        float r = acc[k][t].x + acc[k][t].y;
+        r += __shfl_xor_sync(0xffffffffu, r, 1);
+        r += __shfl_xor_sync(0xffffffffu, r, 2);
+        if (sub == (t & 3) && pp[k] < kC1PY * kC1PX) part[(t * kC1PY + py) * kC1PS + px] = r;
+      }
     }
   }
   __syncthreads();

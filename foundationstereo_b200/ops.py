@@ -127,11 +127,12 @@ def _(f1, f2, num_levels, precision):
 def geo_pyramid(volume: torch.Tensor, num_levels: int) -> List[torch.Tensor]:
     """levels of the geometry volume in the lookup layout (B*H*W, D >> l, Cg) fp32."""
     _need_cuda(volume)
-    volume = volume.float().contiguous()
+    volume = volume.contiguous() if volume.dtype in _DTYPE else volume.float().contiguous()
     B, Cg, D, H, W = volume.shape
     levels = [torch.empty((B * H * W, D >> l, Cg), dtype=torch.float32, device=volume.device)
               for l in range(num_levels)]
-    _call(volume, "fsb_geo_pyramid", volume.data_ptr(), level_array(levels), B, Cg, D, H, W, num_levels)
+    _call(volume, "fsb_geo_pyramid_in", volume.data_ptr(), _DTYPE[volume.dtype], level_array(levels), B, Cg, D, H, W,
+          num_levels)
     return levels
 
 
@@ -209,11 +210,12 @@ def corr_pyramid_into(f1: torch.Tensor, f2: torch.Tensor, levels: List[torch.Ten
 def geo_pyramid_into(volume: torch.Tensor, levels: List[torch.Tensor]) -> None:
     """fsb_geo_pyramid into caller-owned level buffers."""
     _need_cuda(volume)
-    volume = volume.float().contiguous()
+    volume = volume.contiguous() if volume.dtype in _DTYPE else volume.float().contiguous()
     B, Cg, D, H, W = volume.shape
     for l, t in enumerate(levels):
         assert t.shape == (B * H * W, D >> l, Cg) and t.dtype == torch.float32 and t.is_contiguous()
-    _call(volume, "fsb_geo_pyramid", volume.data_ptr(), level_array(levels), B, Cg, D, H, W, len(levels))
+    _call(volume, "fsb_geo_pyramid_in", volume.data_ptr(), _DTYPE[volume.dtype], level_array(levels), B, Cg, D, H, W,
+          len(levels))
 
 
 # ----------------------------------------------------------------------------------------

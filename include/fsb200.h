@@ -100,6 +100,11 @@ int fsb_corr_pyramid(const float* f1, const float* f2, float* const* corr_levels
  * contiguous run per pixel and level.                                                */
 int fsb_geo_pyramid(const float* vol, float* const* geo_levels, int B, int Cg, int D, int H,
                     int W, int L, fsb_stream_t stream);
+/* The same with `vol` in its storage type (fsb_dtype): the filtered volume is fp16 when it leaves the reference's
+ * autocast region and only becomes fp32 through the caller's `.float()` (core/foundation_stereo.py:229); reading it
+ * as it is halves this kernel's input bytes.  The levels are fp32 and bit-identical to converting first. */
+int fsb_geo_pyramid_in(const void* vol, int vol_dtype, float* const* geo_levels, int B, int Cg, int D, int H,
+                       int W, int L, fsb_stream_t stream);
 
 /* ---- kernel 3: per-iteration lookup ------------------------------------------------
  * replaces Combined_Geo_Encoding_Volume.__call__ (core/geometry.py:43-65) with
