@@ -7,6 +7,8 @@
 #include <stdio.h>
 #include <stdarg.h>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/fsb200.h"
 
 namespace fsb {
@@ -14,6 +16,15 @@ namespace fsb {
 // thread-local error text + launch counter (defined in api.cu)
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
+
+// NVTX range around every C-ABI entry (the reference has no tracing hooks; the new code brings
+// its own).  Header-only NVTX3: without a profiler attached a push/pop is a null function-pointer check.
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 inline int cuda_fail(cudaError_t e, const char* what) {
   set_error("%s: %s", what, cudaGetErrorString(e));
@@ -107,6 +118,26 @@ struct LevelPtrs {
   float* p[FSB_MAX_LEVELS];
 };
 
+// Banded init correlation (opt-in): level l stores, for the pixel in image column w1, the bw0 >> l
+// columns [s_l, s_l + (bw0 >> l)) with s_l = s0 >> l and s0 = floor((w1 - off) / align) * align -- the part of the row
+// a lookup with disparities in [0, d_band] and radius r can touch (plus alignment slack), instead of all W2 columns.
+// bw0 == 0 means full rows.  Columns outside [0, W2 >> l) are stored as zeros; a lookup outside the band reads zeros
+// where the reference reads real correlations (core/geometry.py:57 does not clamp the disparity).
+struct CorrBand {
+  int bw0, off, align;
+};
+__host__ __device__ inline int band_floor_div(int a, int b) { return a >= 0 ? a / b : -((-a + b - 1) / b); }
+__host__ __device__ inline int band_start(const CorrBand& bd, int w1) { return band_floor_div(w1 - bd.off, bd.align) * bd.align; }
+inline CorrBand make_corr_band(int d_band, int r, int L) {
+  CorrBand bd;
+  bd.align = 4 << (L - 1);                    // every level's start stays a multiple of 4 columns (16-byte stores)
+  const int left = (r + 2) << (L - 1);        // level-0 columns a coarsest-level tap reaches left of w1 - d_band ...
+  const int right = (r + 3) << (L - 1);       // ... and right of w1 (taps floor(x) and floor(x) + 1, one column of rounding slack)
+  bd.off = d_band + left;
+  bd.bw0 = round_up(d_band + left + right + bd.align - 1, bd.align);
+  return bd;
+}
+
 // corr_umma.cu: init correlation on tcgen05 (nprod 1 = TF32, 3 = 3xTF32 split, fp32-accurate)
 int launch_corr_umma(const float* f1, const float* f2, const LevelPtrs& lv, int B, int C, int H, int W1, int W2, int L,
                      int nprod, cudaStream_t stream);
@@ -114,6 +145,6 @@ int launch_corr_umma(const float* f1, const float* f2, const LevelPtrs& lv, int 
 // corr_tma.cu: the same with the NCHW planes fed by TMA as MN-major operands (needs W % 4 == 0, 16-byte aligned bases)
 bool corr_tma_eligible(const float* f1, const float* f2, int W1, int W2);
 int launch_corr_tma(const float* f1, const float* f2, const LevelPtrs& lv, int B, int C, int H, int W1, int W2, int L,
-                    int nprod, cudaStream_t stream);
+                    int nprod, cudaStream_t stream, CorrBand band = CorrBand{0, 0, 0});
 
 }  // namespace fsb

@@ -865,6 +865,7 @@ static auto halo_kernel_for(int epi) -> void (*)(const ConvParams) {
 }  // namespace fsb
 
 extern "C" int fsb_conv2d_nhwc(const fsb_conv_args* a, int dtype, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_conv2d_nhwc");
   using namespace fsb;
   FSB_REQUIRE(a != nullptr, FSB_ERR_ARG, "fsb_conv2d_nhwc: NULL args");
   FSB_REQUIRE(dtype == FSB_F16 || dtype == FSB_BF16, FSB_ERR_ARG, "fsb_conv2d_nhwc: dtype %d (need f16/bf16)", dtype);

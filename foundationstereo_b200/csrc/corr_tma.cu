@@ -39,6 +39,7 @@ struct CorrTmaParams {
   int boxes_a;  // boxes of the A region of a stage = ceil(rows_m / 32)
   int boxes_b;  // boxes of the B region = ceil(min(W2, 256) padded to 16 / 32)
   int stage0, stage1;  // level 0 / level 1 leave through shared memory as fully coalesced 16-byte stores
+  CorrBand band;       // bw0 > 0: banded output (one n window per m tile, rows of bw0 >> l columns)
 };
 
 // MN-major SWIZZLE_128B_BASE32B operand: atom = 32 pixels (128 B) x 4 channels (rows of 128 B, 512 B per atom);
@@ -72,11 +73,15 @@ corr_tma_kernel(const __grid_constant__ CorrTmaParams p) {
   __shared__ float nA[kCtBM], nB[256];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int m0 = blockIdx.x * p.rows_m, n0 = blockIdx.y * 256;
+  const int m0 = blockIdx.x * p.rows_m;
   const int bh = blockIdx.z, b = bh / p.H, h = bh - b * p.H;
   const int W1 = p.W1, W2 = p.W2;
   const int rowsA = min(p.rows_m, W1 - m0);
-  const int Nv = min(256, W2 - n0);
+  const bool banded = p.band.bw0 > 0;
+  // band mode: ONE n window per m tile = the union of the rows' bands, [s0(m0), s0(m0 + rowsA - 1) + bw0) clipped to the
+  // image (the host sized rows_m so that it is at most 256 columns wide)
+  const int n0 = banded ? max(0, band_start(p.band, m0)) : blockIdx.y * 256;
+  const int Nv = banded ? min(W2, band_start(p.band, m0 + rowsA - 1) + p.band.bw0) - n0 : min(256, W2 - n0);
   const int Npad = (Nv + 15) & ~15;
   const int ldA = (rowsA + kCtBoxW - 1) / kCtBoxW, ldB = (Nv + kCtBoxW - 1) / kCtBoxW;  // boxes to fetch
   const int nboxes = p.boxes_a + p.boxes_b;
@@ -253,6 +258,32 @@ corr_tma_kernel(const __grid_constant__ CorrTmaParams p) {
 #pragma unroll
       for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(raw[i]) * ia * nB[c0 + i];  // nB holds 1/max(|f2|, eps)
       const int col = n0 + c0;
+      if (banded) {
+        // row w1 keeps the columns [s0, s0 + bw0) of level 0 and [s0 >> l, (s0 + bw0) >> l) of level l; everything is a
+        // multiple of 4 columns (s0, n0, c0 are multiples of align = 4 << (L-1), W2 of 4), so whole quads move
+        const int s0 = band_start(p.band, w1);
+        float* brow = p.lv.p[0] + px * p.band.bw0;
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) {
+          const int a = col + 4 * q4, jb = a - s0;
+          if (a < W2 && jb >= 0 && jb < p.band.bw0)
+            *reinterpret_cast<float4*>(brow + jb) = make_float4(v[4 * q4], v[4 * q4 + 1], v[4 * q4 + 2], v[4 * q4 + 3]);
+        }
+        int n = 16, len = W2, cl = col, sl = s0, bw = p.band.bw0;
+        for (int l = 1; l < p.L; ++l) {
+          n >>= 1; len >>= 1; cl >>= 1; sl >>= 1; bw >>= 1;   // s0 is an exact multiple of 2^l: the shift is a division
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (i < n) v[i] = (v[2 * i] + v[2 * i + 1]) * 0.5f;
+          float* rl = p.lv.p[l] + px * bw;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int jb = cl + i - sl;
+            if (i < n && cl + i < len && jb >= 0 && jb < bw) rl[jb] = v[i];
+          }
+        }
+        continue;
+      }
       if (p.stage0) {  // n0 == 0: row r of the staged tile, stride W2 + 4 floats (conflict-free 16-byte stores)
         float* srow = out0 + r * stride0 + c0;
         if (c0 + 16 <= W2) {
@@ -305,6 +336,17 @@ corr_tma_kernel(const __grid_constant__ CorrTmaParams p) {
           for (int i = 0; i < 8; ++i)
             if (i < n && cl + i < len) rl[i] = v[i];
         }
+      }
+    }
+    if (banded && valid && warp < 4) {
+      // band positions that fall outside the image (w1 near the left / right border) hold zeros
+      const int s0 = band_start(p.band, w1);
+      int len = W2, sl = s0, bw = p.band.bw0;
+      for (int l = 0; l < p.L; ++l) {
+        float* rl = p.lv.p[l] + px * bw;
+        for (int jb = 0; jb < min(bw, -sl); ++jb) rl[jb] = 0.f;          // columns left of the image
+        for (int jb = max(0, len - sl); jb < bw; ++jb) rl[jb] = 0.f;     // columns right of it
+        len >>= 1; sl >>= 1; bw >>= 1;
       }
     }
     tc_fence_before();
@@ -364,7 +406,7 @@ bool corr_tma_eligible(const float* f1, const float* f2, int W1, int W2) {
 }
 
 int launch_corr_tma(const float* f1, const float* f2, const LevelPtrs& lv, int B, int C, int H, int W1, int W2, int L,
-                    int nprod, cudaStream_t stream) {
+                    int nprod, cudaStream_t stream, CorrBand band) {
   CorrTmaParams p;
   memset(&p, 0, sizeof(p));
   int rc = make_map(&p.map1, f1, B, C, H, W1);
@@ -373,8 +415,22 @@ int launch_corr_tma(const float* f1, const float* f2, const LevelPtrs& lv, int B
   if (rc != FSB_OK) return rc;
   p.lv = lv;
   p.C = C; p.H = H; p.W1 = W1; p.W2 = W2; p.L = L;
-  const int mtiles = ceil_div(W1, kCtBM);
+  p.band = band;
+  int mtiles = ceil_div(W1, kCtBM);
   p.rows_m = round_up(ceil_div(W1, mtiles), 4);  // e.g. W1 = 160: two CTAs of 80 rows instead of 128 + 32
+  if (band.bw0 > 0) {
+    // the n window of an m tile is rows_m - 1 + bw0 + align - 1 columns at most and must fit ONE 256-column MMA tile
+    FSB_REQUIRE(W1 == W2, FSB_ERR_SHAPE, "fsb_corr_pyramid_band: W1 = %d != W2 = %d", W1, W2);
+    const int max_rows = (256 - band.bw0 - band.align) & ~3;
+    FSB_REQUIRE(max_rows >= 32, FSB_ERR_SHAPE,
+                "fsb_corr_pyramid_band: a band of %d columns (d_band, radius, levels) leaves no room for a pixel tile in a "
+                "256-column window; use the full-matrix mode", band.bw0);
+    const int cap = max_rows < kCtBM ? max_rows : kCtBM;
+    mtiles = ceil_div(W1, cap);
+    p.rows_m = round_up(ceil_div(W1, mtiles), 4);
+    if (p.rows_m > cap) p.rows_m = cap;
+    mtiles = ceil_div(W1, p.rows_m);
+  }
   p.boxes_a = ceil_div(p.rows_m, kCtBoxW);
   p.boxes_b = ceil_div(round_up(W2 < 256 ? W2 : 256, 16), kCtBoxW);
   // the MMA reads M = 128 rows = 4 pixel blocks from the A region: blocks past boxes_a fall into the B region (their
@@ -382,11 +438,12 @@ int launch_corr_tma(const float* f1, const float* f2, const LevelPtrs& lv, int B
   if (p.boxes_a + p.boxes_b < 4) p.boxes_b = 4 - p.boxes_a;
   const size_t stage = (size_t)(p.boxes_a + p.boxes_b) * kCtBox;
   // staged epilogue: one n tile, rows of 16-byte multiples, the staged tile fits the freed operand stages
-  p.stage0 = W2 <= 256 && aligned16(lv.p[0]) && (size_t)p.rows_m * (W2 + 4) * 4 <= 2 * stage;
-  p.stage1 = L >= 2 && W2 <= 256 && (W2 & 7) == 0 && aligned16(lv.p[1]) && (size_t)p.rows_m * ((W2 >> 1) + 4) * 4 <= stage;
+  p.stage0 = band.bw0 == 0 && W2 <= 256 && aligned16(lv.p[0]) && (size_t)p.rows_m * (W2 + 4) * 4 <= 2 * stage;
+  p.stage1 = band.bw0 == 0 && L >= 2 && W2 <= 256 && (W2 & 7) == 0 && aligned16(lv.p[1]) &&
+             (size_t)p.rows_m * ((W2 >> 1) + 4) * 4 <= stage;
   const size_t smem = 3 * stage + 1024;
   FSB_REQUIRE(smem <= 220 * 1024, FSB_ERR_SHAPE, "fsb_corr_pyramid: %zu B shared memory", smem);
-  dim3 grid(mtiles, ceil_div(W2, 256), B * H);
+  dim3 grid(mtiles, band.bw0 > 0 ? 1 : ceil_div(W2, 256), B * H);
   auto kern = nprod == 3 ? corr_tma_kernel<3> : corr_tma_kernel<1>;
   cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (err != cudaSuccess) return cuda_fail(err, "fsb_corr_pyramid: cudaFuncSetAttribute");

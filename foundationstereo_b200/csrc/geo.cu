@@ -301,10 +301,12 @@ constexpr int kLkWarps = 4;
 // geo window v[0..K] (channel c of rows gbase .. gbase+K, zero outside [0, Dl)), this lane's correlation
 // tap cv (lane j <= K holds tap cbase + j), and this lane's per-tap fraction (lane k: geo tap k, lane 16+k:
 // corr tap k).  Window bases are warp-uniform, so the "whole window inside" fast path is a uniform branch.
+// `crow` / `cshift`: row length and first stored column of the correlation level (Wl and 0 for full rows; bw0 >> l and
+// s_l for a banded pyramid, where taps outside the stored band read as zero).
 template <int K>
 __device__ __forceinline__ void lookup_level(const float* __restrict__ gl, const float* __restrict__ cl, long long pix,
                                              int Cg, int Dl, int Wl, float d, float xcor, int r, int lane, int c,
-                                             bool geo_ch, float (&v)[K + 1], float& cv, float& frac) {
+                                             bool geo_ch, float (&v)[K + 1], float& cv, float& frac, int crow, int cshift) {
   const bool is_cor_lane = lane >= 16;
   const int kk = lane & 15;
   const float xc = is_cor_lane ? xcor : d;
@@ -324,14 +326,14 @@ __device__ __forceinline__ void lookup_level(const float* __restrict__ gl, const
 #pragma unroll
     for (int j = 0; j <= K; ++j) v[j] = (geo_ch && (unsigned)(gbase + j) < (unsigned)Dl) ? __ldg(g + j * Cg) : 0.f;
   }
-  const int x = cbase + lane;
-  cv = (lane <= K && (unsigned)x < (unsigned)Wl) ? __ldg(cl + (size_t)pix * Wl + x) : 0.f;
+  const int x = cbase + lane, xb = x - cshift;
+  cv = (lane <= K && (unsigned)x < (unsigned)Wl && (unsigned)xb < (unsigned)crow) ? __ldg(cl + (size_t)pix * crow + xb) : 0.f;
 }
 
 template <typename T, int KT, int LT, int CGT>
 __global__ void __launch_bounds__(kLkWarps * 32, 12)
 lookup_nhwc_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp, const float* __restrict__ coords,
-                   T* __restrict__ out, int Cgrt, int D, int W2, int Lrt, int r, int Cpad, long long npix) {
+                   T* __restrict__ out, int Cgrt, int D, int W2, int Lrt, int r, int Cpad, long long npix, int W1, CorrBand band) {
   pdl_launch_dependents();  // the next kernel may start its prologue
   pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ __align__(16) uint8_t lsm[];
@@ -345,6 +347,7 @@ lookup_nhwc_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp,
   T* orow = reinterpret_cast<T*>(lsm + (size_t)warp * Cpad * sizeof(T));
   const float dsp = __ldg(disp + pix), xco = __ldg(coords + pix);
   const int nout = K * (Cg + 1);
+  const int bs0 = band.bw0 > 0 ? band_start(band, (int)(pix % W1)) : 0;  // the pixel's image column names its band
 
   for (int c0 = 0; c0 < Cg; c0 += 32) {
     const int c = c0 + lane;
@@ -357,7 +360,7 @@ lookup_nhwc_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp,
       const float inv = 1.f / (float)(1 << l);
       const float d = dsp * inv;  // exact: power-of-two scale
       lookup_level<K>(geo.p[l], cor.p[l], pix, Cg, D >> l, W2 >> l, d, __fsub_rn(xco * inv, d), r, lane, c, geo_ch,
-                      v[l], cv[l], frac[l]);
+                      v[l], cv[l], frac[l], band.bw0 > 0 ? band.bw0 >> l : W2 >> l, bs0 >> l);
     }
     // ---- phase C.  The 16-bit result cannot tell lo*(1-f) + hi*f from lo + f*(hi-lo): the shorter form is used.
 #pragma unroll
@@ -392,7 +395,7 @@ lookup_nhwc_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp,
 template <int KT, int CGT>
 __global__ void __launch_bounds__(kLkThreads, 4)
 lookup_nchw_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp, const float* __restrict__ coords,
-                   float* __restrict__ out, int Cgrt, int D, int H, int W, int W2, int L, int r) {
+                   float* __restrict__ out, int Cgrt, int D, int H, int W, int W2, int L, int r, CorrBand band) {
   pdl_launch_dependents();  // the next kernel may start its prologue
   pdl_wait();               // inputs written by the previous kernel are complete and visible
   extern __shared__ float sm[];  // [nout][33]
@@ -428,8 +431,9 @@ lookup_nchw_kernel(LevelPtrs geo, LevelPtrs cor, const float* __restrict__ disp,
           const int px = warp * PPW + i0 + i;
           const float d = dsp[i0 + i] * inv;
           // a slot beyond the row end gathers the row's last pixel again (harmless, never stored)
+          const int bs0 = band.bw0 > 0 ? band_start(band, w0 + min(px, npix - 1)) : 0;
           lookup_level<K>(geo.p[l], cor.p[l], p0 + min(px, npix - 1), Cg, Dl, Wl, d, __fsub_rn(xco[i0 + i] * inv, d), r, lane, c, geo_ch,
-                          v[i], cv[i], frac[i]);
+                          v[i], cv[i], frac[i], band.bw0 > 0 ? band.bw0 >> l : Wl, bs0 >> l);
         }
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
@@ -468,6 +472,7 @@ static size_t lookup_smem_bytes(int Cg, int r) {
 // -------------------------------------------------------------------------------------
 extern "C" int fsb_corr_pyramid(const float* f1, const float* f2, float* const* corr_levels, int B, int C,
                                 int H, int W1, int W2, int L, int precision, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_corr_pyramid");
   using namespace fsb;
   FSB_REQUIRE(f1 && f2 && corr_levels, FSB_ERR_ARG, "fsb_corr_pyramid: NULL pointer");
   FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W1 > 0 && W2 > 0, FSB_ERR_ARG, "fsb_corr_pyramid: non-positive size");
@@ -514,6 +519,7 @@ static int launch_geo_pyramid(const TIN* vol, const LevelPtrs& lv, int B, int Cg
 
 extern "C" int fsb_geo_pyramid_in(const void* vol, int vol_dtype, float* const* geo_levels, int B, int Cg, int D, int H,
                                   int W, int L, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_geo_pyramid_in");
   using namespace fsb;
   FSB_REQUIRE(vol && geo_levels, FSB_ERR_ARG, "fsb_geo_pyramid: NULL pointer");
   FSB_REQUIRE(vol_dtype == FSB_F32 || vol_dtype == FSB_F16 || vol_dtype == FSB_BF16, FSB_ERR_ARG,
@@ -535,12 +541,13 @@ extern "C" int fsb_geo_pyramid_in(const void* vol, int vol_dtype, float* const* 
 
 extern "C" int fsb_geo_pyramid(const float* vol, float* const* geo_levels, int B, int Cg, int D, int H, int W,
                                int L, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_geo_pyramid");
   return fsb_geo_pyramid_in(vol, FSB_F32, geo_levels, B, Cg, D, H, W, L, stream);
 }
 
-extern "C" int fsb_geo_lookup(float* const* geo_levels, float* const* corr_levels, const float* disp,
-                              const float* coords, void* out, int B, int Cg, int D, int H, int W, int W2, int L,
-                              int r, int out_layout, fsb_stream_t stream) {
+static int geo_lookup_impl(float* const* geo_levels, float* const* corr_levels, const float* disp,
+                           const float* coords, void* out, int B, int Cg, int D, int H, int W, int W2, int L,
+                           int r, int out_layout, fsb_stream_t stream, fsb::CorrBand band) {
   using namespace fsb;
   FSB_REQUIRE(geo_levels && corr_levels && disp && coords && out, FSB_ERR_ARG, "fsb_geo_lookup: NULL pointer");
   FSB_REQUIRE(B > 0 && Cg > 0 && D > 0 && H > 0 && W > 0 && W2 > 0, FSB_ERR_ARG, "fsb_geo_lookup: non-positive size");
@@ -573,7 +580,7 @@ extern "C" int fsb_geo_lookup(float* const* geo_levels, float* const* corr_level
       if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_lookup: cudaFuncSetAttribute");                           \
     }                                                                                                              \
     launch_kernel(kern, dim3(blocks), dim3(kLkWarps * 32), smem, (cudaStream_t)stream, g, c, disp, coords,         \
-                  (T*)out, Cg, D, W2, L, r, Cpad, npix);                                                           \
+                  (T*)out, Cg, D, W2, L, r, Cpad, npix, W, band);                                                  \
   } while (0)
 #define FSB_LAUNCH_LK_K(T, LT)                                                                                     \
   do {                                                                                                             \
@@ -606,7 +613,7 @@ extern "C" int fsb_geo_lookup(float* const* geo_levels, float* const* corr_level
       if (e != cudaSuccess) return cuda_fail(e, "fsb_geo_lookup: cudaFuncSetAttribute");                           \
     }                                                                                                              \
     launch_kernel(kern, dim3(grid), dim3(kLkThreads), smem, (cudaStream_t)stream, g, c, disp, coords, (float*)out, \
-                  Cg, D, H, W, W2, L, r);                                                                          \
+                  Cg, D, H, W, W2, L, r, band);                                                                    \
   } while (0)
   switch (r) {
     case 1: FSB_LAUNCH_LKN(3); break;
@@ -617,4 +624,58 @@ extern "C" int fsb_geo_lookup(float* const* geo_levels, float* const* corr_level
 #undef FSB_LAUNCH_LKN
   FSB_CHECK_LAUNCH("fsb_geo_lookup");
   return FSB_OK;
+}
+
+extern "C" int fsb_geo_lookup(float* const* geo_levels, float* const* corr_levels, const float* disp,
+                              const float* coords, void* out, int B, int Cg, int D, int H, int W, int W2, int L,
+                              int r, int out_layout, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_geo_lookup");
+  return geo_lookup_impl(geo_levels, corr_levels, disp, coords, out, B, Cg, D, H, W, W2, L, r, out_layout, stream,
+                         fsb::CorrBand{0, 0, 0});
+}
+
+// ---- banded init correlation (opt-in) ---------------------------------------------------------------------------
+extern "C" int fsb_corr_band_geometry(int d_band, int radius, int L, int* bw0, int* off, int* align) {
+  using namespace fsb;
+  FSB_REQUIRE(d_band >= 1 && radius >= 1 && L >= 1 && L <= 4, FSB_ERR_ARG, "fsb_corr_band_geometry: d_band=%d radius=%d L=%d",
+              d_band, radius, L);
+  const CorrBand bd = make_corr_band(d_band, radius, L);
+  if (bw0) *bw0 = bd.bw0;
+  if (off) *off = bd.off;
+  if (align) *align = bd.align;
+  return FSB_OK;
+}
+
+extern "C" int fsb_corr_pyramid_band(const float* f1, const float* f2, float* const* corr_levels, int B, int C, int H,
+                                     int W, int L, int precision, int d_band, int radius, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_corr_pyramid_band");
+  using namespace fsb;
+  FSB_REQUIRE(f1 && f2 && corr_levels, FSB_ERR_ARG, "fsb_corr_pyramid_band: NULL pointer");
+  FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, FSB_ERR_ARG, "fsb_corr_pyramid_band: non-positive size");
+  FSB_REQUIRE(L >= 1 && L <= 4 && d_band >= 1 && radius >= 1, FSB_ERR_ARG, "fsb_corr_pyramid_band: L=%d d_band=%d radius=%d", L,
+              d_band, radius);
+  FSB_REQUIRE(precision == FSB_PREC_TF32 || precision == FSB_PREC_TF32X3, FSB_ERR_ARG,
+              "fsb_corr_pyramid_band: precision %d (the band form exists on the tensor-core path: FSB_PREC_TF32X3 or FSB_PREC_TF32)",
+              precision);
+  FSB_REQUIRE((long long)B * H < 65536, FSB_ERR_SHAPE, "fsb_corr_pyramid_band: B*H=%lld >= 65536", (long long)B * H);
+  FSB_REQUIRE((W & 3) == 0 && aligned16(f1) && aligned16(f2), FSB_ERR_SHAPE,
+              "fsb_corr_pyramid_band: W=%d must be a multiple of 4 and the features 16-byte aligned (TMA-fed kernel)", W);
+  LevelPtrs lv{};
+  for (int l = 0; l < L; ++l) {
+    FSB_REQUIRE(corr_levels[l], FSB_ERR_ARG, "fsb_corr_pyramid_band: level %d pointer is NULL", l);
+    FSB_REQUIRE(aligned16(corr_levels[l]), FSB_ERR_ALIGN, "fsb_corr_pyramid_band: level %d not 16-byte aligned", l);
+    lv.p[l] = corr_levels[l];
+  }
+  return launch_corr_tma(f1, f2, lv, B, C, H, W, W, L, precision == FSB_PREC_TF32X3 ? 3 : 1, (cudaStream_t)stream,
+                         make_corr_band(d_band, radius, L));
+}
+
+extern "C" int fsb_geo_lookup_band(float* const* geo_levels, float* const* corr_levels, const float* disp,
+                                   const float* coords, void* out, int B, int Cg, int D, int H, int W, int L, int r,
+                                   int out_layout, int d_band, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_geo_lookup_band");
+  FSB_REQUIRE(d_band >= 1, FSB_ERR_ARG, "fsb_geo_lookup_band: d_band=%d", d_band);
+  FSB_REQUIRE(r >= 1 && L >= 1 && L <= 4, FSB_ERR_ARG, "fsb_geo_lookup_band: radius=%d L=%d", r, L);
+  return geo_lookup_impl(geo_levels, corr_levels, disp, coords, out, B, Cg, D, H, W, W, L, r, out_layout, stream,
+                         fsb::make_corr_band(d_band, r, L));
 }

@@ -294,6 +294,7 @@ edgenext_mlp_kernel(const __grid_constant__ MlpParams p) {
 extern "C" int fsb_edgenext_mlp(const void* x, const void* w1, const float* b1, const void* w2, const float* b2,
                                 const float* gamma, const void* res, void* out, long long npix, int C, int F, int dtype,
                                 fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_edgenext_mlp");
   using namespace fsb;
   FSB_REQUIRE(x && w1 && b1 && w2 && b2 && gamma && res && out, FSB_ERR_ARG, "fsb_edgenext_mlp: NULL pointer");
   FSB_REQUIRE(dtype == FSB_F16 || dtype == FSB_BF16, FSB_ERR_ARG, "fsb_edgenext_mlp: dtype %d (need f16/bf16)", dtype);

@@ -488,6 +488,7 @@ static inline bool is16(int dtype) { return dtype == FSB_F16 || dtype == FSB_BF1
 
 extern "C" int fsb_nchw_to_nhwc(const float* src, void* dst16, float* dst32, int B, int C, int H, int W, int Cpad,
                                 int dtype, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_nchw_to_nhwc");
   using namespace fsb;
   FSB_REQUIRE(src && (dst16 || dst32), FSB_ERR_ARG, "fsb_nchw_to_nhwc: NULL pointer");
   FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, FSB_ERR_ARG, "fsb_nchw_to_nhwc: non-positive size");
@@ -502,6 +503,7 @@ extern "C" int fsb_nchw_to_nhwc(const float* src, void* dst16, float* dst32, int
 }
 
 extern "C" int fsb_nhwc_to_nchw(const float* src, float* dst, int B, int C, int H, int W, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_nhwc_to_nchw");
   using namespace fsb;
   FSB_REQUIRE(src && dst, FSB_ERR_ARG, "fsb_nhwc_to_nchw: NULL pointer");
   FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0, FSB_ERR_ARG, "fsb_nhwc_to_nchw: non-positive size");
@@ -514,6 +516,7 @@ extern "C" int fsb_nhwc_to_nchw(const float* src, float* dst, int B, int C, int 
 
 extern "C" int fsb_pool2x_nhwc(const float* src, void* dst, int B, int C, int H, int W, int dtype,
                                fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_pool2x_nhwc");
   using namespace fsb;
   FSB_REQUIRE(src && dst, FSB_ERR_ARG, "fsb_pool2x_nhwc: NULL pointer");
   FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && is16(dtype), FSB_ERR_ARG, "fsb_pool2x_nhwc: bad size or dtype");
@@ -533,6 +536,7 @@ extern "C" int fsb_pool2x_nhwc(const float* src, void* dst, int B, int C, int H,
 
 extern "C" int fsb_resize_nhwc(const float* src, void* dst, int B, int C, int Hs, int Ws, int Hd, int Wd,
                                int dtype, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_resize_nhwc");
   using namespace fsb;
   FSB_REQUIRE(src && dst, FSB_ERR_ARG, "fsb_resize_nhwc: NULL pointer");
   FSB_REQUIRE(B > 0 && C > 0 && Hs > 0 && Ws > 0 && Hd > 0 && Wd > 0 && is16(dtype), FSB_ERR_ARG,
@@ -555,6 +559,7 @@ extern "C" int fsb_resize_nhwc(const float* src, void* dst, int B, int C, int Hs
 extern "C" int fsb_conv7x7_c1(const float* disp, const float* weight, const float* bias, void* out, int ld_out,
                               int Cout, void* disp_out, int ld_disp, int disp_ch, int B, int H, int W, int dtype,
                               fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_conv7x7_c1");
   using namespace fsb;
   FSB_REQUIRE(disp && weight && bias && out, FSB_ERR_ARG, "fsb_conv7x7_c1: NULL pointer");
   FSB_REQUIRE(B > 0 && H > 0 && W > 0 && is16(dtype), FSB_ERR_ARG, "fsb_conv7x7_c1: bad size or dtype");
@@ -571,6 +576,7 @@ extern "C" int fsb_conv7x7_c1(const float* disp, const float* weight, const floa
 
 extern "C" int fsb_dwconv7x7_nhwc(const void* x, const float* weight, const float* bias, void* out, int B, int C,
                                   int H, int W, int dtype, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_dwconv7x7_nhwc");
   using namespace fsb;
   FSB_REQUIRE(x && weight && bias && out, FSB_ERR_ARG, "fsb_dwconv7x7_nhwc: NULL pointer");
   FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && is16(dtype), FSB_ERR_ARG, "fsb_dwconv7x7_nhwc: bad size or dtype");
@@ -603,6 +609,7 @@ extern "C" int fsb_dwconv7x7_nhwc(const void* x, const float* weight, const floa
 
 extern "C" int fsb_conv3x3_cout1(const void* x, const float* weight, const float* bias, float* delta, float* disp_accum,
                                  int B, int C, int H, int W, int dtype, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_conv3x3_cout1");
   using namespace fsb;
   FSB_REQUIRE(x && weight && bias && delta, FSB_ERR_ARG, "fsb_conv3x3_cout1: NULL pointer");
   FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && is16(dtype), FSB_ERR_ARG, "fsb_conv3x3_cout1: bad size or dtype");
@@ -625,6 +632,7 @@ extern "C" int fsb_conv3x3_cout1(const void* x, const float* weight, const float
 }
 
 extern "C" int fsb_axpy_f32(float* y, const float* x, size_t n, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_axpy_f32");
   using namespace fsb;
   FSB_REQUIRE(y && x, FSB_ERR_ARG, "fsb_axpy_f32: NULL pointer");
   if (n == 0) return FSB_OK;

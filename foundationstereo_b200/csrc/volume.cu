@@ -278,6 +278,7 @@ static int volume_entry(const void* fl, const void* fr, const void* pl, const vo
 extern "C" int fsb_volume_gwc_concat(const void* fl, const void* fr, const void* pl, const void* pr,
                                      void* gwc, void* cat, int B, int C, int Cp, int G, int H, int W,
                                      int D, int dtype, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_volume_gwc_concat");
   const size_t hw = (size_t)(H > 0 ? H : 0) * (W > 0 ? W : 0) * (D > 0 ? D : 0);
   return volume_entry(fl, fr, pl, pr, gwc, cat, B, C, Cp, G, H, W, D, (size_t)(G > 0 ? G : 0) * hw,
                       (size_t)2 * (Cp > 0 ? Cp : 0) * hw, dtype, stream, "fsb_volume_gwc_concat");
@@ -285,6 +286,7 @@ extern "C" int fsb_volume_gwc_concat(const void* fl, const void* fr, const void*
 
 extern "C" int fsb_volume_combined(const void* fl, const void* fr, const void* pl, const void* pr, void* out, int B,
                                    int C, int Cp, int G, int H, int W, int D, int dtype, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_volume_combined");
   using namespace fsb;
   FSB_REQUIRE(fl && fr && pl && pr && out, FSB_ERR_ARG, "fsb_volume_combined: NULL pointer");
   FSB_REQUIRE(B > 0 && H > 0 && W > 0 && D > 0 && G > 0 && Cp > 0, FSB_ERR_ARG, "fsb_volume_combined: non-positive size");

@@ -19,13 +19,17 @@ from . import _lib, ops
 class Combined_Geo_Encoding_Volume:
     def __init__(self, init_fmap1: torch.Tensor, init_fmap2: torch.Tensor, geo_volume: torch.Tensor,
                  num_levels: int = 2, dx: Optional[torch.Tensor] = None, precision: int = _lib.FSB_PREC_TF32X3,
-                 workspace: Optional[dict] = None, nhwc16_out=None):
+                 workspace: Optional[dict] = None, nhwc16_out=None, corr_band: Optional[int] = None):
         """``workspace``: optional {"corr": [...], "geo": [...]} caller-owned level buffers of the
         right shapes (stable addresses, so a CUDA graph that holds the lookup can be replayed
         for every pair).  ``nhwc16_out``: optional callable (B,H,W) -> 16-bit (B,H,W,Cpad)
         buffer; when given, a call writes the fused 16-bit NHWC layout into that buffer and
         returns its (B, L*K*(Cg+1), H, W) channels-last view (what SelectiveUpdateBlock
-        consumes in place) instead of the reference's fp32 NCHW tensor."""
+        consumes in place) instead of the reference's fp32 NCHW tensor.
+        ``corr_band``: opt-in BANDED init correlation for disparities in [0, corr_band] (e.g. max_disp // 4): only the
+        band of the W x W matrix a lookup in that range can touch is computed and stored ((BHW, bw0 >> l) per level,
+        include/fsb200.h).  Inside the band results are identical to the full form; a disparity outside it reads zeros
+        where the reference reads real correlations (core/geometry.py:57 never clamps) -- hence opt-in."""
         if dx is None:
             raise ValueError("dx (the (1,1,2r+1,1) offsets, core/foundation_stereo.py:177-179) is required")
         K = dx.numel()
@@ -46,19 +50,33 @@ class Combined_Geo_Encoding_Volume:
         self._w2 = init_fmap2.shape[3]
         # lookup layout: geo level l is (BHW, D>>l, Cg), corr level l is (BHW, W2>>l)
         self._nhwc16_out = nhwc16_out
+        self.corr_band = int(corr_band) if corr_band else None
+        if self.corr_band is not None and precision == _lib.FSB_PREC_FP32:
+            raise ValueError("the banded correlation exists on the tensor-core path (FSB_PREC_TF32X3 / FSB_PREC_TF32)")
         if workspace is not None:
             self.corr_levels = list(workspace["corr"])
             self.geo_levels = list(workspace["geo"])
-            ops.corr_pyramid_into(init_fmap1, init_fmap2, self.corr_levels, precision)
+            if self.corr_band is not None:
+                ops.corr_pyramid_band(init_fmap1, init_fmap2, self.num_levels, precision, self.corr_band, r, self.corr_levels)
+            else:
+                ops.corr_pyramid_into(init_fmap1, init_fmap2, self.corr_levels, precision)
             ops.geo_pyramid_into(geo_volume, self.geo_levels)
         else:
-            self.corr_levels: List[torch.Tensor] = list(ops.corr_pyramid(init_fmap1, init_fmap2, self.num_levels, precision))
+            if self.corr_band is not None:
+                self.corr_levels = list(ops.corr_pyramid_band(init_fmap1, init_fmap2, self.num_levels, precision,
+                                                              self.corr_band, r))
+            else:
+                self.corr_levels = list(ops.corr_pyramid(init_fmap1, init_fmap2, self.num_levels, precision))
             self.geo_levels: List[torch.Tensor] = list(ops.geo_pyramid(geo_volume, self.num_levels))
 
     @staticmethod
-    def make_workspace(B: int, Cg: int, D: int, H: int, W: int, W2: int, num_levels: int, device) -> dict:
-        """Level buffers in the lookup layout: geo (BHW, D>>l, Cg), corr (BHW, W2>>l), fp32."""
+    def make_workspace(B: int, Cg: int, D: int, H: int, W: int, W2: int, num_levels: int, device,
+                       corr_band: Optional[int] = None, radius: int = 4) -> dict:
+        """Level buffers in the lookup layout: geo (BHW, D>>l, Cg), corr (BHW, W2>>l) -- or (BHW, bw0>>l) for a
+        banded correlation -- fp32."""
         n = B * H * W
+        if corr_band:
+            W2 = ops.corr_band_geometry(corr_band, radius, num_levels)[0]
         return {"corr": [torch.empty((n, W2 >> l), dtype=torch.float32, device=device) for l in range(num_levels)],
                 "geo": [torch.empty((n, D >> l, Cg), dtype=torch.float32, device=device) for l in range(num_levels)]}
 
@@ -70,7 +88,7 @@ class Combined_Geo_Encoding_Volume:
 
     @property
     def init_corr_pyramid(self) -> List[torch.Tensor]:
-        """[(BHW, 1, 1, W2_l)] like core/geometry.py:31-40."""
+        """[(BHW, 1, 1, W2_l)] like core/geometry.py:31-40 (the stored band, (BHW, 1, 1, bw0 >> l), in band mode)."""
         return [c[:, None, None, :] for c in self.corr_levels]
 
     def __call__(self, disp: torch.Tensor, coords: torch.Tensor, low_memory: bool = False) -> torch.Tensor:
@@ -78,14 +96,19 @@ class Combined_Geo_Encoding_Volume:
         ``low_memory`` is accepted and ignored like the reference (core/utils/utils.py:44)."""
         if self._nhwc16_out is not None:
             return self.lookup_nhwc16(disp, coords, self._nhwc16_out(*[disp.shape[i] for i in (0, 2, 3)]))
+        if self.corr_band is not None:
+            return ops.geo_lookup_band(self.geo_levels, self.corr_levels, disp, coords, self.radius, self.corr_band)
         return ops.geo_lookup(self.geo_levels, self.corr_levels, disp, coords, self.radius)
 
     def lookup_nhwc16(self, disp: torch.Tensor, coords: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
         """Fused-output lookup into the 16-bit (B,H,W,Cpad) buffer ``out``; returns the
         (B, L*K*(Cg+1), H, W) view of it (channels-last strides, pad channels hidden)."""
         B, H, W, Cpad = out.shape
-        ops.geo_lookup_nhwc16(self.geo_levels, self.corr_levels, disp.float().contiguous(),
-                              coords.float().contiguous(), self.radius, out)
+        if self.corr_band is not None:
+            ops.geo_lookup_band(self.geo_levels, self.corr_levels, disp, coords, self.radius, self.corr_band, out)
+        else:
+            ops.geo_lookup_nhwc16(self.geo_levels, self.corr_levels, disp.float().contiguous(),
+                                  coords.float().contiguous(), self.radius, out)
         planes = self.num_levels * (2 * self.radius + 1) * (self._shape[1] + 1)
         return torch.as_strided(out, (B, planes, H, W), (H * W * Cpad, 1, W * Cpad, Cpad))
 

@@ -27,12 +27,14 @@ class StereoHotPath:
     """
 
     def __init__(self, state_dict: Dict[str, Tensor], max_disp: int, corr_levels: int = 2, corr_radius: int = 4,
-                 num_groups: int = 8, device: str | torch.device = "cuda"):
+                 num_groups: int = 8, device: str | torch.device = "cuda", corr_band: bool = False):
         self.device = torch.device(device)
         self.D = max_disp // 4
         self.L = corr_levels
         self.r = corr_radius
         self.G = num_groups
+        # opt-in banded init correlation over disparities [0, D] (geometry.Combined_Geo_Encoding_Volume, corr_band=)
+        self.corr_band = self.D if corr_band else None
         self.update_block = SelectiveUpdateBlock(state_dict, self.device)
         self.dx = torch.linspace(-corr_radius, corr_radius, 2 * corr_radius + 1).reshape(1, 1, -1, 1)
         self._ws = {}
@@ -52,8 +54,10 @@ class StereoHotPath:
         ws = self._ws.get(key)
         if ws is None:  # level buffers with stable addresses: the per-iteration graph is captured once
             ws = self._ws[key] = Combined_Geo_Encoding_Volume.make_workspace(B, volume.shape[1], volume.shape[2], H, W,
-                                                                           fr.shape[3], self.L, fl.device)
-        geo = Combined_Geo_Encoding_Volume(fl.float(), fr.float(), volume, num_levels=self.L, dx=self.dx, workspace=ws)
+                                                                           fr.shape[3], self.L, fl.device,
+                                                                           corr_band=self.corr_band, radius=self.r)
+        geo = Combined_Geo_Encoding_Volume(fl.float(), fr.float(), volume, num_levels=self.L, dx=self.dx, workspace=ws,
+                                           corr_band=self.corr_band)
         if self.record_loop:
             ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
             ev[0].record()

@@ -259,3 +259,57 @@ def context_upsample(disp_low: torch.Tensor, weights: torch.Tensor, logits: bool
 def _(disp_low, weights, logits, scale):
     B, _, h, w = disp_low.shape
     return disp_low.new_empty((B, 4 * h, 4 * w), dtype=torch.float32)
+
+
+# ----------------------------------------------------------------------------------------
+# banded init correlation (opt-in; include/fsb200.h "BANDED form")
+# ----------------------------------------------------------------------------------------
+def corr_band_geometry(d_band: int, radius: int, num_levels: int):
+    """(bw0, off, align) of the band for lookups with disparities in [0, d_band] (fsb_corr_band_geometry)."""
+    import ctypes
+    bw0, off, align = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    check(lib().fsb_corr_band_geometry(int(d_band), int(radius), int(num_levels), ctypes.byref(bw0), ctypes.byref(off),
+                                       ctypes.byref(align)))
+    return bw0.value, off.value, align.value
+
+
+def corr_pyramid_band(f1: torch.Tensor, f2: torch.Tensor, num_levels: int, precision: int, d_band: int, radius: int,
+                      levels: List[torch.Tensor] | None = None) -> List[torch.Tensor]:
+    """Banded correlation pyramid: level l is (B*H*W, bw0 >> l) fp32 (see include/fsb200.h).  ``levels``: optional
+    caller-owned buffers of those shapes."""
+    _need_cuda(f1, f2)
+    f1 = f1.float().contiguous()
+    f2 = f2.float().contiguous()
+    B, C, H, W = f1.shape
+    assert f2.shape == f1.shape, "the band form needs left and right features of one shape"
+    bw0, _, _ = corr_band_geometry(d_band, radius, num_levels)
+    if levels is None:
+        levels = [torch.empty((B * H * W, bw0 >> l), dtype=torch.float32, device=f1.device) for l in range(num_levels)]
+    for l, t in enumerate(levels):
+        assert t.shape == (B * H * W, bw0 >> l) and t.dtype == torch.float32 and t.is_contiguous()
+    _call(f1, "fsb_corr_pyramid_band", f1.data_ptr(), f2.data_ptr(), level_array(levels), B, C, H, W, num_levels, precision,
+          int(d_band), int(radius))
+    return levels
+
+
+def geo_lookup_band(geo_levels: List[torch.Tensor], corr_levels: List[torch.Tensor], disp: torch.Tensor,
+                    coords: torch.Tensor, radius: int, d_band: int, out16: torch.Tensor | None = None) -> torch.Tensor:
+    """Kernel 3 over a banded correlation pyramid: fp32 (B, L*K*(Cg+1), H, W), or into the 16-bit NHWC buffer ``out16``."""
+    _need_cuda(disp, coords)
+    L = len(geo_levels)
+    B, _, H, W = disp.shape
+    disp = disp.float().contiguous()
+    coords = coords.float().contiguous()
+    N, D, Cg = geo_levels[0].shape
+    assert N == B * H * W and coords.numel() == N and corr_levels[0].shape[0] == N
+    K = 2 * radius + 1
+    if out16 is None:
+        out = torch.empty((B, L * K * (Cg + 1), H, W), dtype=torch.float32, device=disp.device)
+        layout = 0
+    else:
+        cpad = (L * K * (Cg + 1) + 63) // 64 * 64
+        assert out16.shape == (B, H, W, cpad) and out16.is_contiguous() and out16.dtype in (torch.float16, torch.bfloat16)
+        out, layout = out16, (1 if out16.dtype == torch.float16 else 2)
+    _call(disp, "fsb_geo_lookup_band", level_array(geo_levels), level_array(corr_levels), disp.data_ptr(), coords.data_ptr(),
+          out.data_ptr(), B, Cg, D, H, W, L, radius, layout, int(d_band))
+    return out

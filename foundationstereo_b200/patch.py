@@ -24,7 +24,7 @@ _SAVED = {}
 
 
 def install(model=None, modules: Optional[list] = None, fused_lookup: bool = True,
-            fused_upsample: bool = False) -> None:
+            fused_upsample: bool = False, corr_band: Optional[int] = None) -> None:
     """Rebind the three names in every loaded reference module that holds them and, if a
     FoundationStereo ``model`` is given, route ``model.update_block.forward`` through
     SelectiveUpdateBlock built from the module's own parameters.
@@ -39,10 +39,18 @@ def install(model=None, modules: Optional[list] = None, fused_lookup: bool = Tru
     (core/foundation_stereo.py:183-191) for a method that runs the two spx networks as before and
     then ONE kernel for softmax over the 9 weights + ``disp*4`` + convex upsampling."""
     geo_cls = Combined_Geo_Encoding_Volume
+    if corr_band:
+        # opt-in: banded init correlation for disparities in [0, corr_band] (use model.args.max_disp // 4); lookups
+        # outside that range read zeros where the reference reads real correlations (include/fsb200.h)
+        class BandedGeoEncodingVolume(Combined_Geo_Encoding_Volume):
+            def __init__(self, init_fmap1, init_fmap2, geo_volume, num_levels=2, dx=None, **kw):
+                super().__init__(init_fmap1, init_fmap2, geo_volume, num_levels=num_levels, dx=dx, corr_band=corr_band, **kw)
+        geo_cls = BandedGeoEncodingVolume
+    geo_base = geo_cls
     if model is not None:
         engine_of = install_update_block(model.update_block)
         if fused_lookup:
-            class FusedGeoEncodingVolume(Combined_Geo_Encoding_Volume):
+            class FusedGeoEncodingVolume(geo_base):
                 def __init__(self, init_fmap1, init_fmap2, geo_volume, num_levels=2, dx=None):
                     super().__init__(init_fmap1, init_fmap2, geo_volume, num_levels=num_levels, dx=dx,
                                      nhwc16_out=lambda B, H, W: engine_of().corr_buffer(B, H, W))

@@ -564,12 +564,18 @@ class SelectiveUpdateBlock:
         with torch.no_grad(), torch.cuda.device(self.device):
             plan = self.plan_for(B, H, W)
             self._ingest(plan, list(net), inp, att, None, disp.float())
-            key = tuple(t.data_ptr() for t in list(geo.geo_levels) + list(geo.corr_levels)) + (geo.radius, mask_every_iter)
+            key = tuple(t.data_ptr() for t in list(geo.geo_levels) + list(geo.corr_levels)) + (
+                geo.radius, mask_every_iter, getattr(geo, "corr_band", None))
             if plan.iter_key != key:
                 levels = (list(geo.geo_levels), list(geo.corr_levels), geo.radius)
                 from . import ops
-                plan.lookup = lambda: ops.geo_lookup_nhwc16(levels[0], levels[1], plan.disp, plan.coords, levels[2],
-                                                            plan.corr16)
+                band = getattr(geo, "corr_band", None)
+                if band is not None:
+                    plan.lookup = lambda: ops.geo_lookup_band(levels[0], levels[1], plan.disp, plan.coords, levels[2], band,
+                                                              plan.corr16)
+                else:
+                    plan.lookup = lambda: ops.geo_lookup_nhwc16(levels[0], levels[1], plan.disp, plan.coords, levels[2],
+                                                                plan.corr16)
                 plan.iter_key = key
                 plan.iter_graph = None
                 plan.loop_graphs = {}

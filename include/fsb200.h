@@ -120,6 +120,24 @@ int fsb_geo_lookup(float* const* geo_levels, float* const* corr_levels, const fl
                    const float* coords, void* out, int B, int Cg, int D, int H, int W, int W2,
                    int L, int r, int out_layout, fsb_stream_t stream);
 
+/* ---- kernels 2 / 3, BANDED form (opt-in; north_star kernel 2 "a banded tcgen05/TMEM GEMM") ---------
+ * The lookup of core/geometry.py:57 samples the init correlation of the pixel in image column w1 at
+ * x = (w1 - disp) / 2^l + dx, |dx| <= r.  For disparities in [0, d_band] that is a band of the W x W matrix; the band
+ * form computes and stores only that band: level l is (B*H*W, bw0 >> l) fp32 and the row of a pixel in column w1
+ * holds the level-l columns [s0 >> l, (s0 + bw0) >> l), s0 = floor((w1 - off) / align) * align, zeros where that leaves
+ * the image.  fsb_corr_band_geometry gives (bw0, off, align) for (d_band, radius, L): align = 4 << (L-1),
+ * off = d_band + ((radius + 2) << (L-1)), bw0 = d_band + ((2 radius + 5) << (L-1)) + align - 1 rounded up to align.
+ * PARITY STATEMENT: inside the band (0 <= disp <= d_band) lookups are identical to the full-matrix form; outside it
+ * they read ZEROS where the reference reads real correlations (it never clamps the disparity).  The full-matrix
+ * entry points above stay the drop-in default.  Needs W1 == W2 = W, W % 4 == 0 and bw0 + align <= 224. */
+int fsb_corr_band_geometry(int d_band, int radius, int L, int* bw0, int* off, int* align);
+int fsb_corr_pyramid_band(const float* f1, const float* f2, float* const* corr_levels, int B, int C, int H, int W, int L,
+                          int precision /* FSB_PREC_TF32X3 | FSB_PREC_TF32 */, int d_band, int radius, fsb_stream_t stream);
+/* fsb_geo_lookup over a banded correlation pyramid built with the same (d_band, r, L) */
+int fsb_geo_lookup_band(float* const* geo_levels, float* const* corr_levels, const float* disp, const float* coords,
+                        void* out, int B, int Cg, int D, int H, int W, int L, int r, int out_layout, int d_band,
+                        fsb_stream_t stream);
+
 /* ---- kernel 4: 3x3 / 1x1 convolution as a tcgen05 implicit GEMM with fused epilogue ----
  * The convolutions of the update block (core/update.py:20-159): SelectiveConvGRU conv0/conv1,
  * the RaftConvGRU gate convolutions convz/convr/convq with their sigmoid / tanh / blend

@@ -23,6 +23,8 @@ from .hotpath import (  # noqa: F401
     lerp_rows,
     geo_lookup,
     GeoEncodingVolume,
+    corr_band_geometry,
+    band_limit_corr_pyramid,
     update_block,
     selective_gru,
     raft_gru,

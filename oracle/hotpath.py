@@ -167,13 +167,46 @@ def geo_lookup(
     return out.reshape(B, H, W, -1).permute(0, 3, 1, 2).contiguous()
 
 
-class GeoEncodingVolume:
-    """Oracle counterpart of Combined_Geo_Encoding_Volume (core/geometry.py:17-65)."""
+def corr_band_geometry(d_band: int, radius: int, num_levels: int) -> Tuple[int, int, int]:
+    """(bw0, off, align) of the OPT-IN banded init correlation (include/fsb200.h, "BANDED form"): the pixel in image
+    column w1 keeps the level-0 columns [s0, s0 + bw0), s0 = floor((w1 - off) / align) * align, i.e. what a lookup
+    with disparities in [0, d_band] can touch at any level (core/geometry.py:57: x = (w1 - disp) / 2^l + dx)."""
+    align = 4 << (num_levels - 1)
+    left = (radius + 2) << (num_levels - 1)
+    right = (radius + 3) << (num_levels - 1)
+    bw0 = -(-(d_band + left + right + align - 1) // align) * align
+    return bw0, d_band + left, align
 
-    def __init__(self, f1: Tensor, f2: Tensor, volume: Tensor, num_levels: int = 2, radius: int = 4):
+
+def band_limit_corr_pyramid(corr_levels: Sequence[Tensor], W1: int, d_band: int, radius: int) -> List[Tensor]:
+    """The band form's semantics restated on the full pyramid: every (BHW, W2_l) level with the entries OUTSIDE the
+    pixel's band set to zero.  Not a reference behaviour -- the reference keeps the whole row -- so a lookup through
+    this pyramid equals the reference's exactly when it stays inside the band."""
+    L = len(corr_levels)
+    bw0, off, align = corr_band_geometry(d_band, radius, L)
+    out = []
+    for l, c in enumerate(corr_levels):
+        N, Wl = c.shape
+        w1 = torch.arange(N) % W1
+        s0 = torch.div(w1 - off, align, rounding_mode="floor") * align
+        sl = torch.div(s0, 2 ** l, rounding_mode="floor")[:, None]
+        col = torch.arange(Wl)[None, :]
+        keep = (col >= sl) & (col < sl + (bw0 >> l))
+        out.append(c * keep.to(c.dtype))
+    return out
+
+
+class GeoEncodingVolume:
+    """Oracle counterpart of Combined_Geo_Encoding_Volume (core/geometry.py:17-65).  ``corr_band`` restates the
+    opt-in banded form (entries outside the band zeroed, see band_limit_corr_pyramid)."""
+
+    def __init__(self, f1: Tensor, f2: Tensor, volume: Tensor, num_levels: int = 2, radius: int = 4,
+                 corr_band: int = 0):
         self.num_levels = num_levels
         self.radius = radius
         self.corr_levels = corr_pyramid(f1, f2, num_levels)
+        if corr_band:
+            self.corr_levels = band_limit_corr_pyramid(self.corr_levels, f1.shape[3], corr_band, radius)
         self.geo_levels = geo_pyramid(volume, num_levels)
 
     def __call__(self, disp: Tensor, coords: Tensor) -> Tensor:

@@ -437,3 +437,82 @@ def test_refine_mask_once_equals_mask_every_iteration(fsb):
             res.append((disp.clone(), mask.clone(), net[0].clone()))
     for r in res[1:]:
         assert torch.equal(r[0], res[0][0]) and torch.equal(r[1], res[0][1]) and torch.equal(r[2], res[0][2])
+
+
+# ------------------------------------------------------------- banded init correlation (opt-in)
+@pytest.mark.parametrize("cfg", [
+    # B, C, H, W, D (= d_band), L, r
+    (2, 32, 5, 160, 40, 2, 4),
+    (1, 64, 3, 512, 104, 2, 4),   # ERP width: several m tiles, band 144 of 512 columns
+    (1, 32, 4, 96, 24, 3, 3),     # three levels, other radius
+    (1, 32, 3, 64, 104, 2, 4),    # band wider than the image: every row clipped on both sides
+])
+def test_banded_correlation(fsb, cfg):
+    """Band form (include/fsb200.h): (1) the stored band equals the full-matrix pyramid's entries, zeros where the band
+    leaves the image; (2) lookups with disparities inside [0, d_band] are IDENTICAL to the full form's; (3) for any
+    disparity the band lookup equals the oracle's lookup through the band-limited pyramid (zeros outside the band)."""
+    from foundationstereo_b200 import ops
+    from foundationstereo_b200._lib import FSB_PREC_TF32X3
+    B, C, H, W, D, L, r = cfg
+    K = 2 * r + 1
+    x = oracle.make_inputs(B=B, C=C, H=H, W=W, D=D, Cg=28, seed=31)
+    fl, fr, vol = dev(x["fl"]), dev(x["fr"]), dev(x["volume"])
+    dx = torch.linspace(-r, r, K).reshape(1, 1, -1, 1)
+    full = fsb.Combined_Geo_Encoding_Volume(fl, fr, vol, num_levels=L, dx=dx)
+    band = fsb.Combined_Geo_Encoding_Volume(fl, fr, vol, num_levels=L, dx=dx, corr_band=D)
+    bw0, off, align = ops.corr_band_geometry(D, r, L)
+    assert (bw0, off, align) == oracle.corr_band_geometry(D, r, L)
+    w1 = torch.arange(B * H * W, device="cuda") % W
+    s0 = torch.div(w1 - off, align, rounding_mode="floor") * align
+    for l in range(L):
+        bl, fu = band.corr_levels[l], full.corr_levels[l]
+        assert bl.shape == (B * H * W, bw0 >> l)
+        col = (s0 >> l)[:, None] + torch.arange(bw0 >> l, device="cuda")[None, :]
+        ok = (col >= 0) & (col < fu.shape[1])
+        want = torch.gather(fu, 1, col.clamp(0, fu.shape[1] - 1)) * ok
+        assert torch.equal(bl, want), (l, float((bl - want).abs().max()))
+    coords = dev(x["coords"])
+    g = torch.Generator().manual_seed(5)
+    inside = (torch.rand(B, 1, H, W, generator=g) * D).cuda()
+    inside.view(-1)[:4] = torch.tensor([0.0, float(D), D - 0.5, 0.25], device="cuda")
+    assert torch.equal(band(inside, coords), full(inside, coords))
+    anyd = dev(x["disp"]) * 1.5 - 10.0                      # also far outside [0, D]
+    orc = oracle.GeoEncodingVolume(x["fl"], x["fr"], x["volume"], L, r, corr_band=D)
+    with torch.no_grad():
+        want = orc(anyd.cpu(), x["coords"])
+    assert rel_err(band(anyd, coords).cpu(), want) <= TOL_FP32
+    # fused 16-bit output over the band
+    cpad = (L * K * 29 + 63) // 64 * 64
+    buf = torch.empty(B, H, W, cpad, dtype=torch.float16, device="cuda")
+    v16 = band.lookup_nhwc16(inside, coords, buf)
+    ref16 = full.lookup_nhwc16(inside, coords, torch.empty_like(buf))
+    assert torch.equal(v16, ref16)
+
+
+def test_banded_hot_path_equals_full_when_disparities_stay_inside(fsb):
+    """StereoHotPath(corr_band=True): with the disparity kept inside [0, D] the whole refinement equals the full form."""
+    H, W, D, iters = 24, 64, 32, 4
+    p = oracle.make_update_block_params(seed=2, delta_scale=0.05)
+    x = oracle.make_inputs(B=1, C=32, H=H, W=W, D=D, Cg=28, seed=4)
+    x["disp"] = x["disp"].clamp(4.0, D - 4.0)
+    c = lambda t: t.cuda()
+    outs = []
+    for banded in (False, True):
+        hp = fsb.StereoHotPath(p, max_disp=4 * D, corr_band=banded)
+        for _ in range(2):
+            got, _, _ = hp.run(c(x["fl"]), c(x["fr"]), c(x["pl"]), c(x["pr"]), c(x["volume"]), c(x["disp"]),
+                               [c(t) for t in x["net"]], [c(t) for t in x["inp"]], [c(t) for t in x["att"]], iters)
+        outs.append(got.clone())
+    assert float(outs[0].min()) > 0 and float(outs[0].max()) < D
+    assert torch.equal(outs[0], outs[1])
+
+
+def test_banded_correlation_rejects_unsupported(fsb):
+    from foundationstereo_b200 import ops
+    from foundationstereo_b200._lib import FSB_PREC_TF32X3
+    f = torch.randn(1, 32, 2, 64, device="cuda")
+    with pytest.raises(fsb.FsbError):   # a band too wide for one 256-column window (d_band 104, four levels)
+        ops.corr_pyramid_band(f, f, 4, FSB_PREC_TF32X3, 104, 4)
+    f3 = torch.randn(1, 32, 2, 62, device="cuda")
+    with pytest.raises(fsb.FsbError):   # W % 4 != 0: no TMA-fed path
+        ops.corr_pyramid_band(f3, f3, 2, FSB_PREC_TF32X3, 16, 4)
