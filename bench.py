@@ -569,6 +569,9 @@ def emit(obj) -> None:
 
 
 def main():
+    if os.environ.get("FSB_BENCH_WATCHDOG"):  # debugging aid: dump every thread's Python stack and exit after N seconds
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["FSB_BENCH_WATCHDOG"]), exit=True)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)

@@ -106,6 +106,7 @@ class SelectiveUpdateBlock:
         self.dtype = dtype
         self.use_graph = use_graph and _os.environ.get("FSB_GRAPH", "1") != "0"
         self.loop_graph = _os.environ.get("FSB_LOOP_GRAPH", "1") != "0"  # refine(): one graph for all iterations
+        self.pdl_cross = _os.environ.get("FSB_PDL_CROSS", "0") == "1"  # programmatic edges across lanes too (hung: see run_steps)
         self.two_lanes = _os.environ.get("FSB_TWO_LANES", "1") != "0"  # side stream for encoder / mask head
         self.copy_outputs = copy_outputs  # forward returns fresh tensors instead of views of the plan's buffers
         self.dot_head4 = dot_head4  # False: disp_head.conv.4 as a tensor-core convolution launch + a separate disp += delta
@@ -250,7 +251,12 @@ class SelectiveUpdateBlock:
         nsteps = sum(k * k * sum(srcs[i].shape[3] // 64 for i in idx) for k, idx in segs)
         nacc = len(segs)
         if epilogue == _lib.FSB_EPI_GATE_ZR:
-            cand, rows_of = [64, 128, 256], lambda bn: 2 * cout // 2  # rows == 2 * hidden exactly
+            # N = 256 (both gates of all 128 hidden channels in one tile, 2 x 256 = all 512 TMEM columns, accumulators NOT
+            # double-buffered) is what this model prefers from 12 pairs of 480x640 on -- and on the B200 it HUNG the
+            # two-lane, PDL-chained iteration graph there (2 of 2 runs; never with one lane, without PDL, without graphs
+            # or with N = 128; profiles/r02f_hang_isolation.txt).  Root cause not established; N = 128 is also the
+            # faster choice (98.7 vs 96.4 pairs/s at 12 pairs), so the gate launches stay on double-buffered tiles.
+            cand, rows_of = [64, 128], lambda bn: 2 * cout // 2  # rows == 2 * hidden exactly
         elif epilogue == _lib.FSB_EPI_GATE_Q:
             cand, rows_of = [32, 64, 128], lambda bn: cout
         else:
@@ -297,6 +303,11 @@ class SelectiveUpdateBlock:
         # layer shape of the block (tools/conv_sweep.py: 3x3 512->512 288 vs 295 us, 384->384 182 vs 184 us), so
         # no launch defaults to the halo layout any more; `halo=[...]` still selects it per launch.
         plan.tile = {}
+        import os as _os
+        for kv in _os.environ.get("FSB_TILE", "").split(","):   # experiments: FSB_TILE="gru04.zr=128,gru16.conv1=128"
+            if "=" in kv:
+                k, v = kv.split("=")
+                plan.tile[k.strip()] = (_lib.FSB_CONV_LAYOUT_TAP, int(v))
         plan.shape = [(B, H, W), (B, _down(H), _down(W)), (B, _down(_down(H)), _down(_down(W)))]
         new = lambda lvl, c, dtype=dt: torch.empty(*plan.shape[lvl], c, dtype=dtype, device=dev)
         plan.h32 = [new(l, hd, torch.float32) for l in range(3)]
@@ -477,6 +488,24 @@ class SelectiveUpdateBlock:
         if lookup:
             plan.lookup()
         single = not self.two_lanes
+        # A launch that follows a cross-lane wait goes out WITHOUT the programmatic-dependent-launch attribute, so the
+        # captured graph keeps a full (completion) edge across lanes and only same-lane edges are programmatic.
+        # With every edge programmatic the two-lane iteration graph hung on the B200 from 12 pairs of 480x640 on
+        # (profiles/r02f_hang_isolation.txt); FSB_PDL_CROSS=1 restores that behaviour for experiments.
+        lib = _lib.lib()
+        fence = [False, False]
+
+        def launch(fn, lane):
+            if fence[lane] and not self.pdl_cross:
+                fence[lane] = False
+                old = lib.fsb_set_pdl(0)
+                try:
+                    fn()
+                finally:
+                    lib.fsb_set_pdl(old)
+            else:
+                fn()
+
         for fn, lane, tag in zip(plan.steps, plan.lanes, plan.tags):
             if (tag == "mask") != only_mask and (only_mask or not mask):
                 continue
@@ -486,13 +515,15 @@ class SelectiveUpdateBlock:
                 continue
             if fn is FORK:
                 plan.side.wait_stream(main)
+                fence[1] = True
             elif fn is JOIN:
                 main.wait_stream(plan.side)
+                fence[0] = True
             elif lane == 0:
-                fn()
+                launch(fn, 0)
             else:
                 with torch.cuda.stream(plan.side):
-                    fn()
+                    launch(fn, 1)
         if lookup and not plan.accum:
             C.axpy(plan.disp, plan.delta)
 
