@@ -468,6 +468,15 @@ def run_b200(args):
         }
         per_step = {"volume_gwc_concat": n_micro, "corr_pyramid": n_micro, "geo_pyramid": n_micro,
                     "geo_lookup": iters * n_micro, "geo_lookup_fp32_nchw": 0}
+        # opt-in banded init correlation (disparities in [0, D]): reported beside the full-matrix default
+        bw0 = ops.corr_band_geometry(D, r, L)[0]
+        if bw0 + (4 << (L - 1)) <= 224:
+            band_lv = [torch.empty((c["B"] * c["H"] * c["W"], bw0 >> l), dtype=torch.float32, device=device) for l in range(L)]
+            kern_ms["corr_pyramid_band"] = time_kernel(
+                torch, lambda: ops.corr_pyramid_band(dev["fl"], dev["fr"], L, FSB_PREC_TF32X3, D, r, band_lv), 20, flush)
+            kern_ms["geo_lookup_band"] = time_kernel(
+                torch, lambda: ops.geo_lookup_band(geo.geo_levels, band_lv, dev["disp"], coords, r, D, plan.corr16), 20, flush)
+            per_step.update(corr_pyramid_band=0, geo_lookup_band=0)
         if args.config == "vits480":
             kern_ms["corr_pyramid_fp32_cuda_cores"] = time_kernel(torch, lambda: ops.corr_pyramid(dev["fl"], dev["fr"], L, FSB_PREC_FP32), 20, flush)
             # the steps either side of the loop: not part of the timed step, reported beside it
@@ -478,6 +487,10 @@ def run_b200(args):
             per_step.update(corr_pyramid_fp32_cuda_cores=0, softmax_disparity_regression=0, softmax_context_upsample=0)
         alg = algorithmic_bytes(c)
         alg["corr_pyramid_fp32_cuda_cores"] = alg["corr_pyramid"]
+        px_ = c["B"] * c["H"] * c["W"]
+        alg["corr_pyramid_band"] = 8 * px_ * c["C"] + 4 * px_ * sum(bw0 >> l for l in range(L))
+        K_ = 2 * r + 1
+        alg["geo_lookup_band"] = alg["geo_lookup"]   # the lookup reads the same windows, only their addresses differ
         kernels = {}
         for k, ms in kern_ms.items():
             gbs = alg[k] / (ms * 1e-3) / 1e9

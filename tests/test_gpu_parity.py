@@ -215,10 +215,30 @@ def test_update_block_vs_oracle_midsize(fsb):
     ub = fsb.SelectiveUpdateBlock(p, "cuda")
     net, mask, delta = ub([t.cuda() for t in x["net"]], [t.cuda() for t in x["inp"]], corr.cuda(), x["disp"].cuda(),
                           [t.cuda() for t in x["att"]])
+    # measured error per output, committed under profiles/: the max-normalised figure the tolerance is read against AND
+    # an elementwise one (|d| / (|ref| + 1e-3 max|ref|): a small-magnitude channel that is entirely wrong shows up here)
+    import json
+    import os
+    report = {}
+    for name, got, want in [("net0", net[0], want_net[0]), ("net1", net[1], want_net[1]), ("net2", net[2], want_net[2]),
+                            ("mask", mask, want_mask), ("delta", delta, want_delta)]:
+        g, w = got.double().cpu(), want.double()
+        d = (g - w).abs()
+        elem = d / (w.abs() + 1e-3 * w.abs().max())
+        per_ch = d.amax(dim=(0, 2, 3)) / w.abs().amax(dim=(0, 2, 3)).clamp_min(1e-30)
+        report[name] = {"max_normalised": float(d.max() / w.abs().max()), "elementwise_p99": float(elem.flatten().quantile(0.99)),
+                        "elementwise_max": float(elem.max()), "worst_channel_max_normalised": float(per_ch.max())}
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    with open(os.path.join(out, "update_block_errors.json"), "w") as fh:
+        json.dump({"shape": "B=2, 40x56, fp16 operands / fp32 accumulate vs fp32 CPU oracle", "outputs": report}, fh, indent=1)
+    print("[update block errors]", json.dumps(report))
     for i in range(3):
         assert rel_err(net[i].cpu(), want_net[i]) <= TOL_F16
     assert rel_err(mask.cpu(), want_mask) <= TOL_F16
     assert rel_err(delta.cpu(), want_delta) <= TOL_F16
+    for name, r in report.items():   # no channel may be wrong as a whole, however small it is
+        assert r["worst_channel_max_normalised"] <= 2.5 * TOL_F16, (name, r)
 
 
 @pytest.mark.parametrize("iters", [8, 32])
