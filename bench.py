@@ -417,8 +417,8 @@ def run_b200(args):
         # ---- inside the clocks window: the refinement loop alone and the per-launch durations of one update step
         ws = fsb.Combined_Geo_Encoding_Volume.make_workspace(c["B"], c["Cg"], D, c["H"], c["W"], c["W"], L, device)
         geo_ws = fsb.Combined_Geo_Encoding_Volume(dev["fl"], dev["fr"], dev["volume"], num_levels=L, dx=hp.dx, workspace=ws)
-        for _ in range(2):
-            ub.refine(geo_ws, dev["net"], dev["inp"], dev["att"], dev["disp"], 2)
+        for _ in range(2):   # eager pass, then the capture of the whole-loop graph for this geometry volume
+            ub.refine(geo_ws, dev["net"], dev["inp"], dev["att"], dev["disp"], iters)
         g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
         g0.record()

@@ -370,7 +370,7 @@ dwconv7x7_kernel(const T* __restrict__ x, const float* __restrict__ weight, cons
 constexpr int kC1TY = 8, kC1TX = 32, kC1PY = kC1TY + 2, kC1PX = kC1TX + 2, kC1PS = kC1PX + 1;
 
 template <typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 conv3x3_cout1_kernel(const T* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                      float* __restrict__ delta, float* __restrict__ disp, int C, int H, int W) {
   pdl_launch_dependents();
@@ -406,21 +406,14 @@ conv3x3_cout1_kernel(const T* __restrict__ x, const float* __restrict__ w, const
     for (int k = 0; k < kPix; ++k)
 #pragma unroll
       for (int t = 0; t < 9; ++t) acc[k][t] = make_float2(0.f, 0.f);
-    // the 4 lanes of a pixel read 64 contiguous bytes per chunk of 32 channels; the next chunk's loads are in
-    // flight while this one is multiplied
-    uint4 u[kPix], un[kPix];
-#pragma unroll
-    for (int k = 0; k < kPix; ++k) u[k] = ok[k] ? *reinterpret_cast<const uint4*>(src[k]) : make_uint4(0u, 0u, 0u, 0u);
+    // the 4 lanes of a pixel read 64 contiguous bytes per chunk of 32 channels; two CTAs per SM (128 registers) cover
+    // the load latency of each other
     for (int c0 = 0; c0 < C; c0 += 32) {
-      if (c0 + 32 < C) {
-#pragma unroll
-        for (int k = 0; k < kPix; ++k)
-          un[k] = ok[k] ? *reinterpret_cast<const uint4*>(src[k] + c0 + 32) : make_uint4(0u, 0u, 0u, 0u);
-      }
       float2 v[kPix][4];
 #pragma unroll
       for (int k = 0; k < kPix; ++k) {
-        v[k][0] = unpack2f<T>(u[k].x); v[k][1] = unpack2f<T>(u[k].y); v[k][2] = unpack2f<T>(u[k].z); v[k][3] = unpack2f<T>(u[k].w);
+        const uint4 u = ok[k] ? *reinterpret_cast<const uint4*>(src[k] + c0) : make_uint4(0u, 0u, 0u, 0u);
+        v[k][0] = unpack2f<T>(u.x); v[k][1] = unpack2f<T>(u.y); v[k][2] = unpack2f<T>(u.z); v[k][3] = unpack2f<T>(u.w);
       }
       const float* wc = ws + c0 + sub * 8;
 #pragma unroll
@@ -437,8 +430,6 @@ conv3x3_cout1_kernel(const T* __restrict__ x, const float* __restrict__ w, const
           acc[k][t] = __ffma2_rn(v[k][3], w3, acc[k][t]);
         }
       }
-#pragma unroll
-      for (int k = 0; k < kPix; ++k) u[k] = un[k];
     }
 #pragma unroll
     for (int k = 0; k < kPix; ++k) {

@@ -237,8 +237,9 @@ def test_update_block_vs_oracle_midsize(fsb):
         assert rel_err(net[i].cpu(), want_net[i]) <= TOL_F16
     assert rel_err(mask.cpu(), want_mask) <= TOL_F16
     assert rel_err(delta.cpu(), want_delta) <= TOL_F16
-    for name, r in report.items():   # no channel may be wrong as a whole, however small it is
-        assert r["worst_channel_max_normalised"] <= 2.5 * TOL_F16, (name, r)
+    for name, r in report.items():   # measured on the B200: 4e-4 .. 6e-4 max-normalised, worst single channel 8e-4
+        assert r["max_normalised"] <= 5e-3, (name, r)               # (profiles/r02k_update_block_errors.json)
+        assert r["worst_channel_max_normalised"] <= 1e-2, (name, r)  # no channel may be wrong as a whole, however small
 
 
 @pytest.mark.parametrize("iters", [8, 32])

@@ -2,6 +2,9 @@
 # compute-sanitizer over one small pass of every kernel (tools/sanitize_case.py).  ONE tool per gpurun call
 # (B200_PROFILING.md: several tools in one call have left a GPU unusable):
 #     gpurun -- 'bash tools/sanitize.sh memcheck'      (then racecheck, initcheck, synccheck in later calls)
+# STATUS on this pool (round 2): the plain run passes (116 launches, results checked against the CPU oracle), but
+# `compute-sanitizer` answers "closed on this pool and stays closed" (exit 86, gpurun_out/sanitize_memcheck.log), so no
+# sanitizer summary could be committed; the script is kept for a pool where the tool is open.
 # The plain run must pass first; the summary line of the tool goes to gpurun_out/sanitize_<tool>.log.
 TOOL=${1:-memcheck}
 mkdir -p gpurun_out

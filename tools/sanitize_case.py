@@ -32,6 +32,7 @@ featb = band(c(x["disp"]).clamp(0, D), c(x["coords"]))
 p = oracle.make_update_block_params(seed=1)
 ub = fsb.SelectiveUpdateBlock(p, "cuda", use_graph=False)
 net, mask, delta = ub([c(t) for t in x["net"]], [c(t) for t in x["inp"]], feat, c(x["disp"]), [c(t) for t in x["att"]])
+net, mask, delta = [t.clone() for t in net], mask.clone(), delta.clone()   # views of the plan's buffers: refine() below reuses them
 ws = fsb.Combined_Geo_Encoding_Volume.make_workspace(B, 28, D, H, W, W, L, "cuda")
 geo = fsb.Combined_Geo_Encoding_Volume(c(x["fl"]), c(x["fr"]), c(x["volume"]), num_levels=L, dx=dx, workspace=ws)
 disp2, mask2, _ = ub.refine(geo, [c(t) for t in x["net"]], [c(t) for t in x["inp"]], [c(t) for t in x["att"]], c(x["disp"]), 2)
