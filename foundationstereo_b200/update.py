@@ -106,6 +106,10 @@ class SelectiveUpdateBlock:
         self.dtype = dtype
         self.use_graph = use_graph and _os.environ.get("FSB_GRAPH", "1") != "0"
         self.loop_graph = _os.environ.get("FSB_LOOP_GRAPH", "1") != "0"  # refine(): one graph for all iterations
+        # refine(): pool2x for the NEXT iteration on the side lane under the disparity head instead of at the head of the
+        # iteration.  Measured neutral on the B200 (90.5 / 91.4 with, 91.8 / 91.6 pairs/s without: the extra cross-lane
+        # fork / join costs what the 45 us of pooling save), so it is off by default; FSB_TAIL_POOLS=1 switches it on.
+        self.tail_pools = _os.environ.get("FSB_TAIL_POOLS", "0") == "1"
         self.pdl_cross = _os.environ.get("FSB_PDL_CROSS", "0") == "1"  # programmatic edges across lanes too (hung: see run_steps)
         self.two_lanes = _os.environ.get("FSB_TWO_LANES", "1") != "0"  # side stream for encoder / mask head
         self.copy_outputs = copy_outputs  # forward returns fresh tensors instead of views of the plan's buffers
@@ -342,12 +346,16 @@ class SelectiveUpdateBlock:
             if n == 3:
                 # gru16: x = [inp[2], pool2x(net[1])]                               (core/update.py:143)
                 p1 = new(2, hd)
+                plan.tag = "pool_head"
                 add("pool2x(net1)", lambda: C.pool2x(plan.h32[1], p1))
+                plan.tag = None
                 self._gru(plan, "gru16", 2, [plan.inp16[2], p1])
                 plan.keep.append(p1)
             # gru08: x = [inp[1], pool2x(net[0]) (, interp(net[2]) with three levels)]  (:145-148)
             p0 = new(1, hd)
+            plan.tag = "pool_head"
             add("pool2x(net0)", lambda: C.pool2x(plan.h32[0], p0))
+            plan.tag = None
             xs08 = [plan.inp16[1], p0]
             if n == 3:
                 u2 = new(1, hd)
@@ -360,6 +368,19 @@ class SelectiveUpdateBlock:
             add("interp(net1)", lambda: C.resize(plan.h32[1], u1))
             self._gru(plan, "gru04", 0, [plan.inp16[0], motion, u1])
             plan.keep += xs08 + [u1]
+        if n >= 2:
+            # `refine` (which owns the loop) pools the NEXT iteration's inputs here, on the side lane under the disparity
+            # head, instead of at the head of the next iteration: pool2x(net[1]) / pool2x(net[0]) only depend on hidden
+            # states that are final once gru08 / gru04 have run (core/update.py:143-146), and the two small streaming
+            # kernels (45 us at 8 pairs) leave the critical path.  The drop-in `forward` keeps them at the head.
+            plan.tag = "pool_tail"
+            add(FORK, FORK)
+            plan.lane = 1
+            if n == 3:
+                add("pool2x(net1)'", lambda: C.pool2x(plan.h32[1], p1))
+            add("pool2x(net0)'", lambda: C.pool2x(plan.h32[0], p0))
+            plan.lane = 0
+            plan.tag = None
         # mask head (core/update.py:134-139,158) -- side lane; tagged so `refine` can leave it out of the iteration
         # graph and run it once after the last iteration (only that one's mask is consumed in test_mode,
         # core/foundation_stereo.py:243-247)
@@ -478,13 +499,31 @@ class SelectiveUpdateBlock:
         output writes here and convc1 reads it in place."""
         return self.plan_for(B, H, W).corr16
 
-    def run_steps(self, plan: _Plan, lookup: bool = False, mask: bool = True, only_mask: bool = False) -> None:
+    def run_steps(self, plan: _Plan, lookup: bool = False, mask: bool = True, only_mask: bool = False,
+                  tail_pools: bool = False, only_tag: Optional[str] = None) -> None:
         """The launches of one refinement step, issued on the current stream and the plan's
         side stream (no graph).  With ``lookup`` the bound geometry lookup runs first and the
         disparity update (core/foundation_stereo.py:242) last: one whole loop iteration.
-        ``mask=False`` leaves the mask head out; ``only_mask`` runs nothing else."""
+        ``mask=False`` leaves the mask head out; ``only_mask`` / ``only_tag`` run nothing but the steps of that tag (on
+        the current stream); ``tail_pools``: the pool2x launches run at the end of the step for the NEXT one (see
+        `_build_plan`) instead of at its head."""
+        if only_mask:
+            only_tag = "mask"
+        only = only_tag is not None
+
+        def skip(tag):
+            if only:
+                return tag != only_tag
+            if tag == "mask":
+                return not mask
+            if tag == "pool_head":
+                return tail_pools
+            if tag == "pool_tail":
+                return not tail_pools
+            return False
+
         main = torch.cuda.current_stream()
-        plan.accum = lookup and self.dot_head4 and not only_mask  # disp += delta inside the disp_head.conv.4 launch
+        plan.accum = lookup and self.dot_head4 and not only  # disp += delta inside the disp_head.conv.4 launch
         if lookup:
             plan.lookup()
         single = not self.two_lanes
@@ -507,9 +546,9 @@ class SelectiveUpdateBlock:
                 fn()
 
         for fn, lane, tag in zip(plan.steps, plan.lanes, plan.tags):
-            if (tag == "mask") != only_mask and (only_mask or not mask):
+            if skip(tag):
                 continue
-            if single or only_mask:
+            if single or only:
                 if fn is not FORK and fn is not JOIN:
                     fn()
                 continue
@@ -527,13 +566,25 @@ class SelectiveUpdateBlock:
         if lookup and not plan.accum:
             C.axpy(plan.disp, plan.delta)
 
-    def _capture(self, plan: _Plan, lookup: bool, mask: bool = True, repeat: int = 1) -> torch.cuda.CUDAGraph:
+    def _capture(self, plan: _Plan, lookup: bool, mask: bool = True, repeat: int = 1,
+                 tail_pools: bool = False) -> torch.cuda.CUDAGraph:
+        # Dead Python cycles that hold CUDA graphs / streams of an earlier engine must not be collected DURING the
+        # capture: destroying a graph or a stream from the capturing thread invalidates it
+        # (cudaErrorStreamCaptureInvalidated; this torch no longer runs gc.collect() in torch.cuda.graph.__enter__).
+        import gc
         g = torch.cuda.CUDAGraph()
         torch.cuda.synchronize()
+        gc.collect()
+        gc_was_on = gc.isenabled()
+        gc.disable()
         n0 = _lib.launch_count()
-        with torch.cuda.graph(g):
-            for _ in range(repeat):
-                self.run_steps(plan, lookup, mask)
+        try:
+            with torch.cuda.graph(g):
+                for _ in range(repeat):
+                    self.run_steps(plan, lookup, mask, tail_pools=tail_pools)
+        finally:
+            if gc_was_on:
+                gc.enable()
         g.fsb_kernels = _lib.launch_count() - n0  # libfsb200 kernels one replay launches
         return g
 
@@ -611,22 +662,26 @@ class SelectiveUpdateBlock:
                 plan.iter_graph = None
                 plan.loop_graphs = {}
                 plan.iter_calls = 0
+            # prologue: the first iteration's pooled inputs; every iteration then pools for its successor (tail_pools)
+            tp = self.tail_pools
+            if tp:
+                self.run_steps(plan, only_tag="pool_head")
             if self.use_graph and self.loop_graph and plan.iter_calls > 0:
                 # the WHOLE loop as one graph (iters x 30-odd kernel nodes): programmatic dependent launch keeps
                 # overlapping kernel tails across iteration boundaries and the host launches once per pair batch
                 g = plan.loop_graphs.get(iters)
                 if g is None:
-                    g = plan.loop_graphs[iters] = self._capture(plan, True, mask_every_iter, iters)
+                    g = plan.loop_graphs[iters] = self._capture(plan, True, mask_every_iter, iters, tail_pools=tp)
                 self._replay(g)
                 plan.iter_calls += iters
             else:
                 for _ in range(iters):
                     plan.iter_calls += 1
                     if not self.use_graph or plan.iter_calls == 1:
-                        self.run_steps(plan, True, mask_every_iter)
+                        self.run_steps(plan, True, mask_every_iter, tail_pools=tp)
                         continue
                     if plan.iter_graph is None:
-                        plan.iter_graph = self._capture(plan, True, mask_every_iter)
+                        plan.iter_graph = self._capture(plan, True, mask_every_iter, tail_pools=tp)
                     self._replay(plan.iter_graph)
             if not mask_every_iter:
                 self.run_steps(plan, only_mask=True)
