@@ -63,7 +63,7 @@ def config_block(name, pairs, world):
     """The `config` object of the JSON line -- identical for the b200 and the reference arm."""
     c = CONFIGS[name]
     return {"workload": c["workload"], "name": name, "pairs_per_gpu_per_step": pairs, "iters": c["iters"],
-            "l2": "inputs+outputs of a step (per pair: 224 MB filtered volume, 256 MB cost volume, 335 MB geo pyramid) "
+            "l2": "inputs+outputs of a step (per pair: 112 MB fp16 filtered volume, 256 MB cost volume, 335 MB geo pyramid) "
                   "exceed the 126 MB L2; per-kernel timings flush L2 with a 512 MiB write before each launch",
             "parallelism": "pairs sharded over the GPUs, no collective on the path",
             "update_block": "tcgen05 implicit-GEMM convolutions with fused gate epilogues (csrc/conv.cu), one CUDA graph per iteration"}
@@ -89,6 +89,8 @@ class CpuReference:
                                                          volume_dim=c["Cg"])
         self.x = [synthetic.hot_path_inputs(1, p["C"], p["H"], p["W"], c["D"], c["Cp"], c["Cg"], seed=0)
                   for p in c["passes"]]
+        for x in self.x:   # fp16-representable values, as the model's autocast region produces them
+            x["volume"] = x["volume"].half().float()
         from oracle import refmodel
         if refmodel.available():
             self.kind = "reference"
@@ -234,7 +236,7 @@ def algorithmic_bytes(c):
     return {
         "volume_gwc_concat": px * ((2 * C + 2 * Cp) * 4 + (G + 2 * Cp) * D * 4),
         "corr_pyramid": 8 * px * C + 4 * px * sum(W >> l for l in range(L)),
-        "geo_pyramid": 4 * px * Cg * (D + sum(D >> l for l in range(L))),
+        "geo_pyramid": px * Cg * (c.get("vol_bytes", 4) * D + 4 * sum(D >> l for l in range(L))),
         # the fused lookup writes 16-bit NHWC rows of Cpad channels instead of fp32 NCHW
         "geo_lookup": px * (4 + L * (Cg + 1) * (K + 1) * 4 + cpad * 2),
         "geo_lookup_fp32_nchw": px * (4 + L * (Cg + 1) * (K + 1) * 4 + L * K * (Cg + 1) * 4),
@@ -320,6 +322,11 @@ def run_b200(args):
     # micro-batch of the rank's range: the timing does not depend on the values)
     xs = [synthetic.hot_path_inputs(pairs, c["C"], c["H"], c["W"], c["D"], c["Cp"], c["Cg"], seed=rank + 17 * i)
           for i, c in enumerate(passes)]
+    # the filtered cost volume leaves the reference's autocast region in fp16 and only becomes fp32 through the caller's
+    # `.float()` (core/foundation_stereo.py:213-229): it is handed over (and uploaded) as fp16 and kernel 2b reads it as
+    # such (fsb_geo_pyramid_in); the CPU arm gets the same values through `.float()`
+    for x in xs:
+        x["volume"] = x["volume"].half()
     hosts = [{k: ([pin(t) for t in v] if isinstance(v, list) else pin(v)) for k, v in x.items()} for x in xs]
     del xs
     devs = [{k: ([t.to(device, non_blocking=True) for t in v] if isinstance(v, list) else v.to(device, non_blocking=True))
@@ -485,7 +492,7 @@ def run_b200(args):
             kern_ms["softmax_disparity_regression"] = time_kernel(torch, lambda: ops.disparity_regression(cls_logits, True), 20, flush)
             kern_ms["softmax_context_upsample"] = time_kernel(torch, lambda: ops.context_upsample(dev["disp"], spx_logits, True, 4.0), 20, flush)
             per_step.update(corr_pyramid_fp32_cuda_cores=0, softmax_disparity_regression=0, softmax_context_upsample=0)
-        alg = algorithmic_bytes(c)
+        alg = algorithmic_bytes(dict(c, vol_bytes=dev["volume"].element_size()))
         alg["corr_pyramid_fp32_cuda_cores"] = alg["corr_pyramid"]
         px_ = c["B"] * c["H"] * c["W"]
         alg["corr_pyramid_band"] = 8 * px_ * c["C"] + 4 * px_ * sum(bw0 >> l for l in range(L))

@@ -537,3 +537,16 @@ def test_banded_correlation_rejects_unsupported(fsb):
     f3 = torch.randn(1, 32, 2, 62, device="cuda")
     with pytest.raises(fsb.FsbError):   # W % 4 != 0: no TMA-fed path
         ops.corr_pyramid_band(f3, f3, 2, FSB_PREC_TF32X3, 16, 4)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+def test_geo_pyramid_reads_16bit_volume(fsb, dtype):
+    """fsb_geo_pyramid_in: the filtered volume in its storage type (fp16 out of the reference's autocast region,
+    core/foundation_stereo.py:213-229) gives bit-identical levels to converting it to fp32 first."""
+    from foundationstereo_b200 import ops
+    for Cg, D, H, W, L in [(28, 26, 7, 45, 2), (12, 17, 5, 33, 3)]:
+        vol = torch.randn(2, Cg, D, H, W, device="cuda").to(dtype)
+        a = ops.geo_pyramid(vol, L)
+        b = ops.geo_pyramid(vol.float(), L)
+        for x, y in zip(a, b):
+            assert x.dtype == torch.float32 and torch.equal(x, y)
