@@ -90,6 +90,8 @@ _PROTOS = {
     "fsb_nhwc_to_nchw": (c_int, [c_void_p] * 2 + [c_int] * 4 + [c_void_p]),
     "fsb_pool2x_nhwc": (c_int, [c_void_p] * 2 + [c_int] * 5 + [c_void_p]),
     "fsb_resize_nhwc": (c_int, [c_void_p] * 2 + [c_int] * 7 + [c_void_p]),
+    "fsb_pool2x_nhwc16": (c_int, [c_void_p] * 2 + [c_int] * 5 + [c_void_p]),
+    "fsb_resize_nhwc16": (c_int, [c_void_p] * 2 + [c_int] * 7 + [c_void_p]),
     "fsb_conv7x7_c1": (c_int, [c_void_p] * 4 + [c_int] * 2 + [c_void_p] + [c_int] * 6 + [c_void_p]),
     "fsb_dwconv7x7_nhwc": (c_int, [c_void_p] * 4 + [c_int] * 5 + [c_void_p]),
     "fsb_edgenext_mlp": (c_int, [c_void_p] * 8 + [ctypes.c_longlong] + [c_int] * 3 + [c_void_p]),

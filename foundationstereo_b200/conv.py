@@ -150,16 +150,26 @@ def nhwc_to_nchw(src: Tensor, dst: Tensor) -> None:
     check(lib().fsb_nhwc_to_nchw(src.data_ptr(), dst.data_ptr(), B, C, H, W, _stream()))
 
 
-def pool2x(src32: Tensor, dst16: Tensor) -> None:
-    B, H, W, C = src32.shape
+def pool2x(src: Tensor, dst16: Tensor) -> None:
+    """pool2x (core/update.py:72-73) of an NHWC tensor; ``src`` fp32 or the 16-bit type of ``dst16``."""
+    B, H, W, C = src.shape
     assert dst16.shape == (B, (H + 1) // 2, (W + 1) // 2, C)
-    check(lib().fsb_pool2x_nhwc(src32.data_ptr(), dst16.data_ptr(), B, C, H, W, _DT[dst16.dtype], _stream()))
+    if src.dtype == torch.float32:
+        check(lib().fsb_pool2x_nhwc(src.data_ptr(), dst16.data_ptr(), B, C, H, W, _DT[dst16.dtype], _stream()))
+    else:
+        assert src.dtype == dst16.dtype
+        check(lib().fsb_pool2x_nhwc16(src.data_ptr(), dst16.data_ptr(), B, C, H, W, _DT[dst16.dtype], _stream()))
 
 
-def resize(src32: Tensor, dst16: Tensor) -> None:
-    B, Hs, Ws, C = src32.shape
+def resize(src: Tensor, dst16: Tensor) -> None:
+    """interp (core/update.py:78-80) of an NHWC tensor; ``src`` fp32 or the 16-bit type of ``dst16``."""
+    B, Hs, Ws, C = src.shape
     _, Hd, Wd, _ = dst16.shape
-    check(lib().fsb_resize_nhwc(src32.data_ptr(), dst16.data_ptr(), B, C, Hs, Ws, Hd, Wd, _DT[dst16.dtype], _stream()))
+    if src.dtype == torch.float32:
+        check(lib().fsb_resize_nhwc(src.data_ptr(), dst16.data_ptr(), B, C, Hs, Ws, Hd, Wd, _DT[dst16.dtype], _stream()))
+    else:
+        assert src.dtype == dst16.dtype
+        check(lib().fsb_resize_nhwc16(src.data_ptr(), dst16.data_ptr(), B, C, Hs, Ws, Hd, Wd, _DT[dst16.dtype], _stream()))
 
 
 def conv7x7_c1(disp: Tensor, weight: Tensor, bias: Tensor, out: Tensor, cout: int, disp_out: Optional[Tensor],

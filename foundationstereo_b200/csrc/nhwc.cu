@@ -72,6 +72,28 @@ __device__ __forceinline__ void store_vec(T* p, const float (&a)[V]) {
     Quad<T>::store(p, a[0], a[1], a[2], a[3]);
   }
 }
+template <typename S> __device__ __forceinline__ float2 unpack2s(uint32_t v);
+template <> __device__ __forceinline__ float2 unpack2s<__half>(uint32_t v) { return __half22float2(*reinterpret_cast<const __half2*>(&v)); }
+template <> __device__ __forceinline__ float2 unpack2s<__nv_bfloat16>(uint32_t v) {
+  return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&v));
+}
+// 16-bit source: V = 8 -> one 16-byte load, V = 4 -> one 8-byte load
+template <int V, typename S>
+__device__ __forceinline__ void load_vec(const S* p, float (&a)[V]) {
+  uint32_t w[V / 2];
+  if constexpr (V == 8) {
+    const uint4 t = __ldg(reinterpret_cast<const uint4*>(p));
+    w[0] = t.x; w[1] = t.y; w[2] = t.z; w[3] = t.w;
+  } else {
+    const uint2 t = __ldg(reinterpret_cast<const uint2*>(p));
+    w[0] = t.x; w[1] = t.y;
+  }
+#pragma unroll
+  for (int q = 0; q < V / 2; ++q) {
+    const float2 f = unpack2s<S>(w[q]);
+    a[2 * q] = f.x; a[2 * q + 1] = f.y;
+  }
+}
 template <int V>
 __device__ __forceinline__ void load_vec(const float* p, float (&a)[V]) {
 #pragma unroll
@@ -81,9 +103,9 @@ __device__ __forceinline__ void load_vec(const float* p, float (&a)[V]) {
   }
 }
 
-template <typename T, int V>
+template <typename T, int V, typename S = float>
 __global__ void __launch_bounds__(256)
-pool2x_kernel(const float* __restrict__ src, T* __restrict__ dst, int CV, int H, int W, int Ho, int Wo,
+pool2x_kernel(const S* __restrict__ src, T* __restrict__ dst, int CV, int H, int W, int Ho, int Wo,
               size_t total) {
   pdl_launch_dependents();  // the next kernel may start its prologue
   pdl_wait();               // inputs written by the previous kernel are complete and visible
@@ -95,7 +117,7 @@ pool2x_kernel(const float* __restrict__ src, T* __restrict__ dst, int CV, int H,
   r /= Wo;
   const int yo = (int)(r % Ho);
   const int b = (int)(r / Ho);
-  const float* s = src + ((size_t)b * H * W * CV + cv) * V;
+  const S* s = src + ((size_t)b * H * W * CV + cv) * V;
   float a[V];
 #pragma unroll
   for (int j = 0; j < V; ++j) a[j] = 0.f;
@@ -119,9 +141,9 @@ pool2x_kernel(const float* __restrict__ src, T* __restrict__ dst, int CV, int H,
   store_vec<T, V>(dst + i * V, a);
 }
 
-template <typename T, int V>
+template <typename T, int V, typename S = float>
 __global__ void __launch_bounds__(256)
-resize_kernel(const float* __restrict__ src, T* __restrict__ dst, int CV, int Hs, int Ws, int Hd, int Wd,
+resize_kernel(const S* __restrict__ src, T* __restrict__ dst, int CV, int Hs, int Ws, int Hd, int Wd,
               float sy, float sx, size_t total) {
   pdl_launch_dependents();  // the next kernel may start its prologue
   pdl_wait();               // inputs written by the previous kernel are complete and visible
@@ -138,7 +160,7 @@ resize_kernel(const float* __restrict__ src, T* __restrict__ dst, int CV, int Hs
   const int y0 = min((int)fy, Hs - 1), x0 = min((int)fx, Ws - 1);
   const int y1 = min(y0 + 1, Hs - 1), x1 = min(x0 + 1, Ws - 1);
   const float ly = fy - (float)y0, lx = fx - (float)x0;
-  const float* s = src + ((size_t)b * Hs * Ws * CV + cv) * V;
+  const S* s = src + ((size_t)b * Hs * Ws * CV + cv) * V;
   float v00[V], v01[V], v10[V], v11[V], o[V];
   load_vec<V>(s + ((size_t)y0 * Ws + x0) * CV * V, v00);
   load_vec<V>(s + ((size_t)y0 * Ws + x1) * CV * V, v01);
@@ -544,6 +566,41 @@ extern "C" int fsb_resize_nhwc(const float* src, void* dst, int B, int C, int Hs
     FSB_DISPATCH16(dtype, (launch_kernel(resize_kernel<T, 4>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, src, (T*)dst, C / 4, Hs, Ws, Hd, Wd, sy, sx, total)));
   }
   FSB_CHECK_LAUNCH("fsb_resize_nhwc");
+  return FSB_OK;
+}
+
+// pool2x / interp with the source in the 16-bit storage type (the hidden state as the reference's autocast region holds
+// it): half the bytes of the fp32 forms above
+extern "C" int fsb_pool2x_nhwc16(const void* src, void* dst, int B, int C, int H, int W, int dtype, fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_pool2x_nhwc16");
+  using namespace fsb;
+  FSB_REQUIRE(src && dst, FSB_ERR_ARG, "fsb_pool2x_nhwc16: NULL pointer");
+  FSB_REQUIRE(B > 0 && C > 0 && H > 0 && W > 0 && is16(dtype), FSB_ERR_ARG, "fsb_pool2x_nhwc16: bad size or dtype");
+  FSB_REQUIRE(C % 8 == 0 && aligned16(src) && aligned16(dst), FSB_ERR_SHAPE,
+              "fsb_pool2x_nhwc16: C=%d must be a multiple of 8, pointers 16-byte aligned", C);
+  const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
+  const size_t total = (size_t)B * Ho * Wo * (C / 8);
+  const unsigned blocks = (unsigned)((total + 255) / 256);
+  FSB_DISPATCH16(dtype, (launch_kernel(pool2x_kernel<T, 8, T>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, (const T*)src, (T*)dst, C / 8, H, W, Ho, Wo, total)));
+  FSB_CHECK_LAUNCH("fsb_pool2x_nhwc16");
+  return FSB_OK;
+}
+
+extern "C" int fsb_resize_nhwc16(const void* src, void* dst, int B, int C, int Hs, int Ws, int Hd, int Wd, int dtype,
+                                 fsb_stream_t stream) {
+  fsb::NvtxRange nvtx_range__("fsb_resize_nhwc16");
+  using namespace fsb;
+  FSB_REQUIRE(src && dst, FSB_ERR_ARG, "fsb_resize_nhwc16: NULL pointer");
+  FSB_REQUIRE(B > 0 && C > 0 && Hs > 0 && Ws > 0 && Hd > 0 && Wd > 0 && is16(dtype), FSB_ERR_ARG,
+              "fsb_resize_nhwc16: bad size or dtype");
+  FSB_REQUIRE(C % 8 == 0 && aligned16(src) && aligned16(dst), FSB_ERR_SHAPE,
+              "fsb_resize_nhwc16: C=%d must be a multiple of 8, pointers 16-byte aligned", C);
+  const float sy = Hd > 1 ? (float)(Hs - 1) / (float)(Hd - 1) : 0.f;
+  const float sx = Wd > 1 ? (float)(Ws - 1) / (float)(Wd - 1) : 0.f;
+  const size_t total = (size_t)B * Hd * Wd * (C / 8);
+  const unsigned blocks = (unsigned)((total + 255) / 256);
+  FSB_DISPATCH16(dtype, (launch_kernel(resize_kernel<T, 8, T>, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, (const T*)src, (T*)dst, C / 8, Hs, Ws, Hd, Wd, sy, sx, total)));
+  FSB_CHECK_LAUNCH("fsb_resize_nhwc16");
   return FSB_OK;
 }
 

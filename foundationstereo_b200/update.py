@@ -110,6 +110,7 @@ class SelectiveUpdateBlock:
         # iteration.  Measured neutral on the B200 (90.5 / 91.4 with, 91.8 / 91.6 pairs/s without: the extra cross-lane
         # fork / join costs what the 45 us of pooling save), so it is off by default; FSB_TAIL_POOLS=1 switches it on.
         self.tail_pools = _os.environ.get("FSB_TAIL_POOLS", "0") == "1"
+        self.pool_fp32 = _os.environ.get("FSB_POOL_FP32", "0") == "1"
         self.pdl_cross = _os.environ.get("FSB_PDL_CROSS", "0") == "1"  # programmatic edges across lanes too (hung: see run_steps)
         self.two_lanes = _os.environ.get("FSB_TWO_LANES", "1") != "0"  # side stream for encoder / mask head
         self.copy_outputs = copy_outputs  # forward returns fresh tensors instead of views of the plan's buffers
@@ -281,6 +282,12 @@ class SelectiveUpdateBlock:
                 best, best_t = bn, t
         return best
 
+    def _hsrc(self, plan: _Plan) -> List[Tensor]:
+        """What pool2x / interp read: the 16-bit copy of the hidden state (the reference's autocast region pools and
+        interpolates fp16 tensors, core/foundation_stereo.py:239-240 -> core/update.py:143-152; half the bytes of the fp32
+        master copy) unless FSB_POOL_FP32=1."""
+        return plan.h32 if self.pool_fp32 else plan.h16
+
     def _gru(self, plan: _Plan, g: str, lvl: int, xs: Sequence[Tensor]) -> None:
         """SelectiveConvGRU.forward (core/update.py:112-119) on level `lvl`: 4 launches."""
         hd = self.hidden
@@ -347,25 +354,25 @@ class SelectiveUpdateBlock:
                 # gru16: x = [inp[2], pool2x(net[1])]                               (core/update.py:143)
                 p1 = new(2, hd)
                 plan.tag = "pool_head"
-                add("pool2x(net1)", lambda: C.pool2x(plan.h32[1], p1))
+                add("pool2x(net1)", lambda: C.pool2x(self._hsrc(plan)[1], p1))
                 plan.tag = None
                 self._gru(plan, "gru16", 2, [plan.inp16[2], p1])
                 plan.keep.append(p1)
             # gru08: x = [inp[1], pool2x(net[0]) (, interp(net[2]) with three levels)]  (:145-148)
             p0 = new(1, hd)
             plan.tag = "pool_head"
-            add("pool2x(net0)", lambda: C.pool2x(plan.h32[0], p0))
+            add("pool2x(net0)", lambda: C.pool2x(self._hsrc(plan)[0], p0))
             plan.tag = None
             xs08 = [plan.inp16[1], p0]
             if n == 3:
                 u2 = new(1, hd)
-                add("interp(net2)", lambda: C.resize(plan.h32[2], u2))
+                add("interp(net2)", lambda: C.resize(self._hsrc(plan)[2], u2))
                 xs08.append(u2)
             self._gru(plan, "gru08", 1, xs08)
             add(JOIN, JOIN)
             # gru04: x = [inp[0], motion, interp(net[1])]                           (:150-153)
             u1 = new(0, hd)
-            add("interp(net1)", lambda: C.resize(plan.h32[1], u1))
+            add("interp(net1)", lambda: C.resize(self._hsrc(plan)[1], u1))
             self._gru(plan, "gru04", 0, [plan.inp16[0], motion, u1])
             plan.keep += xs08 + [u1]
         if n >= 2:
@@ -377,8 +384,8 @@ class SelectiveUpdateBlock:
             add(FORK, FORK)
             plan.lane = 1
             if n == 3:
-                add("pool2x(net1)'", lambda: C.pool2x(plan.h32[1], p1))
-            add("pool2x(net0)'", lambda: C.pool2x(plan.h32[0], p0))
+                add("pool2x(net1)'", lambda: C.pool2x(self._hsrc(plan)[1], p1))
+            add("pool2x(net0)'", lambda: C.pool2x(self._hsrc(plan)[0], p0))
             plan.lane = 0
             plan.tag = None
         # mask head (core/update.py:134-139,158) -- side lane; tagged so `refine` can leave it out of the iteration

@@ -249,6 +249,12 @@ int fsb_pool2x_nhwc(const float* src, void* dst, int B, int C, int H, int W, int
 /* interp (core/update.py:78-80): bilinear, align_corners=True, fp32 NHWC (B,Hs,Ws,C) -> 16-bit (B,Hd,Wd,C) */
 int fsb_resize_nhwc(const float* src, void* dst, int B, int C, int Hs, int Ws, int Hd, int Wd, int dtype,
                     fsb_stream_t stream);
+/* The same two with the source in the 16-bit storage type `dtype` (src, dst both (..,C) 16-bit, C % 8 == 0): under the
+ * reference's autocast the hidden state these read IS 16-bit (core/foundation_stereo.py:239-240), and reading it so
+ * halves the bytes.  Results are rounded to `dtype` like the fp32-source forms. */
+int fsb_pool2x_nhwc16(const void* src, void* dst, int B, int C, int H, int W, int dtype, fsb_stream_t stream);
+int fsb_resize_nhwc16(const void* src, void* dst, int B, int C, int Hs, int Ws, int Hd, int Wd, int dtype,
+                      fsb_stream_t stream);
 /* BasicMotionEncoder.convd1 (core/update.py:58,66): 7x7, 1 -> Cout channels, pad 3, + bias, ReLU.
  * disp fp32 (B,1,H,W); weight fp32 (Cout,49); out 16-bit NHWC (B,H,W,ld_out) channels [0,Cout).
  * If disp_out != NULL also writes disp itself as channel disp_ch of disp_out (ld_disp channels/pixel):

@@ -187,6 +187,19 @@ def test_pool_and_resize(fsb, hw):
     C.resize(small, up)
     want_up = F.interpolate(want, (H, W), mode="bilinear", align_corners=True)
     assert rel_err(up.permute(0, 3, 1, 2).float(), want_up) <= 1e-3
+    # 16-bit sources (what the engine reads: the fp16 / bf16 copy of the hidden state) against fp32 PyTorch on the same
+    # rounded values
+    for dt, tol in ((torch.float16, 1e-3), (torch.bfloat16, 8e-3)):
+        x16 = x_nhwc.to(dt)
+        p16 = torch.empty(2, Ho, Wo, 128, dtype=dt, device="cuda")
+        C.pool2x(x16, p16)
+        want16 = F.avg_pool2d(x16.float().permute(0, 3, 1, 2), 3, stride=2, padding=1)
+        assert rel_err(p16.permute(0, 3, 1, 2).float(), want16) <= tol
+        s16 = want16.permute(0, 2, 3, 1).contiguous().to(dt)
+        up16 = torch.empty(2, H, W, 128, dtype=dt, device="cuda")
+        C.resize(s16, up16)
+        want_up16 = F.interpolate(s16.float().permute(0, 3, 1, 2), (H, W), mode="bilinear", align_corners=True)
+        assert rel_err(up16.permute(0, 3, 1, 2).float(), want_up16) <= tol
 
 
 def test_conv7x7_helpers(fsb):
