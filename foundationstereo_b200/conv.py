@@ -210,6 +210,19 @@ def conv3x3_cout1(x: Tensor, weight: Tensor, bias: Tensor, delta: Tensor, disp_a
                                   _stream()))
 
 
+def edgenext_block(x: Tensor, dw_w: Tensor, dw_b: Tensor, w1: Tensor, b1: Tensor, w2: Tensor, b2: Tensor, gamma: Tensor,
+                   out: Tensor) -> None:
+    """out = x + gamma * (GELU(dwconv7x7(x) @ w1^T + b1) @ w2^T + b2): one EdgeNeXt block in one launch (csrc/edgenext.cu)."""
+    B, H, W, C = x.shape
+    F = w1.shape[0]
+    assert x.is_contiguous() and out.is_contiguous() and x.shape == out.shape and x.data_ptr() != out.data_ptr()
+    assert w1.is_contiguous() and w2.is_contiguous() and w1.shape == (F, C) and w2.shape == (C, F)
+    assert x.dtype == w1.dtype == w2.dtype == out.dtype and dw_w.dtype == torch.float32 and dw_w.shape == (C, 49)
+    check(lib().fsb_edgenext_block(x.data_ptr(), dw_w.data_ptr(), dw_b.data_ptr(), w1.data_ptr(), b1.data_ptr(),
+                                   w2.data_ptr(), b2.data_ptr(), gamma.data_ptr(), out.data_ptr(), B, H, W, C, F,
+                                   _DT[x.dtype], _stream()))
+
+
 def axpy(y: Tensor, x: Tensor) -> None:
     assert y.dtype == x.dtype == torch.float32 and y.numel() == x.numel()
     check(lib().fsb_axpy_f32(y.data_ptr(), x.data_ptr(), y.numel(), _stream()))

@@ -96,7 +96,8 @@ class SelectiveUpdateBlock:
     def __init__(self, state_dict: Dict[str, Tensor], device: torch.device | str = "cuda",
                  dtype: torch.dtype = torch.float16, use_graph: bool = True,
                  block_n: Optional[Dict[str, int]] = None, halo: Optional[Sequence[str]] = None,
-                 fused_mlp: bool = True, copy_outputs: bool = False, dot_head4: bool = True):
+                 fused_mlp: bool = True, copy_outputs: bool = False, dot_head4: bool = True,
+                 fused_block: Optional[bool] = None):
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise RuntimeError("SelectiveUpdateBlock runs on CUDA only (no CPU path)")
@@ -115,6 +116,12 @@ class SelectiveUpdateBlock:
         self.two_lanes = _os.environ.get("FSB_TWO_LANES", "1") != "0"  # side stream for encoder / mask head
         self.copy_outputs = copy_outputs  # forward returns fresh tensors instead of views of the plan's buffers
         self.dot_head4 = dot_head4  # False: disp_head.conv.4 as a tensor-core convolution launch + a separate disp += delta
+        # depthwise 7x7 + MLP of a disparity-head block as ONE launch (csrc/edgenext.cu; bit-identical to the two launches).
+        # Measured on the B200: 178 us per block against 82 + 87 us, 92.9 vs 93.4 pairs/s -- the eight depthwise warps that
+        # fit beside the 16 epilogue warps are slower than the stand-alone kernel's 16 (both sit at ~2x their fmaheavy-pipe
+        # floor), and with one X slot they only overlap the last 45 % of the previous tile.  Off by default
+        # (FSB_FUSED_BLOCK=1 / fused_block=True switch it on).
+        self.fused_block = (_os.environ.get("FSB_FUSED_BLOCK", "0") == "1") if fused_block is None else fused_block
         self.fused_mlp = fused_mlp  # False: pwconv1 / pwconv2 of the disparity head as two convolution launches
         self.bn = dict(DEFAULT_BLOCK_N)
         if block_n:
@@ -405,6 +412,16 @@ class SelectiveUpdateBlock:
         t, u = new(0, hd), new(0, 4 * hd)
         self._conv(plan, "disp_head.conv.0", "head0", [plan.h16[0]], [(3, [0])], "head0", _lib.FSB_EPI_RELU, out=y[0])
         for k, i in enumerate((2, 3)):
+            if self.fused_mlp and self.fused_block:
+                # the whole EdgeNeXt block -- depthwise 7x7 -> pwconv1 -> GELU -> pwconv2 -> gamma * . + residual -- in ONE
+                # launch (csrc/edgenext.cu): the depthwise tile is produced in shared memory as the first GEMM's operand
+                def block(k=k, i=i):
+                    C.edgenext_block(y[k], self.f[f"dw{i}.w"], self.f[f"dw{i}.b"], self.f[f"pw1_{i}.w"], self.f[f"pw1_{i}.b"],
+                                     self.f[f"pw2_{i}.w"], self.f[f"pw2_{i}.b"], self.f[f"gamma{i}"], y[k + 1])
+                block.flops = 2.0 * B * H * W * (2 * hd * 4 * hd)
+                add(f"disp_head.conv.{i}.block", block)
+                plan.flops += block.flops
+                continue
             add(f"disp_head.conv.{i}.dwconv",
                 lambda k=k, i=i: C.dwconv7x7(y[k], self.f[f"dw{i}.w"], self.f[f"dw{i}.b"], t))
             if self.fused_mlp:

@@ -280,6 +280,14 @@ int fsb_edgenext_mlp(const void* x, const void* w1, const float* b1, const void*
  *   core/foundation_stereo.py:242 folded into the same launch). */
 int fsb_conv3x3_cout1(const void* x, const float* weight, const float* bias, float* delta, float* disp_accum, int B,
                       int C, int H, int W, int dtype, fsb_stream_t stream);
+/* A WHOLE EdgeNextConvEncoder block (core/submodule.py:565-591, norm=None) in one launch:
+ *     out = x + gamma * (GELU(dwconv7x7(x; dw_w, dw_b) @ w1^T + b1) @ w2^T + b2)
+ * = fsb_dwconv7x7_nhwc followed by fsb_edgenext_mlp (bit-identical to that pair), with the depthwise output tile produced
+ * in shared memory as the A operand of the first GEMM instead of making a round trip through memory.
+ * x, out 16-bit NHWC (B,H,W,C), out != x; dw_w fp32 (C,49); w1 (F,C), w2 (C,F) 16-bit row-major; C = 128, F = 512. */
+int fsb_edgenext_block(const void* x, const float* dw_w, const float* dw_b, const void* w1, const float* b1,
+                       const void* w2, const float* b2, const float* gamma, void* out, int B, int H, int W, int C,
+                       int F, int dtype, fsb_stream_t stream);
 /* y += x (fp32, n elements): the disparity update of core/foundation_stereo.py:242 */
 int fsb_axpy_f32(float* y, const float* x, size_t n, fsb_stream_t stream);
 

@@ -304,3 +304,32 @@ def test_update_block_dot_head4_equals_tensor_core_head4(fsb):
         net, mask, delta = ub([c(t) for t in x["net"]], [c(t) for t in x["inp"]], corr, c(x["disp"]), [c(t) for t in x["att"]])
         outs.append(delta.clone())
     assert rel_err(outs[0].cpu(), outs[1].cpu()) <= 1e-4
+
+
+# ------------------------------------------------------------------ whole EdgeNeXt block in one launch (csrc/edgenext.cu)
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("shape", [(1, 8, 16), (2, 13, 37), (1, 24, 40), (3, 120, 160)])  # one tile, ragged, several tiles per CTA
+def test_edgenext_block_equals_dwconv_plus_mlp(fsb, dtype, shape):
+    """fsb_edgenext_block == fsb_dwconv7x7_nhwc followed by fsb_edgenext_mlp, BIT for bit (same accumulation order in
+    the depthwise part, the same 16-bit operand tile feeds the same MMA sequence), and against fp32 PyTorch."""
+    from foundationstereo_b200 import conv as Cv
+    B, H, W = shape
+    C_, F_ = 128, 512
+    x = _rand(B, H, W, C_, seed=1).to(dtype).cuda()
+    dw_w, dw_b = (_rand(C_, 49, seed=2) / 7).cuda(), (_rand(C_, seed=3) * 0.1).cuda()
+    w1 = (_rand(F_, C_, seed=4) / C_ ** 0.5).to(dtype).cuda()
+    w2 = (_rand(C_, F_, seed=5) / F_ ** 0.5).to(dtype).cuda()
+    b1, b2, gamma = (_rand(F_, seed=6) * 0.1).cuda(), (_rand(C_, seed=7) * 0.1).cuda(), _rand(C_, seed=8).cuda()
+    t = torch.empty_like(x)
+    Cv.dwconv7x7(x, dw_w, dw_b, t)
+    two = torch.empty_like(x)
+    Cv.edgenext_mlp(t, w1, b1, w2, b2, gamma, x, two)
+    one = torch.full_like(x, 7.0)
+    Cv.edgenext_block(x, dw_w, dw_b, w1, b1, w2, b2, gamma, one)
+    torch.cuda.synchronize()
+    assert torch.equal(one, two), float((one.float() - two.float()).abs().max())
+    xt = x.float().permute(0, 3, 1, 2)
+    tt = F.conv2d(xt, dw_w.reshape(C_, 1, 7, 7), dw_b, padding=3, groups=C_).permute(0, 2, 3, 1).to(dtype).float()
+    h = F.gelu(tt @ w1.float().t() + b1).to(dtype).float()
+    want = x.float() + gamma * (h @ w2.float().t() + b2)
+    assert rel_err(one.float().cpu(), want.cpu()) <= 2 * _tol(dtype)
