@@ -15,6 +15,7 @@ B, C, H, W, D, L, r = 1, 128, 120, 160, 104, 2, 4
 B = int(sys.argv[2]) if len(sys.argv) > 2 else B
 x = synthetic.hot_path_inputs(B, C, H, W, D)
 d = {k: v.cuda() for k, v in x.items() if isinstance(v, torch.Tensor)}
+d["volume"] = d["volume"].half()   # as bench.py hands it over: the filtered volume in the reference's autocast dtype
 dx = torch.linspace(-r, r, 2 * r + 1).reshape(1, 1, -1, 1)
 coords = torch.arange(W, dtype=torch.float32, device="cuda").reshape(1, 1, W, 1).repeat(B, H, 1, 1)
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
@@ -29,5 +30,7 @@ for _ in range(reps):
     geo = fsb.Combined_Geo_Encoding_Volume(d["fl"], d["fr"], d["volume"], num_levels=L, dx=dx)
     out = geo(d["disp"], coords)
     geo.lookup_nhwc16(d["disp"], coords, out16)
+    band = fsb.Combined_Geo_Encoding_Volume(d["fl"], d["fr"], d["volume"], num_levels=L, dx=dx, corr_band=D)
+    band.lookup_nhwc16(d["disp"], coords, out16)
 torch.cuda.synchronize()
 print("ok", out.shape, fsb.launch_count())
