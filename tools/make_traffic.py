@@ -37,7 +37,12 @@ names = {"volume_kernel": "volume_gwc_concat", "corr_umma": "corr_pyramid", "cor
 for n, b, _ in k123:
     for k, v in names.items():
         if k in n:
-            t[v] = b  # last launch of each kernel
+            if v == "corr_pyramid" and v in t:
+                t["corr_pyramid_band"] = b  # tools/prof_kernels.py launches the full form first, then the band form
+            elif v == "geo_lookup" and v in t:
+                t["geo_lookup_band"] = b
+            elif v not in t:
+                t[v] = b  # first launch of each kernel
 t["note"] = "bytes per launch at 8 pairs (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum); conv_umma_kernel = " \
             "sum over the tensor-core launches of one update step"
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
