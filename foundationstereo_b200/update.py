@@ -118,8 +118,8 @@ class SelectiveUpdateBlock:
         self.dot_head4 = dot_head4  # False: disp_head.conv.4 as a tensor-core convolution launch + a separate disp += delta
         # depthwise 7x7 + MLP of a disparity-head block as ONE launch (csrc/edgenext.cu; bit-identical to the two launches).
         # Measured on the B200: 178 us per block against 82 + 87 us, 92.9 vs 93.4 pairs/s -- the eight depthwise warps that
-        # fit beside the 16 epilogue warps are slower than the stand-alone kernel's 16 (both sit at ~2x their fmaheavy-pipe
-        # floor), and with one X slot they only overlap the last 45 % of the previous tile.  Off by default
+        # fit beside the 16 epilogue warps are slower than the stand-alone kernel's 16 (the depthwise part is
+        # latency-bound at either occupancy), and with one X slot they only overlap the last 45 % of the previous tile.  Off by default
         # (FSB_FUSED_BLOCK=1 / fused_block=True switch it on).
         self.fused_block = (_os.environ.get("FSB_FUSED_BLOCK", "0") == "1") if fused_block is None else fused_block
         self.fused_mlp = fused_mlp  # False: pwconv1 / pwconv2 of the disparity head as two convolution launches
