@@ -97,6 +97,8 @@ _PROTOS = {
     "fsb_edgenext_mlp": (c_int, [c_void_p] * 8 + [ctypes.c_longlong] + [c_int] * 3 + [c_void_p]),
     "fsb_conv3x3_cout1": (c_int, [c_void_p] * 5 + [c_int] * 5 + [c_void_p]),
     "fsb_edgenext_block": (c_int, [c_void_p] * 9 + [c_int] * 6 + [c_void_p]),
+    "fsb_edgenext_block_noalloc": (c_int, [c_void_p] * 9 + [c_int] * 6 + [c_void_p]),
+    "fsb_noalloc_max_pixels": (c_size_t, []),
     "fsb_axpy_f32": (c_int, [c_void_p, c_void_p, c_size_t, c_void_p]),
     "fsb_disparity_regression": (c_int, [c_void_p] * 2 + [c_int] * 6 + [c_void_p]),
     "fsb_context_upsample": (c_int, [c_void_p] * 3 + [c_int] * 4 + [c_float, c_int, c_void_p]),

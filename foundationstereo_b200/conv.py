@@ -223,6 +223,21 @@ def edgenext_block(x: Tensor, dw_w: Tensor, dw_b: Tensor, w1: Tensor, b1: Tensor
                                    _DT[x.dtype], _stream()))
 
 
+def edgenext_block_noalloc(x: Tensor, dw_w: Tensor, dw_b: Tensor, w1: Tensor, b1: Tensor, w2: Tensor, b2: Tensor,
+                           gamma: Tensor, out: Tensor) -> None:
+    """``edgenext_block`` for callers that cannot allocate: the depthwise output lives in a static device array of the
+    library (csrc/noalloc.cu; at most ``lib().fsb_noalloc_max_pixels()`` pixels per call, calls that overlap on the GPU
+    race on it).  No counterpart in the reference."""
+    B, H, W, C = x.shape
+    F = w1.shape[0]
+    assert x.is_contiguous() and out.is_contiguous() and x.shape == out.shape and x.data_ptr() != out.data_ptr()
+    assert w1.is_contiguous() and w2.is_contiguous() and w1.shape == (F, C) and w2.shape == (C, F)
+    assert x.dtype == w1.dtype == w2.dtype == out.dtype and dw_w.dtype == torch.float32 and dw_w.shape == (C, 49)
+    check(lib().fsb_edgenext_block_noalloc(x.data_ptr(), dw_w.data_ptr(), dw_b.data_ptr(), w1.data_ptr(), b1.data_ptr(),
+                                           w2.data_ptr(), b2.data_ptr(), gamma.data_ptr(), out.data_ptr(), B, H, W, C, F,
+                                           _DT[x.dtype], _stream()))
+
+
 def axpy(y: Tensor, x: Tensor) -> None:
     assert y.dtype == x.dtype == torch.float32 and y.numel() == x.numel()
     check(lib().fsb_axpy_f32(y.data_ptr(), x.data_ptr(), y.numel(), _stream()))

@@ -288,6 +288,19 @@ int fsb_conv3x3_cout1(const void* x, const float* weight, const float* bias, flo
 int fsb_edgenext_block(const void* x, const float* dw_w, const float* dw_b, const void* w1, const float* b1,
                        const void* w2, const float* b2, const float* gamma, void* out, int B, int H, int W, int C,
                        int F, int dtype, fsb_stream_t stream);
+/* fsb_edgenext_block for callers that cannot allocate device memory (CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and result as fsb_edgenext_block, computed as fsb_dwconv7x7_nhwc -> fsb_edgenext_mlp with the
+ * depthwise output held in a file-scope `static __device__` array of the library (csrc/noalloc.cu) instead of a
+ * caller-owned buffer; nothing is allocated or freed by the call.
+ *   - limit: C = 128 and B*H*W <= fsb_noalloc_max_pixels() (32768 pixels = 8 MiB of 16-bit scratch, held by every GPU
+ *     that loads the library until the process exits); larger calls return FSB_ERR_SHAPE with a message naming the limit;
+ *   - all calls share the one array (it keeps the last call's contents; nothing in it has to start at zero): calls on
+ *     one stream are ordered, calls that OVERLAP on the GPU (two streams / threads on one device) race on it.     */
+int fsb_edgenext_block_noalloc(const void* x, const float* dw_w, const float* dw_b, const void* w1, const float* b1,
+                               const void* w2, const float* b2, const float* gamma, void* out, int B, int H, int W,
+                               int C, int F, int dtype, fsb_stream_t stream);
+size_t fsb_noalloc_max_pixels(void);
 /* y += x (fp32, n elements): the disparity update of core/foundation_stereo.py:242 */
 int fsb_axpy_f32(float* y, const float* x, size_t n, fsb_stream_t stream);
 
