@@ -61,8 +61,10 @@ class _Plan:
         self.names: List[str] = []
         self.lanes: List[int] = []
         self.tags: List[Optional[str]] = []
+        self.groups: List[Optional[str]] = []  # "enc" | "coarse" | "fine" | "head": what `run_loop_pipelined` reorders
         self.lane = 0
         self.tag: Optional[str] = None
+        self.group: Optional[str] = None
         self.keep: list = []
         self.accum = False
         self.graph: Optional[torch.cuda.CUDAGraph] = None
@@ -80,6 +82,7 @@ class _Plan:
         self.names.append(name)
         self.lanes.append(self.lane)
         self.tags.append(self.tag)
+        self.groups.append(self.group)
 
 
 class SelectiveUpdateBlock:
@@ -112,6 +115,11 @@ class SelectiveUpdateBlock:
         # fork / join costs what the 45 us of pooling save), so it is off by default; FSB_TAIL_POOLS=1 switches it on.
         self.tail_pools = _os.environ.get("FSB_TAIL_POOLS", "0") == "1"
         self.pool_fp32 = _os.environ.get("FSB_POOL_FP32", "0") == "1"
+        # refine(): coarse GRU levels of iteration i+1 under the disparity head of iteration i (run_loop_pipelined).
+        # Bit-identical results; B200, 8 pairs: 93.0 -> 93.9 pairs/s (2640 -> 2614 us per iteration) -- the step runs at
+        # the 1000 W power cap, and the SM clock under load dropped from 1615 to 1555 MHz with the busier schedule, which
+        # is why better overlap buys only 1 %.  FSB_PIPELINE=0 restores the iteration-by-iteration order.
+        self.pipelined = _os.environ.get("FSB_PIPELINE", "1") != "0"
         self.pdl_cross = _os.environ.get("FSB_PDL_CROSS", "0") == "1"  # programmatic edges across lanes too (hung: see run_steps)
         self.two_lanes = _os.environ.get("FSB_TWO_LANES", "1") != "0"  # side stream for encoder / mask head
         self.copy_outputs = copy_outputs  # forward returns fresh tensors instead of views of the plan's buffers
@@ -348,6 +356,7 @@ class SelectiveUpdateBlock:
             # encoder (core/update.py:62-70): motion = [conv(cat[cor, d]) (127) | disp (1)]  -- side lane
             add(FORK, FORK)
             plan.lane = 1
+            plan.group = "enc"
             c1, c2, d1, d2, motion = new(0, 256), new(0, 256), new(0, 64), new(0, 64), new(0, hd)
             self._conv(plan, "encoder.convc1", "convc1", [plan.corr16], [(1, [0])], "convc1", _lib.FSB_EPI_RELU, out=c1)
             self._conv(plan, "encoder.convc2", "convc2", [c1], [(3, [0])], "convc2", _lib.FSB_EPI_RELU, out=c2)
@@ -356,6 +365,7 @@ class SelectiveUpdateBlock:
             self._conv(plan, "encoder.convd2", "convd2", [d1], [(3, [0])], "convd2", _lib.FSB_EPI_RELU, out=d2)
             self._conv(plan, "encoder.conv", "enc_conv", [c2, d2], [(3, [0, 1])], "enc_conv", _lib.FSB_EPI_RELU, out=motion)
             plan.lane = 0
+            plan.group = "coarse"
             plan.keep += [c1, c2, d1, d2, motion]
             if n == 3:
                 # gru16: x = [inp[2], pool2x(net[1])]                               (core/update.py:143)
@@ -376,11 +386,14 @@ class SelectiveUpdateBlock:
                 add("interp(net2)", lambda: C.resize(self._hsrc(plan)[2], u2))
                 xs08.append(u2)
             self._gru(plan, "gru08", 1, xs08)
+            plan.group = None
             add(JOIN, JOIN)
+            plan.group = "fine"
             # gru04: x = [inp[0], motion, interp(net[1])]                           (:150-153)
             u1 = new(0, hd)
             add("interp(net1)", lambda: C.resize(self._hsrc(plan)[1], u1))
             self._gru(plan, "gru04", 0, [plan.inp16[0], motion, u1])
+            plan.group = None
             plan.keep += xs08 + [u1]
         if n >= 2:
             # `refine` (which owns the loop) pools the NEXT iteration's inputs here, on the side lane under the disparity
@@ -408,6 +421,7 @@ class SelectiveUpdateBlock:
         plan.lane = 0
         plan.tag = None
         # disp head (core/update.py:20-32) with EdgeNextConvEncoder (core/submodule.py:565-591)
+        plan.group = "head"
         y = [new(0, hd) for _ in range(3)]
         t, u = new(0, hd), new(0, 4 * hd)
         self._conv(plan, "disp_head.conv.0", "head0", [plan.h16[0]], [(3, [0])], "head0", _lib.FSB_EPI_RELU, out=y[0])
@@ -445,6 +459,7 @@ class SelectiveUpdateBlock:
         else:
             self._conv(plan, "disp_head.conv.4", "head4", [y[2]], [(3, [0])], "head4", _lib.FSB_EPI_BIAS,
                        out_f32=plan.delta)
+        plan.group = None
         add(JOIN, JOIN)
         plan.keep += [y, t, u, m0]
         return plan
@@ -590,8 +605,65 @@ class SelectiveUpdateBlock:
         if lookup and not plan.accum:
             C.axpy(plan.disp, plan.delta)
 
+    def run_loop_pipelined(self, plan: _Plan, iters: int) -> None:
+        """``iters`` whole loop iterations (lookup -> update block -> disp += delta, no mask head) with the coarse GRU
+        levels of iteration i+1 issued UNDER the disparity head of iteration i:
+
+            side lane:                 coarse(i+1) = pool2x, gru16, pool2x, interp, gru08
+            main lane:  ... fine(i) -> head(i) -> lookup(i+1) -> encoder(i+1) -> [join] -> fine(i+1) = interp, gru04 -> ...
+
+        gru16 / gru08 of the next iteration depend on the hidden states only (core/update.py:143-148), which are final
+        once gru04 has run; the disparity head (:155), the lookup (core/foundation_stereo.py:238) and the motion encoder
+        (core/update.py:149) neither read what the coarse levels write nor write what they read.  The same kernels on
+        the same operands as `run_steps` -> bit-identical results; only the stream order differs: the head's
+        latency-bound launches (depthwise 7x7, GELU MLP) share the GPU with the coarse levels' small grids instead of
+        each running alone."""
+        assert self.n_layers >= 2
+        main = torch.cuda.current_stream()
+        plan.accum = self.dot_head4
+        lib = _lib.lib()
+        fence = [False, False]
+
+        def launch(fn, lane):
+            if fence[lane] and not self.pdl_cross:   # full completion edge across lanes (see run_steps)
+                fence[lane] = False
+                old = lib.fsb_set_pdl(0)
+                try:
+                    fn()
+                finally:
+                    lib.fsb_set_pdl(old)
+            else:
+                fn()
+
+        def group(name, lane):
+            for fn, g, tag in zip(plan.steps, plan.groups, plan.tags):
+                if g != name or fn is FORK or fn is JOIN or tag in ("mask", "pool_tail"):
+                    continue
+                if lane == 0:
+                    launch(fn, 0)
+                else:
+                    with torch.cuda.stream(plan.side):
+                        launch(fn, 1)
+
+        for i in range(iters):
+            plan.side.wait_stream(main)          # fork: the hidden states of iteration i-1 are final
+            fence[1] = True
+            group("coarse", 1)
+            if i > 0:
+                group("head", 0)                 # disparity head of iteration i-1, disp += delta in its last launch
+                if not plan.accum:
+                    C.axpy(plan.disp, plan.delta)
+            plan.lookup()
+            group("enc", 0)
+            main.wait_stream(plan.side)          # join
+            fence[0] = True
+            group("fine", 0)
+        group("head", 0)
+        if not plan.accum:
+            C.axpy(plan.disp, plan.delta)
+
     def _capture(self, plan: _Plan, lookup: bool, mask: bool = True, repeat: int = 1,
-                 tail_pools: bool = False) -> torch.cuda.CUDAGraph:
+                 tail_pools: bool = False, pipelined: bool = False) -> torch.cuda.CUDAGraph:
         # Dead Python cycles that hold CUDA graphs / streams of an earlier engine must not be collected DURING the
         # capture: destroying a graph or a stream from the capturing thread invalidates it
         # (cudaErrorStreamCaptureInvalidated; this torch no longer runs gc.collect() in torch.cuda.graph.__enter__).
@@ -604,8 +676,11 @@ class SelectiveUpdateBlock:
         n0 = _lib.launch_count()
         try:
             with torch.cuda.graph(g):
-                for _ in range(repeat):
-                    self.run_steps(plan, lookup, mask, tail_pools=tail_pools)
+                if pipelined:
+                    self.run_loop_pipelined(plan, repeat)
+                else:
+                    for _ in range(repeat):
+                        self.run_steps(plan, lookup, mask, tail_pools=tail_pools)
         finally:
             if gc_was_on:
                 gc.enable()
@@ -695,7 +770,9 @@ class SelectiveUpdateBlock:
                 # overlapping kernel tails across iteration boundaries and the host launches once per pair batch
                 g = plan.loop_graphs.get(iters)
                 if g is None:
-                    g = plan.loop_graphs[iters] = self._capture(plan, True, mask_every_iter, iters, tail_pools=tp)
+                    pipe = self.pipelined and self.two_lanes and self.n_layers >= 2 and not mask_every_iter and not tp
+                    g = plan.loop_graphs[iters] = self._capture(plan, True, mask_every_iter, iters, tail_pools=tp,
+                                                                pipelined=pipe)
                 self._replay(g)
                 plan.iter_calls += iters
             else:

@@ -357,6 +357,31 @@ def test_fused_loop_equals_stepwise_path(fsb):
     assert torch.equal(got2, got)
 
 
+@pytest.mark.parametrize("layers", [3, 2])
+def test_pipelined_loop_is_bit_identical(fsb, layers):
+    """refine() with the coarse GRU levels of iteration i+1 issued under the disparity head of iteration i
+    (run_loop_pipelined) launches the same kernels on the same operands in another stream order: the disparity, the mask
+    features and the hidden states are BIT-identical to the default loop graph's, on repeated replays too."""
+    H, W, D, iters = 24, 40, 16, 6
+    p = oracle.make_update_block_params(seed=3, delta_scale=0.25, n_gru_layers=layers)
+    x = oracle.make_inputs(B=2, C=32, H=H, W=W, D=D, Cg=28, seed=6)
+    c = lambda t: t.cuda()
+    dx = torch.linspace(-4, 4, 9).reshape(1, 1, -1, 1)
+    geo = fsb.Combined_Geo_Encoding_Volume(c(x["fl"]), c(x["fr"]), c(x["volume"]), num_levels=2, dx=dx)
+    inp, att = [c(t) for t in x["inp"]][:layers], [c(t) for t in x["att"]][:layers]
+    outs = []
+    for pipe in (False, True):
+        ub = fsb.SelectiveUpdateBlock(p, "cuda", use_graph=True)
+        ub.pipelined = pipe
+        for _ in range(3):  # eager + per-iteration graph, then the captured loop graph, then its replay
+            got, mask, net = ub.refine(geo, [c(t) for t in x["net"]][:layers], inp, att, c(x["disp"]), iters)
+        outs.append((got.clone(), mask.clone(), [t.clone() for t in net]))
+    torch.cuda.synchronize()
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    for a, b in zip(outs[0][2], outs[1][2]):
+        assert torch.equal(a, b)
+
+
 # ------------------------------------------------------- kernel 2 on tcgen05 (TF32 / 3xTF32)
 @pytest.mark.parametrize("shape", [
     # B, C, H, W1(=W2)
