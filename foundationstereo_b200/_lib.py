@@ -84,6 +84,7 @@ _PROTOS = {
     "fsb_corr_pyramid_band": (c_int, [c_void_p, c_void_p, POINTER(c_void_p)] + [c_int] * 8 + [c_void_p]),
     "fsb_geo_lookup_band": (c_int, [POINTER(c_void_p), POINTER(c_void_p), c_void_p, c_void_p, c_void_p]
                             + [c_int] * 9 + [c_void_p]),
+    "fsb_lookup_convc1": (c_int, [POINTER(c_void_p), POINTER(c_void_p)] + [c_void_p] * 5 + [c_int] * 10 + [c_void_p]),
     "fsb_conv_args_size": (c_size_t, []),
     "fsb_conv2d_nhwc": (c_int, [POINTER(ConvArgs), c_int, c_void_p]),
     "fsb_nchw_to_nhwc": (c_int, [c_void_p] * 3 + [c_int] * 6 + [c_void_p]),

@@ -194,6 +194,46 @@ def geo_lookup_nhwc16(geo_levels: List[torch.Tensor], corr_levels: List[torch.Te
     return out
 
 
+def lookup_convc1(geo_levels: List[torch.Tensor], corr_levels: List[torch.Tensor], disp: torch.Tensor,
+                  coords: torch.Tensor, radius: int, weight: torch.Tensor, bias: torch.Tensor,
+                  out: torch.Tensor) -> torch.Tensor:
+    """Kernels 3+4 fused (csrc/lookconv.cu): ``out`` (B,H,W,256) 16-bit NHWC = ReLU(convc1(lookup(disp))) without the
+    lookup tensor ever reaching HBM (core/geometry.py:43-65 + core/update.py:56,63).  ``weight`` (256, Cpad) 16-bit =
+    ``pack_convc1_weight(convc1.weight, L, K, Cg)``: level l's K*(Cg+1) columns at [l*Kl, ...), Kl = K*(Cg+1) rounded up
+    to 64, zeros between; ``bias`` fp32."""
+    _need_cuda(disp, coords, out, weight, bias)
+    L = len(geo_levels)
+    B, _, H, W = disp.shape
+    N, D, Cg = geo_levels[0].shape
+    W2 = corr_levels[0].shape[1]
+    K = 2 * radius + 1
+    cpad = L * ((K * (Cg + 1) + 63) // 64 * 64)
+    cout = weight.shape[0]
+    assert weight.shape == (cout, cpad) and weight.is_contiguous() and weight.dtype == out.dtype
+    assert out.shape == (B, H, W, cout) and out.is_contiguous() and out.dtype in (torch.float16, torch.bfloat16)
+    assert bias.dtype == torch.float32 and bias.numel() == cout
+    assert disp.dtype == torch.float32 and disp.is_contiguous() and coords.dtype == torch.float32 \
+        and coords.is_contiguous() and coords.numel() == N == B * H * W
+    _call(disp, "fsb_lookup_convc1", level_array(geo_levels), level_array(corr_levels), disp.data_ptr(), coords.data_ptr(),
+          weight.data_ptr(), bias.data_ptr(), out.data_ptr(), B, Cg, D, H, W, W2, L, radius, cout,
+          1 if out.dtype == torch.float16 else 2)
+    return out
+
+
+def pack_convc1_weight(weight: torch.Tensor, L: int, K: int, Cg: int, dtype: torch.dtype) -> torch.Tensor:
+    """convc1.weight (Cout, L*K*(Cg+1)[, 1, 1]) in the reference's channel order (core/geometry.py:60-65: per level the
+    K*Cg geometry samples c*K + k, then the K correlation taps) -> the (Cout, L*Kl) 16-bit matrix fsb_lookup_convc1 reads:
+    every level starts at a multiple of Kl = K*(Cg+1) rounded up to 64 columns, the columns in between are zero."""
+    n = K * (Cg + 1)
+    kl = (n + 63) // 64 * 64
+    w = weight.reshape(weight.shape[0], -1)
+    assert w.shape[1] == L * n, (tuple(weight.shape), L, K, Cg)
+    out = torch.zeros(w.shape[0], L * kl, dtype=dtype, device=w.device)
+    for l in range(L):
+        out[:, l * kl:l * kl + n] = w[:, l * n:(l + 1) * n].to(dtype)
+    return out.contiguous()
+
+
 def corr_pyramid_into(f1: torch.Tensor, f2: torch.Tensor, levels: List[torch.Tensor], precision: int) -> None:
     """fsb_corr_pyramid into caller-owned level buffers (stable addresses for graph capture)."""
     _need_cuda(f1, f2)

@@ -72,6 +72,8 @@ class _Plan:
         self.loop_graphs: Dict[int, torch.cuda.CUDAGraph] = {}
         self.iter_key = None
         self.lookup: Optional[Callable[[], None]] = None
+        self.fused_c1: Optional[Callable[[], None]] = None
+        self.loop_active = False
         self.calls = 0
         self.iter_calls = 0
         self.flops = 0.0
@@ -83,6 +85,21 @@ class _Plan:
         self.lanes.append(self.lane)
         self.tags.append(self.tag)
         self.groups.append(self.group)
+
+
+class _Convc1Step:
+    """The encoder.convc1 step of a plan: the plain 1x1 convolution over the lookup buffer, or -- when `refine` has
+    bound ``plan.fused_c1`` -- the lookup fused into it."""
+
+    def __init__(self, plan: _Plan, conv):
+        self.plan, self.conv = plan, conv
+        self.flops = conv.flops
+        self.args = conv.args
+
+    def __call__(self) -> None:
+        # only inside refine()'s loop: the drop-in forward() is handed ITS caller's lookup tensor
+        fused = self.plan.fused_c1 if self.plan.loop_active else None
+        (fused or self.conv)()
 
 
 class SelectiveUpdateBlock:
@@ -115,6 +132,13 @@ class SelectiveUpdateBlock:
         # fork / join costs what the 45 us of pooling save), so it is off by default; FSB_TAIL_POOLS=1 switches it on.
         self.tail_pools = _os.environ.get("FSB_TAIL_POOLS", "0") == "1"
         self.pool_fp32 = _os.environ.get("FSB_POOL_FP32", "0") == "1"
+        # refine(): the lookup fused into encoder.convc1 (csrc/lookconv.cu: the lookup tensor never reaches HBM, 354 MB of
+        # DRAM traffic per 8-pair iteration gone).  B200, 8 pairs: 156 us against 93 + 53 us for the two launches alone,
+        # 92.4 vs 91.6 pairs/s in the loop.  Same 16-bit operand values; the GEMM's K order differs (split by level), so
+        # results agree to fp32 accumulation order (max |d disparity| 2.6e-5 px after 6 iterations in the test).
+        # FSB_FUSED_LOOKUP_CONV=0 restores the two launches; radius != 4, more than two levels, Cg % 4 != 0 or a banded
+        # correlation pyramid use them anyway.
+        self.fused_lookup_conv = _os.environ.get("FSB_FUSED_LOOKUP_CONV", "1") != "0"
         # refine(): coarse GRU levels of iteration i+1 under the disparity head of iteration i (run_loop_pipelined).
         # Bit-identical results; B200, 8 pairs: 93.0 -> 93.9 pairs/s (2640 -> 2614 us per iteration) -- the step runs at
         # the 1000 W power cap, and the SM clock under load dropped from 1615 to 1555 MHz with the busier schedule, which
@@ -153,6 +177,7 @@ class SelectiveUpdateBlock:
         self.f: Dict[str, Tensor] = {}                      # fp32 side parameters
         self._pack(sd)
         self._plans: Dict[Tuple[int, int, int], _Plan] = {}
+        self._w1_levels = None   # convc1 weights in the per-level layout of fsb_lookup_convc1
 
     # ---- weight packing -----------------------------------------------------------------
     def _lay(self, launch: str) -> int:
@@ -359,6 +384,10 @@ class SelectiveUpdateBlock:
             plan.group = "enc"
             c1, c2, d1, d2, motion = new(0, 256), new(0, 256), new(0, 64), new(0, 64), new(0, hd)
             self._conv(plan, "encoder.convc1", "convc1", [plan.corr16], [(1, [0])], "convc1", _lib.FSB_EPI_RELU, out=c1)
+            # refine() may bind `plan.fused_c1`: ONE launch that gathers the lookup straight into this GEMM's shared
+            # memory operand (csrc/lookconv.cu) -- then `plan.lookup` is a no-op and corr16 is not written at all
+            plan.c1 = c1
+            plan.steps[-1] = _Convc1Step(plan, plan.steps[-1])
             self._conv(plan, "encoder.convc2", "convc2", [c1], [(3, [0])], "convc2", _lib.FSB_EPI_RELU, out=c2)
             add("encoder.convd1", lambda: C.conv7x7_c1(plan.disp, self.f["convd1.w"], self.f["convd1.b"], d1, 64, motion,
                                                         hd - 1))
@@ -751,7 +780,20 @@ class SelectiveUpdateBlock:
                 levels = (list(geo.geo_levels), list(geo.corr_levels), geo.radius)
                 from . import ops
                 band = getattr(geo, "corr_band", None)
-                if band is not None:
+                plan.fused_c1 = None
+                Cg = levels[0][0].shape[2]
+                if (self.fused_lookup_conv and band is None and self.n_layers >= 2 and levels[2] == 4
+                        and len(levels[0]) <= 2 and Cg % 4 == 0 and Cg <= 28):
+                    # lookup -> convc1 as ONE launch (csrc/lookconv.cu): the lookup tensor never reaches HBM
+                    L_ = len(levels[0])
+                    if self._w1_levels is None or self._w1_levels[0] != (L_, Cg):
+                        self._w1_levels = ((L_, Cg), ops.pack_convc1_weight(self._sd["encoder.convc1.weight"], L_, 9, Cg, self.dtype),
+                                           self._sd["encoder.convc1.bias"].float().contiguous())
+                    _, w1, b1 = self._w1_levels
+                    plan.fused_c1 = lambda: ops.lookup_convc1(levels[0], levels[1], plan.disp, plan.coords, levels[2], w1,
+                                                              b1, plan.c1)
+                    plan.lookup = lambda: None
+                elif band is not None:
                     plan.lookup = lambda: ops.geo_lookup_band(levels[0], levels[1], plan.disp, plan.coords, levels[2], band,
                                                               plan.corr16)
                 else:
@@ -761,6 +803,17 @@ class SelectiveUpdateBlock:
                 plan.iter_graph = None
                 plan.loop_graphs = {}
                 plan.iter_calls = 0
+            plan.loop_active = True
+            try:
+                self._refine_loop(plan, iters, mask_every_iter)
+            finally:
+                plan.loop_active = False
+            if not mask_every_iter:
+                self.run_steps(plan, only_mask=True)
+            return plan.disp.clone(), plan.mask, [plan.h32[l].permute(0, 3, 1, 2) for l in range(self.n_layers)]
+
+    def _refine_loop(self, plan: _Plan, iters: int, mask_every_iter: bool) -> None:
+        if True:
             # prologue: the first iteration's pooled inputs; every iteration then pools for its successor (tail_pools)
             tp = self.tail_pools
             if tp:
@@ -784,6 +837,3 @@ class SelectiveUpdateBlock:
                     if plan.iter_graph is None:
                         plan.iter_graph = self._capture(plan, True, mask_every_iter, tail_pools=tp)
                     self._replay(plan.iter_graph)
-            if not mask_every_iter:
-                self.run_steps(plan, only_mask=True)
-            return plan.disp.clone(), plan.mask, [plan.h32[l].permute(0, 3, 1, 2) for l in range(self.n_layers)]

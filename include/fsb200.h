@@ -138,6 +138,23 @@ int fsb_geo_lookup_band(float* const* geo_levels, float* const* corr_levels, con
                         void* out, int B, int Cg, int D, int H, int W, int L, int r, int out_layout, int d_band,
                         fsb_stream_t stream);
 
+/* ---- kernels 3+4 fused: lookup -> encoder.convc1 --------------------------------------
+ * replaces Combined_Geo_Encoding_Volume.__call__ (core/geometry.py:43-65, bilinear_sampler core/utils/utils.py:44-55)
+ * TOGETHER WITH the first layer of BasicMotionEncoder, cor = ReLU(convc1(corr)) (core/update.py:56,63): the
+ * L*K*(Cg+1)-channel lookup tensor is produced in shared memory as the GEMM operand and never exists in HBM.
+ *   geo_levels / corr_levels / disp / coords : as fsb_geo_lookup
+ *   w    : (Cout, L*Kl) 16-bit row-major, Kl = round_up(K*(Cg+1), 64): the columns of convc1.weight
+ *          (Cout, L*K*(Cg+1), 1, 1) that belong to level l (the reference's channel order inside a level: c*K + k for
+ *          the geometry samples, then the K correlation taps) at [l*Kl, l*Kl + K*(Cg+1)), zeros in between -- the GEMM's
+ *          K dimension is split by level so that one level's MMAs run under the other level's gather
+ *   bias : (Cout) fp32;   out : (B,H,W,Cout) 16-bit NHWC
+ * Same values as fsb_geo_lookup(out_layout 1 / 2) followed by the 1x1 convolution with FSB_EPI_RELU.
+ * Limits: radius 4, L <= 2, Cg a multiple of 4 and <= 28, Cout = 256 (the reference's inference configuration); anything else returns
+ * FSB_ERR_SHAPE and the two separate calls are the path. */
+int fsb_lookup_convc1(float* const* geo_levels, float* const* corr_levels, const float* disp, const float* coords,
+                      const void* w, const float* bias, void* out, int B, int Cg, int D, int H, int W, int W2, int L,
+                      int r, int Cout, int dtype, fsb_stream_t stream);
+
 /* ---- kernel 4: 3x3 / 1x1 convolution as a tcgen05 implicit GEMM with fused epilogue ----
  * The convolutions of the update block (core/update.py:20-159): SelectiveConvGRU conv0/conv1,
  * the RaftConvGRU gate convolutions convz/convr/convq with their sigmoid / tanh / blend

@@ -357,6 +357,89 @@ def test_fused_loop_equals_stepwise_path(fsb):
     assert torch.equal(got2, got)
 
 
+@pytest.mark.parametrize("cfg", [
+    # B, H, W, D, Cg, L, dtype
+    (1, 24, 40, 16, 28, 2, torch.float16),     # 8 tiles, the last one ragged
+    (2, 7, 23, 13, 28, 2, torch.bfloat16),     # odd sizes, 3 tiles
+    (3, 60, 80, 52, 28, 2, torch.float16),     # 113 tiles: fewer than the SMs
+    (2, 120, 160, 104, 28, 2, torch.float16),  # the bench's shape, 300 tiles: several per CTA (operand / accumulator reuse)
+    (1, 9, 31, 20, 12, 1, torch.float16),      # one level, other Cg
+])
+def test_lookup_fused_into_convc1(fsb, cfg):
+    """fsb_lookup_convc1 (the lookup produced in shared memory as convc1's GEMM operand) against (a) the two existing
+    launches -- fsb_geo_lookup(16-bit NHWC) + the 1x1 convolution with ReLU -- and (b) fp32 PyTorch on the oracle's lookup."""
+    from foundationstereo_b200 import ops, conv as Cv, _lib
+    B, H, W, D, Cg, L, dtype = cfg
+    r, K = 4, 9
+    x = oracle.make_inputs(B=B, C=16, H=H, W=W, D=D, Cg=Cg, seed=21)
+    dx = torch.linspace(-r, r, K).reshape(1, 1, -1, 1)
+    vol = fsb.Combined_Geo_Encoding_Volume(dev(x["fl"]), dev(x["fr"]), dev(x["volume"]), num_levels=L, dx=dx)
+    disp, coords = dev(x["disp"]), dev(x["coords"])
+    P = L * K * (Cg + 1)
+    cpad = (P + 63) // 64 * 64
+    g = torch.Generator().manual_seed(5)
+    w = torch.randn(256, P, generator=g) / P ** 0.5
+    bias = (torch.randn(256, generator=g) * 0.1).cuda()
+    wp = torch.zeros(256, cpad, dtype=dtype, device="cuda")
+    wp[:, :P] = w.to(dtype)
+    wl = ops.pack_convc1_weight(w.cuda(), L, K, Cg, dtype)     # the same weights in the per-level layout
+    got = torch.full((B, H, W, 256), 9.0, dtype=dtype, device="cuda")
+    ops.lookup_convc1(vol.geo_levels, vol.corr_levels, disp, coords, r, wl, bias, got)
+    # (a) the two launches
+    buf = torch.empty(B, H, W, cpad, dtype=dtype, device="cuda")
+    vol.lookup_nhwc16(disp, coords, buf)
+    two = torch.empty_like(got)
+    Cv.ConvLaunch(srcs=[buf], segs=[(1, [0])], weight=wp, bias=bias, cout=256, block_n=128, epilogue=_lib.FSB_EPI_RELU,
+                  name="convc1", layout=_lib.FSB_CONV_LAYOUT_TAP, out=two)()
+    torch.cuda.synchronize()
+    eps = 2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7
+    assert torch.isfinite(got.float()).all()
+    assert rel_err(got.float(), two.float()) <= 2 * eps, rel_err(got.float(), two.float())
+    # (b) fp32 PyTorch on the same 16-bit-rounded operands
+    want = torch.relu(buf[..., :P].float() @ wp[:, :P].float().t() + bias)
+    assert rel_err(got.float(), want) <= 2 * eps
+    # a second call on another disparity through the same buffers (operand rows of a ragged last tile keep old values)
+    disp2 = (disp * 0.5 + 1.0).contiguous()
+    ops.lookup_convc1(vol.geo_levels, vol.corr_levels, disp2, coords, r, wl, bias, got)
+    vol.lookup_nhwc16(disp2, coords, buf)
+    want2 = torch.relu(buf[..., :P].float() @ wp[:, :P].float().t() + bias)
+    torch.cuda.synchronize()
+    assert rel_err(got.float(), want2) <= 2 * eps
+
+
+def test_loop_with_lookup_fused_into_convc1(fsb):
+    """refine() with the lookup gathered straight into encoder.convc1's shared-memory operand (fused_lookup_conv) against
+    the default loop (lookup kernel -> 16-bit NHWC buffer -> convc1): the same 16-bit operand values and fp32 accumulation,
+    so the trajectories agree to accumulation-order noise; the drop-in forward() on the same plan still uses ITS corr."""
+    H, W, D, iters = 24, 40, 16, 6
+    p = oracle.make_update_block_params(seed=3, delta_scale=0.25)
+    x = oracle.make_inputs(B=2, C=32, H=H, W=W, D=D, Cg=28, seed=6)
+    c = lambda t: t.cuda()
+    dx = torch.linspace(-4, 4, 9).reshape(1, 1, -1, 1)
+    geo = fsb.Combined_Geo_Encoding_Volume(c(x["fl"]), c(x["fr"]), c(x["volume"]), num_levels=2, dx=dx)
+    inp, att = [c(t) for t in x["inp"]], [c(t) for t in x["att"]]
+    outs = []
+    for fused in (False, True):
+        ub = fsb.SelectiveUpdateBlock(p, "cuda", use_graph=True)
+        ub.fused_lookup_conv = fused
+        for _ in range(3):  # eager + per-iteration graph, then the captured loop graph, then its replay
+            got, mask, net = ub.refine(geo, [c(t) for t in x["net"]], inp, att, c(x["disp"]), iters)
+        outs.append((got.clone(), mask.clone(), [t.clone() for t in net]))
+        if fused:
+            n0 = fsb.launch_count()
+            feat = geo(c(x["disp"]), c(x["coords"]))
+            _, _, d1 = ub([c(t) for t in x["net"]], inp, feat, c(x["disp"]), att)
+            ub0 = fsb.SelectiveUpdateBlock(p, "cuda", use_graph=False)
+            _, _, d0 = ub0([c(t) for t in x["net"]], inp, feat, c(x["disp"]), att)
+            assert torch.equal(d1, d0)
+    torch.cuda.synchronize()
+    assert (outs[0][0] - outs[1][0]).abs().max().item() <= 2e-3
+    assert rel_err(outs[1][1], outs[0][1]) <= 5e-3
+    for a, b in zip(outs[1][2], outs[0][2]):
+        assert rel_err(a, b) <= 5e-3
+    print("fused lookup->convc1 loop: max |d disparity| =", (outs[0][0] - outs[1][0]).abs().max().item())
+
+
 @pytest.mark.parametrize("layers", [3, 2])
 def test_pipelined_loop_is_bit_identical(fsb, layers):
     """refine() with the coarse GRU levels of iteration i+1 issued under the disparity head of iteration i
@@ -545,6 +628,9 @@ def test_banded_hot_path_equals_full_when_disparities_stay_inside(fsb):
     outs = []
     for banded in (False, True):
         hp = fsb.StereoHotPath(p, max_disp=4 * D, corr_band=banded)
+        # like with like: the band form always runs lookup and convc1 as two launches; the fused lookup -> convc1 kernel
+        # of the full form accumulates in another K order (equal to fp32 rounding, not bit for bit)
+        hp.update_block.fused_lookup_conv = False
         for _ in range(2):
             got, _, _ = hp.run(c(x["fl"]), c(x["fr"]), c(x["pl"]), c(x["pr"]), c(x["volume"]), c(x["disp"]),
                                [c(t) for t in x["net"]], [c(t) for t in x["inp"]], [c(t) for t in x["att"]], iters)
