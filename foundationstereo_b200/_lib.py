@@ -75,6 +75,7 @@ _PROTOS = {
     "fsb_set_pdl": (c_int, [c_int]),
     "fsb_volume_gwc_concat": (c_int, [c_void_p] * 6 + [c_int] * 8 + [c_void_p]),
     "fsb_volume_combined": (c_int, [c_void_p] * 5 + [c_int] * 8 + [c_void_p]),
+    "fsb_volume_stem": (c_int, [c_void_p] * 9 + [c_int] * 9 + [c_void_p]),
     "fsb_corr_pyramid": (c_int, [c_void_p, c_void_p, POINTER(c_void_p)] + [c_int] * 7 + [c_void_p]),
     "fsb_geo_pyramid": (c_int, [c_void_p, POINTER(c_void_p)] + [c_int] * 6 + [c_void_p]),
     "fsb_geo_pyramid_in": (c_int, [c_void_p, c_int, POINTER(c_void_p)] + [c_int] * 6 + [c_void_p]),

@@ -98,6 +98,27 @@ def _(fl, fr, pl, pr, maxdisp, num_groups):
     return fl.new_empty((B, num_groups + 2 * pl.shape[1], maxdisp, H, W))
 
 
+def volume_stem(fl: torch.Tensor, fr: torch.Tensor, pl: torch.Tensor, pr: torch.Tensor, weight: torch.Tensor,
+                bias: torch.Tensor, maxdisp: int, num_groups: int) -> torch.Tensor:
+    """corr_stem[0](cat([gwc volume, concat volume], 1)) in one launch (csrc/volstem.cu; core/foundation_stereo.py:207-213
+    with the 1x1x1 Conv3d of :164-165): ``weight`` (Co, G + 2 Cp[, 1, 1, 1]) and ``bias`` (Co) are that convolution's
+    parameters.  -> (B, Co, maxdisp, H, W) in the dtype of ``fl``.  Opt-in: the caller hands over part of corr_stem."""
+    _need_cuda(fl, fr, pl, pr, weight, bias)
+    assert fl.shape == fr.shape and pl.shape == pr.shape and fl.dtype == fr.dtype == pl.dtype == pr.dtype
+    B, C, H, W = fl.shape
+    Cp = pl.shape[1]
+    w = weight.reshape(weight.shape[0], -1).float().contiguous()
+    Co = w.shape[0]
+    assert w.shape[1] == num_groups + 2 * Cp and bias.numel() == Co
+    fl, fr, pl, pr, bias = fl.contiguous(), fr.contiguous(), pl.contiguous(), pr.contiguous(), bias.float().contiguous()
+    out = fl.new_empty((B, Co, maxdisp, H, W))
+    scratch = torch.empty((2, B, C, H, W), dtype=torch.float32, device=fl.device)   # the L2-normalised features
+    wg_host = w[:, :num_groups].cpu().contiguous()   # (Co, G) on the host: passed to the kernel by value
+    _call(fl, "fsb_volume_stem", fl.data_ptr(), fr.data_ptr(), pl.data_ptr(), pr.data_ptr(), w.data_ptr(), bias.data_ptr(),
+          wg_host.data_ptr(), scratch.data_ptr(), out.data_ptr(), B, C, Cp, num_groups, Co, H, W, maxdisp, _DTYPE[fl.dtype])
+    return out
+
+
 # ----------------------------------------------------------------------------------------
 # kernels 2 / 2b
 # ----------------------------------------------------------------------------------------

@@ -24,7 +24,7 @@ _SAVED = {}
 
 
 def install(model=None, modules: Optional[list] = None, fused_lookup: bool = True,
-            fused_upsample: bool = False, corr_band: Optional[int] = None) -> None:
+            fused_upsample: bool = False, corr_band: Optional[int] = None, fused_stem: bool = False) -> None:
     """Rebind the three names in every loaded reference module that holds them and, if a
     FoundationStereo ``model`` is given, route ``model.update_block.forward`` through
     SelectiveUpdateBlock built from the module's own parameters.
@@ -37,7 +37,14 @@ def install(model=None, modules: Optional[list] = None, fused_lookup: bool = Tru
 
     ``fused_upsample`` (opt-in, needs a model) swaps ``model.upsample_disp``
     (core/foundation_stereo.py:183-191) for a method that runs the two spx networks as before and
-    then ONE kernel for softmax over the 9 weights + ``disp*4`` + convex upsampling."""
+    then ONE kernel for softmax over the 9 weights + ``disp*4`` + convex upsampling.
+
+    ``fused_stem`` (opt-in, needs a model) folds the first layer of ``model.corr_stem`` -- the 1x1x1
+    Conv3d(32 -> 28) of core/foundation_stereo.py:164-165 -- into the volume kernel (csrc/volstem.cu): the unchanged
+    caller's ``build_gwc_volume`` call (:207) only records the features and returns a zero-channel tensor, its
+    ``build_concat_volume`` call (:210) returns the convolution's RESULT, ``torch.cat`` (:212) passes it through and
+    ``corr_stem[0].forward`` becomes the identity (the module and its ``state_dict`` keys stay).  The 32-channel volume is
+    never written, concatenated or read back."""
     geo_cls = Combined_Geo_Encoding_Volume
     if corr_band:
         # opt-in: banded init correlation for disparities in [0, corr_band] (use model.args.max_disp // 4); lookups
@@ -58,9 +65,14 @@ def install(model=None, modules: Optional[list] = None, fused_lookup: bool = Tru
             geo_cls = FusedGeoEncodingVolume
         if fused_upsample:
             install_upsample(model)
+    gwc_fn, cat_fn = build_gwc_volume, build_concat_volume
+    if fused_stem:
+        if model is None:
+            raise ValueError("fused_stem needs the model (it reads corr_stem[0]'s parameters)")
+        gwc_fn, cat_fn = install_stem(model)
     names = {
-        "build_gwc_volume": build_gwc_volume,
-        "build_concat_volume": build_concat_volume,
+        "build_gwc_volume": gwc_fn,
+        "build_concat_volume": cat_fn,
         "Combined_Geo_Encoding_Volume": geo_cls,
         "disparity_regression": disparity_regression,
         "context_upsample": context_upsample,
@@ -106,6 +118,28 @@ def install_update_block(update_block):
     return engine
 
 
+def install_stem(model):
+    """-> (build_gwc_volume, build_concat_volume) stand-ins that together return corr_stem[0](cat([gwc, concat], 1)) from
+    ONE launch (ops.volume_stem), and make ``model.corr_stem[0].forward`` the identity."""
+    from . import ops
+    conv0 = model.corr_stem[0]
+    pending = {}
+
+    def gwc_deferred(refimg_fea, targetimg_fea, maxdisp, num_groups, stride=1):
+        pending["f"] = (refimg_fea, targetimg_fea, num_groups)
+        B, _, H, W = refimg_fea.shape
+        return refimg_fea.new_empty((B, 0, maxdisp, H, W))   # torch.cat (core/foundation_stereo.py:212) skips it
+
+    def concat_with_stem(refimg_fea, targetimg_fea, maxdisp):
+        fl, fr, groups = pending.pop("f")
+        dt = fl.dtype
+        return ops.volume_stem(fl, fr, refimg_fea.to(dt), targetimg_fea.to(dt), conv0.weight, conv0.bias, maxdisp, groups)
+
+    _SAVED.setdefault(("corr_stem0", id(model)), conv0.forward)
+    conv0.forward = types.MethodType(lambda self, x: x, conv0)
+    return gwc_deferred, concat_with_stem
+
+
 def install_upsample(model) -> None:
     """``model.upsample_disp`` (core/foundation_stereo.py:183-191) with its tail fused: the spx
     networks stay the model's own modules, softmax + ``disp*4.`` + context_upsample are one launch."""
@@ -123,7 +157,7 @@ def install_upsample(model) -> None:
 
 def uninstall(model=None) -> None:
     for (modname, name), fn in list(_SAVED.items()):
-        if modname in ("update_block", "upsample_disp"):
+        if modname in ("update_block", "upsample_disp", "corr_stem0"):
             continue
         mod = sys.modules.get(modname)
         if mod is not None:
@@ -136,3 +170,6 @@ def uninstall(model=None) -> None:
         key = ("upsample_disp", id(model))
         if key in _SAVED:
             model.upsample_disp = _SAVED.pop(key)
+        key = ("corr_stem0", id(model))
+        if key in _SAVED:
+            model.corr_stem[0].forward = _SAVED.pop(key)

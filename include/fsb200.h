@@ -79,6 +79,25 @@ int fsb_volume_gwc_concat(const void* fl, const void* fr, const void* pl, const 
 int fsb_volume_combined(const void* fl, const void* fr, const void* pl, const void* pr, void* out, int B, int C,
                         int Cp, int G, int H, int W, int D, int dtype, fsb_stream_t stream);
 
+/* ---- kernel 1 fused with its consumer -- OPT-IN: it computes part of corr_stem ----------
+ * replaces core/foundation_stereo.py:207-213 up to and including corr_stem[0], the 1x1x1 Conv3d(G + 2 Cp -> Co) of
+ * :164-165:    out = corr_stem[0](cat([build_gwc_volume(fl, fr), build_concat_volume(pl, pr)], 1))
+ * in one launch; the (B, G + 2 Cp, D, H, W) volume, its torch.cat copy and the convolution's read never exist.
+ *   fl, fr, pl, pr : as fsb_volume_gwc_concat (all of `dtype`)
+ *   weight : (Co, G + 2 Cp) fp32 row-major = corr_stem[0].weight (Co, 32, 1, 1, 1): columns [gwc groups | left proj |
+ *            right proj], the channel order of the reference's cat;   bias : (Co) fp32
+ *   wg_host: HOST pointer to the (Co, G) correlation block weight[:, :G], row-major fp32 (the one host pointer of the
+ *            library: these 224 values reach the kernel as launch parameters, so that every FFMA of the 1x1x1 convolution
+ *            takes its weight from the constant bank); read during the call, not retained
+ *   scratch: 2 * B * C * H * W floats, caller-owned, 16-byte aligned (the L2-normalised features, written by a first
+ *            launch and read by the second)
+ *   out    : (B, Co, D, H, W) of `dtype`, contiguous.  fp32 arithmetic throughout.
+ * Limits: G <= 8, Co <= 32, and one image row's working set must fit shared memory (W = 312, D = 104 does, the
+ * W = 512 panorama does not: FSB_ERR_SHAPE). */
+int fsb_volume_stem(const void* fl, const void* fr, const void* pl, const void* pr, const float* weight,
+                    const float* bias, const float* wg_host, float* scratch, void* out, int B, int C, int Cp, int G, int Co, int H, int W, int D,
+                    int dtype, fsb_stream_t stream);
+
 /* ---- kernel 2: init correlation + its avg-pool pyramid ---------------------------
  * replaces Combined_Geo_Encoding_Volume.corr (core/geometry.py:68-77) and the
  * init_corr pyramid (core/geometry.py:31,38-40).

@@ -76,10 +76,12 @@ def run(model, left, right, **kw):
         return model(left, right, iters=ITERS, test_mode=True, **kw)
 
 
-@pytest.mark.parametrize("variant", ["default", "fused_lookup_off", "fused_upsample", "outer_autocast", "inference_mode"])
+@pytest.mark.parametrize("variant", ["default", "fused_lookup_off", "fused_upsample", "outer_autocast", "inference_mode",
+                                     "fused_stem"])
 def test_install_matches_stock_forward(rm, fsb, ctx, variant):
     model, left, right, stock = ctx["model"], ctx["left"], ctx["right"], ctx["stock"]
-    kw = {"fused_lookup": variant != "fused_lookup_off", "fused_upsample": variant == "fused_upsample"}
+    kw = {"fused_lookup": variant != "fused_lookup_off", "fused_upsample": variant == "fused_upsample",
+          "fused_stem": variant == "fused_stem"}
     n0 = fsb.launch_count()
     fsb.install(model, **kw)
     try:

@@ -8,6 +8,7 @@ in fp32; pure copies bit-exact.  "relative" = max|a-b| / max|b| (conftest.rel_er
 """
 import pytest
 import torch
+import torch.nn.functional as F
 
 import oracle
 from conftest import load_golden, rel_err
@@ -287,6 +288,43 @@ def test_run_pinned_matches_run(fsb):
     assert len(outs) == 3
     for o, w in zip(outs, want):
         assert o.is_pinned() and torch.equal(o, w)
+
+
+@pytest.mark.parametrize("cfg", [
+    # B, C, H, W, D, dtype
+    (1, 128, 6, 160, 104, torch.float32),    # the bench's row shape
+    (2, 128, 5, 160, 104, torch.float16),    # what the autocast caller hands over
+    (1, 64, 3, 23, 13, torch.float32),       # odd W (scalar stores), D not a multiple of the 8-disparity chunk
+    (1, 224, 2, 312, 104, torch.bfloat16),   # ViT-L channels, KITTI width
+    (1, 32, 4, 20, 40, torch.float32),       # D > W: most of the volume lies in the w < d triangle
+])
+def test_volume_fused_with_corr_stem(fsb, cfg):
+    """fsb_volume_stem == corr_stem[0](cat([gwc volume, concat volume], 1)) (core/foundation_stereo.py:207-213,164-165):
+    against fp32 PyTorch on the oracle's volumes.  fp32 <= 1e-4 relative; 16-bit storage: the reference rounds the
+    volume to 16 bits before the convolution and its output after it, the fused kernel rounds only the output."""
+    from foundationstereo_b200 import ops
+    B, C, H, W, D, dtype = cfg
+    G, Cp, Co = 8, 12, 28
+    x = oracle.make_inputs(B=B, C=C, H=H, W=W, D=D, Cg=28, seed=31)
+    g = torch.Generator().manual_seed(7)
+    wst = torch.randn(Co, G + 2 * Cp, generator=g) / (G + 2 * Cp) ** 0.5
+    bst = torch.randn(Co, generator=g) * 0.1
+    fl, fr, pl, pr = (x[k].to(dtype) for k in ("fl", "fr", "pl", "pr"))
+    with torch.no_grad():
+        vol = torch.cat([oracle.gwc_volume(fl.float(), fr.float(), D, G), oracle.concat_volume(pl.float(), pr.float(), D)], 1)
+        want = F.conv3d(vol, wst.reshape(Co, -1, 1, 1, 1), bst)
+    got = ops.volume_stem(dev(fl), dev(fr), dev(pl), dev(pr), wst.reshape(Co, -1, 1, 1, 1).cuda(), bst.cuda(), D, G)
+    assert got.shape == want.shape and got.dtype == dtype and got.is_contiguous()
+    tol = 1e-4 if dtype == torch.float32 else (2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7)
+    assert rel_err(got.float().cpu(), want) <= tol, rel_err(got.float().cpu(), want)
+
+
+def test_volume_stem_rejects_rows_beyond_shared_memory(fsb):
+    from foundationstereo_b200 import ops
+    f = torch.zeros(1, 128, 1, 512, device="cuda")
+    pj = torch.zeros(1, 12, 1, 512, device="cuda")
+    with pytest.raises(fsb.FsbError):   # the W = 512 panorama row does not fit: the separate kernels are the path there
+        ops.volume_stem(f, f, pj, pj, torch.zeros(28, 32, device="cuda"), torch.zeros(28, device="cuda"), 104, 8)
 
 
 # ------------------------------------------------------------- fused lookup output / fused loop
