@@ -450,11 +450,17 @@ def run_b200(args):
         plan.loop_active = False
         t_gpu_end = time.perf_counter()
         clocks.stop()
-        conv_ms = sum(t for (n_, f_), t in zip(steps_, tot) if hasattr(f_, "flops"))
-        other_ms = sum(t for (n_, f_), t in zip(steps_, tot) if not hasattr(f_, "flops"))
-        n_conv = sum(1 for n_, f_ in steps_ if hasattr(f_, "flops"))
+        # with the lookup fused into encoder.convc1 (csrc/lookconv.cu, the default loop) that launch is the HBM-bound gather
+        # with a small GEMM under it: it is reported under hbm_kernels, not in the tensor-core roofline
+        fused_c1 = bool(ub.fused_lookup_conv and plan.fused_c1 is not None)
+        is_conv = lambda n_, f_: hasattr(f_, "flops") and not (fused_c1 and n_ == "encoder.convc1")
+        conv_ms = sum(t for (n_, f_), t in zip(steps_, tot) if is_conv(n_, f_))
+        other_ms = sum(t for (n_, f_), t in zip(steps_, tot) if not is_conv(n_, f_))
+        n_conv = sum(1 for n_, f_ in steps_ if is_conv(n_, f_))
         flops_by_pass = [synthetic.update_block_flops(state, p["B"], p["H"], p["W"]) for p in passes]
-        conv_flops = flops_by_pass[-1]
+        c1_flops = sum(f_.flops for n_, f_ in steps_ if n_ == "encoder.convc1") if fused_c1 else 0.0
+        c1_ms = sum(t for (n_, f_), t in zip(steps_, tot) if n_ == "encoder.convc1")
+        conv_flops = flops_by_pass[-1] - c1_flops
         tf = conv_flops / (conv_ms * 1e-3) / 1e12
         peak_tf = peaks["bf16_tflops_sustained"]
         # in-step figure: the loops were timed with CUDA events INSIDE the timed steps (StereoHotPath.record_loop)
@@ -476,7 +482,10 @@ def run_b200(args):
             "geo_lookup_fp32_nchw": time_kernel(torch, lambda: geo(dev["disp"], coords), 20, flush),
         }
         per_step = {"volume_gwc_concat": n_micro, "corr_pyramid": n_micro, "geo_pyramid": n_micro,
-                    "geo_lookup": iters * n_micro, "geo_lookup_fp32_nchw": 0}
+                    "geo_lookup": 0 if fused_c1 else iters * n_micro, "geo_lookup_fp32_nchw": 0}
+        if fused_c1:   # timed above among the loop's launches (no L2 flush: the 2.7 GB geometry pyramid does not fit anyway)
+            kern_ms["lookup_convc1"] = c1_ms
+            per_step["lookup_convc1"] = iters * n_micro
         # opt-in banded init correlation (disparities in [0, D]): reported beside the full-matrix default
         bw0 = ops.corr_band_geometry(D, r, L)[0]
         if bw0 + (4 << (L - 1)) <= 224:
@@ -500,6 +509,8 @@ def run_b200(args):
         alg["corr_pyramid_band"] = 8 * px_ * c["C"] + 4 * px_ * sum(bw0 >> l for l in range(L))
         K_ = 2 * r + 1
         alg["geo_lookup_band"] = alg["geo_lookup"]   # the lookup reads the same windows, only their addresses differ
+        # lookup fused into convc1: disparity + coordinate, the (K+1)-row windows of every level, convc1's 256 x 16-bit output
+        alg["lookup_convc1"] = px_ * (8 + L * (c["Cg"] + 1) * (K_ + 1) * 4 + 256 * 2)
         kernels = {}
         for k, ms in kern_ms.items():
             gbs = alg[k] / (ms * 1e-3) / 1e9
