@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """profiles/traffic.json from two `ncu --set full` captures (8 pairs per launch, as bench.py's default):
-    python tools/make_traffic.py <update-step capture .ncu-rep> <kernels 1-3 capture .ncu-rep>
+    python tools/make_traffic.py <update-step capture .ncu-rep> <kernels 1-3 capture .ncu-rep> [<lookup_convc1 capture>]
 DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per launch; for the update block the sum over the
 tensor-core launches of ONE step (what bench.py's roofline.achieved is defined over)."""
 import csv
@@ -43,6 +43,10 @@ for n, b, _ in k123:
                 t["geo_lookup_band"] = b
             elif v not in t:
                 t[v] = b  # first launch of each kernel
+if len(sys.argv) > 3:   # optional third capture: the lookup fused into encoder.convc1 (tools/lookconv_exp.py)
+    for n, b, _ in rows(sys.argv[3]):
+        if "lookup_convc1" in n:
+            t.setdefault("lookup_convc1", b)
 t["note"] = "bytes per launch at 8 pairs (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum); conv_umma_kernel = " \
             "sum over the tensor-core launches of one update step"
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
