@@ -51,6 +51,8 @@ def test_noalloc_block_matches_existing_entry_points_twice_in_a_row(dtype):
         x = _rand(B, H, W, C_, seed=seed).to(dtype).cuda()
         data.append((x, _params(dtype, seed), torch.full_like(x, 7.0), torch.full_like(x, -3.0), torch.empty_like(x),
                      torch.full_like(x, 5.0)))
+    import gc
+    gc.collect()   # garbage of earlier tests must not be released between the two readings below
     torch.cuda.synchronize()
     for i, (x, prm, got, want_block, tmp, want_pair) in enumerate(data):
         before = torch.cuda.memory_allocated(), torch.cuda.mem_get_info()[0]
@@ -58,7 +60,7 @@ def test_noalloc_block_matches_existing_entry_points_twice_in_a_row(dtype):
         assert rc == 0, lib.fsb_last_error()
         torch.cuda.synchronize()
         after = torch.cuda.memory_allocated(), torch.cuda.mem_get_info()[0]
-        assert after[0] == before[0], "the call went through torch's allocator"
+        assert after[0] <= before[0], "the call went through torch's allocator"
         if i > 0:  # (the first call may load the kernels' module images lazily)
             assert after[1] >= before[1], f"device memory shrank by {before[1] - after[1]} bytes across a no-alloc call"
     for x, prm, got, want_block, tmp, want_pair in data:
