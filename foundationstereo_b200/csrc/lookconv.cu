@@ -7,19 +7,22 @@
 // One persistent CTA per SM walks 128-pixel tiles.  The K dimension of the GEMM is split BY PYRAMID LEVEL: level l owns
 // the operand half A[l] (Kl = K*(Cg+1) rounded up to 64 channels = 5 chunks of 64 for Cg = 28) and the columns
 // [l*Kl, (l+1)*Kl) of the packed weight matrix, so the two halves ping-pong:
-//   * 16 GATHER warps produce A[l] straight into shared memory: warp = pixel, lane = channel, exactly the gather of
-//     lookup_nhwc_kernel (geo.cu; lookup.cuh) -- positions with the reference's fp32 round trip, (K+1) window rows as
-//     coalesced 4*Cg-byte requests, four pixels in flight per warp -- and each lane writes its K lerped taps as 16-bit
-//     values into row p of the K-major SWIZZLE_128B tile [chunk][128 rows][64 channels], the layout TMA would have
-//     delivered from an NHWC lookup tensor (a warp's rows share row & 7, so its swizzled offsets are loop invariants);
+//   * 16 GATHER warps produce A[l] straight into shared memory.  A pass = 4 consecutive pixels: positions with the
+//     reference's fp32 round trip (lookup.cuh), computed co-operatively -- one division per tap, shuffled to the lanes
+//     that use them --, lane (pixel slot, channel quad) loads the K+1 window rows of its four channels as float4 (the
+//     window of a pixel is one contiguous run in the (BHW, D_l, Cg) layout), lerps 4 x K samples and writes them -- 72
+//     contiguous bytes of row p of the K-major SWIZZLE_128B tile [chunk][128 rows][64 channels], the layout TMA would
+//     have delivered from an NHWC lookup tensor -- as four 16-byte and one 8-byte store; lanes 28..31 do the
+//     correlation taps;
 //   * a TMA warp streams W1 (Cout = 256 rows, 16-bit K-major) from L2 through a two-stage ring of 64-channel chunks;
 //   * one elected thread issues tcgen05.mma (M = 128 pixels, N = 256, K = 16 per instruction) over the chunks of A[l]
 //     while the gather warps fill A[1-l], into one of TWO 256-column TMEM accumulators, so that
 //   * 4 EPILOGUE warps (bias, ReLU, 16-bit, 64 contiguous bytes per lane and 32 columns) drain tile i under tile i+1.
 // The first form of this kernel (one 144 KB operand, all levels, then the MMAs) serialised gather and MMA -- the weight
 // stream is latency-bound at 64 KB in flight, 7 us per tile -- and ran 255 us against 93 + 54 us for the two launches.
-// Same values as fsb_geo_lookup(out_layout 1/2) followed by the convc1 launch of fsb_conv2d_nhwc (bit-identical in the
-// tests): the operand is rounded to 16 bits exactly as the lookup kernel rounds its output, fp32 accumulation in TMEM.
+// Same operand values as fsb_geo_lookup(out_layout 1/2) followed by the convc1 launch of fsb_conv2d_nhwc -- rounded to 16
+// bits exactly as the lookup kernel rounds its output --, fp32 accumulation in TMEM in another K order (by level): the two
+// paths agree to accumulation-order rounding (4e-4 of the 16-bit result's range in the tests).
 #include "common.cuh"
 #include "lookup.cuh"
 #include "umma.cuh"
@@ -229,6 +232,11 @@ lookup_convc1_kernel(const __grid_constant__ LcParams p) {
         nx[i] = ok ? __ldg(p.coords + ppix) : 0.f;
       }
     };
+    // level pointers in registers (the steps below are unrolled over the level)
+    const float* const geo0 = p.geo.p[0];
+    const float* const geo1 = p.geo.p[LT > 1 ? 1 : 0];
+    const float* const cor0 = p.cor.p[0];
+    const float* const cor1 = p.cor.p[LT > 1 ? 1 : 0];
     // pipeline state of the two passes in flight
     float4 v[kLcDepth][K + 1];
     float pfr[kLcDepth][3];   // the producer role's fractions (taps sub, sub + 4, sub + 8): shuffled to the consumers at use
@@ -256,7 +264,7 @@ lookup_convc1_kernel(const __grid_constant__ LcParams p) {
       const bool fast = __all_sync(0xffffffffu, !live[b] || inside);   // whole windows inside: no per-row tests
       if (live[b]) {
         if (!is_cor) {
-          const float4* g4 = reinterpret_cast<const float4*>(p.geo.p[h] + ((long long)pix * Dl + base_) * Cg) + q;
+          const float4* g4 = reinterpret_cast<const float4*>((h == 0 ? geo0 : geo1) + ((long long)pix * Dl + base_) * Cg) + q;
           if (fast) {
 #pragma unroll
             for (int j = 0; j <= K; ++j) v[b][j] = __ldg(g4 + j * nq);
@@ -266,7 +274,7 @@ lookup_convc1_kernel(const __grid_constant__ LcParams p) {
               v[b][j] = (unsigned)(base_ + j) < (unsigned)Dl ? __ldg(g4 + j * nq) : make_float4(0.f, 0.f, 0.f, 0.f);
           }
         } else {
-          const float* c1 = p.cor.p[h] + (long long)pix * Wl + base_;
+          const float* c1 = (h == 0 ? cor0 : cor1) + (long long)pix * Wl + base_;
           if (fast) {
 #pragma unroll
             for (int j = 0; j <= K; ++j) v[b][j].x = __ldg(c1 + j);
