@@ -66,7 +66,7 @@ def config_block(name, pairs, world):
             "l2": "inputs+outputs of a step (per pair: 112 MB fp16 filtered volume, 256 MB cost volume, 335 MB geo pyramid) "
                   "exceed the 126 MB L2; per-kernel timings flush L2 with a 512 MiB write before each launch",
             "parallelism": "pairs sharded over the GPUs, no collective on the path",
-            "update_block": "tcgen05 implicit-GEMM convolutions with fused gate epilogues (csrc/conv.cu), one CUDA graph per iteration"}
+            "update_block": "tcgen05 implicit-GEMM convolutions with fused gate epilogues (csrc/conv.cu), ONE CUDA graph for the whole refinement loop"}
 
 
 # --------------------------------------------------------------------------------------
@@ -560,7 +560,7 @@ def run_b200(args):
                 "peak_source": peaks["source"] + " (MEASURED_PEAKS.json bf16_tflops_sustained: the kernel runs inside a long step)",
                 "algorithmic_flops_per_update_step": conv_flops, "launches_per_step": n_conv * iters * n_micro,
                 "ms_per_update_step_sum_of_launches": conv_ms, "ms_other_kernels_per_update_step": other_ms,
-                # the same FLOPs over the loop time measured INSIDE the timed steps (all 35 kernels of an iteration, two
+                # the same FLOPs over the loop time measured INSIDE the timed steps (all 29 kernels of an iteration, two
                 # lanes): what the tensor launches deliver in the step, the figure `frac` must agree with
                 "in_step_achieved": in_step_tf, "in_step_frac": in_step_tf / peak_tf,
                 "whole_step_achieved": whole_step_tf, "whole_step_frac": whole_step_tf / peak_tf,

@@ -73,7 +73,7 @@ class StereoHotPath:
         """Runs a sequence of batches whose inputs live in PINNED HOST memory (dicts with the keys of
         `run`: fl, fr, pl, pr, volume, disp, net, inp, att) and returns the final disparities in pinned
         host tensors.  Every batch is copied host->device on a copy stream into one of two static
-        device slots while the previous batch computes (the 0.54 GB of inputs per pair take longer over
+        device slots while the previous batch computes (the 0.16-0.27 GB of inputs per pair take longer over
         PCIe than a third of the compute, so a serial copy costs 25 % of the throughput); the result
         goes device->host asynchronously.  Synchronises once, at the end."""
         batches = list(batches)
