@@ -67,3 +67,50 @@ def test_patch_rebinds_reference_names():
     assert mod.Combined_Geo_Encoding_Volume is fsb.Combined_Geo_Encoding_Volume
     assert mod.disparity_regression is fsb.disparity_regression
     assert mod.context_upsample is fsb.context_upsample
+
+
+def test_convc1_weight_layout_for_the_fused_lookup():
+    """ops.pack_convc1_weight: every pyramid level's K*(Cg+1) columns of convc1.weight start at a multiple of
+    Kl = K*(Cg+1) rounded up to 64, zeros in between (the layout fsb_lookup_convc1 documents in include/fsb200.h)."""
+    import torch
+    from foundationstereo_b200 import ops
+    L, K, Cg = 2, 9, 28
+    n = K * (Cg + 1)
+    w = torch.arange(256 * L * n, dtype=torch.float32).reshape(256, L * n, 1, 1) / 1000.0
+    p = ops.pack_convc1_weight(w, L, K, Cg, torch.float32)
+    kl = 320
+    assert p.shape == (256, L * kl) and p.is_contiguous()
+    for l in range(L):
+        assert torch.equal(p[:, l * kl:l * kl + n], w[:, l * n:(l + 1) * n, 0, 0])
+        assert (p[:, l * kl + n:(l + 1) * kl] == 0).all()
+    assert ops.pack_convc1_weight(w[:, :n], 1, K, Cg, torch.float16).shape == (256, kl)
+
+
+def test_fused_stem_patch_keeps_the_module_and_restores_it():
+    """install(model, fused_stem=True): corr_stem[0] stays in the module tree (state_dict keys for
+    checkpoints) with an identity forward, the deferred build_gwc_volume returns a zero-channel tensor that torch.cat
+    passes over, and uninstall() puts the convolution's forward back.  (The fused launch itself is a GPU test.)"""
+    import types
+    import torch
+    from foundationstereo_b200 import patch
+
+    class Stub(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.corr_stem = torch.nn.Sequential(torch.nn.Conv3d(32, 28, kernel_size=1))
+
+    model = Stub()
+    keys = sorted(model.state_dict().keys())
+    x = torch.randn(1, 32, 2, 3, 4)
+    want = model.corr_stem(x)
+    gwc_fn, cat_fn = patch.install_stem(model)
+    try:
+        assert sorted(model.state_dict().keys()) == keys
+        assert model.corr_stem(x) is x                              # identity: the fused kernel already applied it
+        placeholder = gwc_fn(torch.zeros(2, 16, 3, 4), torch.zeros(2, 16, 3, 4), 5, 8)
+        assert placeholder.shape == (2, 0, 5, 3, 4)
+        y = torch.zeros(2, 28, 5, 3, 4)
+        assert torch.cat([placeholder, y], dim=1).shape == y.shape   # what core/foundation_stereo.py:212 does with it
+    finally:
+        patch.uninstall(model)
+    assert torch.equal(model.corr_stem(x), want)
