@@ -775,7 +775,7 @@ class SelectiveUpdateBlock:
             plan = self.plan_for(B, H, W)
             self._ingest(plan, list(net), inp, att, None, disp.float())
             key = tuple(t.data_ptr() for t in list(geo.geo_levels) + list(geo.corr_levels)) + (
-                geo.radius, mask_every_iter, getattr(geo, "corr_band", None))
+                geo.radius, mask_every_iter, getattr(geo, "corr_band", None), self.fused_lookup_conv, self.pipelined)
             if plan.iter_key != key:
                 levels = (list(geo.geo_levels), list(geo.corr_levels), geo.radius)
                 from . import ops
