@@ -45,6 +45,7 @@ def _down(n: int) -> int:
 
 
 FORK, JOIN = "fork", "join"
+_ENC_D = ("encoder.convd1", "encoder.convd2")
 
 
 class _Plan:
@@ -144,6 +145,10 @@ class SelectiveUpdateBlock:
         # the 1000 W power cap, and the SM clock under load dropped from 1615 to 1555 MHz with the busier schedule, which
         # is why better overlap buys only 1 %.  FSB_PIPELINE=0 restores the iteration-by-iteration order.
         self.pipelined = _os.environ.get("FSB_PIPELINE", "1") != "0"
+        # pipelined loop: convd1 / convd2 on the side lane behind the coarse levels (FSB_ENCD_SIDE=1).  Measured on the B200
+        # (8 pairs, A/B twice): 91.6 / 91.7 against 93.5 / 93.2 pairs/s -- the extra cross-lane event and the earlier join
+        # cost more than the 85 us they take off the main lane; off.
+        self.encd_side = _os.environ.get("FSB_ENCD_SIDE", "0") == "1"
         self.pdl_cross = _os.environ.get("FSB_PDL_CROSS", "0") == "1"  # programmatic edges across lanes too (hung: see run_steps)
         self.two_lanes = _os.environ.get("FSB_TWO_LANES", "1") != "0"  # side stream for encoder / mask head
         self.copy_outputs = copy_outputs  # forward returns fresh tensors instead of views of the plan's buffers
@@ -664,9 +669,11 @@ class SelectiveUpdateBlock:
             else:
                 fn()
 
-        def group(name, lane):
-            for fn, g, tag in zip(plan.steps, plan.groups, plan.tags):
+        def group(name, lane, only=None, skip=()):
+            for fn, g, tag, nm in zip(plan.steps, plan.groups, plan.tags, plan.names):
                 if g != name or fn is FORK or fn is JOIN or tag in ("mask", "pool_tail"):
+                    continue
+                if (only is not None and nm not in only) or nm in skip:
                     continue
                 if lane == 0:
                     launch(fn, 0)
@@ -682,10 +689,25 @@ class SelectiveUpdateBlock:
                 group("head", 0)                 # disparity head of iteration i-1, disp += delta in its last launch
                 if not plan.accum:
                     C.axpy(plan.disp, plan.delta)
-            plan.lookup()
-            group("enc", 0)
-            main.wait_stream(plan.side)          # join
-            fence[0] = True
+            if self.encd_side:
+                # the disparity branch of the motion encoder (convd1 -> convd2, core/update.py:66-67) needs only the new
+                # disparity: it follows the coarse levels on the side lane, and the join moves in front of encoder.conv
+                if i > 0:
+                    ev = torch.cuda.Event()
+                    ev.record(main)
+                    plan.side.wait_event(ev)
+                    fence[1] = True
+                group("enc", 1, only=_ENC_D)
+                plan.lookup()
+                group("enc", 0, skip=_ENC_D + ("encoder.conv",))
+                main.wait_stream(plan.side)      # join
+                fence[0] = True
+                group("enc", 0, only=("encoder.conv",))
+            else:
+                plan.lookup()
+                group("enc", 0)
+                main.wait_stream(plan.side)      # join
+                fence[0] = True
             group("fine", 0)
         group("head", 0)
         if not plan.accum:
@@ -775,7 +797,7 @@ class SelectiveUpdateBlock:
             plan = self.plan_for(B, H, W)
             self._ingest(plan, list(net), inp, att, None, disp.float())
             key = tuple(t.data_ptr() for t in list(geo.geo_levels) + list(geo.corr_levels)) + (
-                geo.radius, mask_every_iter, getattr(geo, "corr_band", None), self.fused_lookup_conv, self.pipelined)
+                geo.radius, mask_every_iter, getattr(geo, "corr_band", None), self.fused_lookup_conv, self.pipelined, self.encd_side)
             if plan.iter_key != key:
                 levels = (list(geo.geo_levels), list(geo.corr_levels), geo.radius)
                 from . import ops

@@ -491,16 +491,18 @@ def test_pipelined_loop_is_bit_identical(fsb, layers):
     geo = fsb.Combined_Geo_Encoding_Volume(c(x["fl"]), c(x["fr"]), c(x["volume"]), num_levels=2, dx=dx)
     inp, att = [c(t) for t in x["inp"]][:layers], [c(t) for t in x["att"]][:layers]
     outs = []
-    for pipe in (False, True):
+    for pipe in (False, True, "encd_side"):
         ub = fsb.SelectiveUpdateBlock(p, "cuda", use_graph=True)
-        ub.pipelined = pipe
+        ub.pipelined = bool(pipe)
+        ub.encd_side = pipe == "encd_side"   # convd1 / convd2 on the side lane as well
         for _ in range(3):  # eager + per-iteration graph, then the captured loop graph, then its replay
             got, mask, net = ub.refine(geo, [c(t) for t in x["net"]][:layers], inp, att, c(x["disp"]), iters)
         outs.append((got.clone(), mask.clone(), [t.clone() for t in net]))
     torch.cuda.synchronize()
-    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
-    for a, b in zip(outs[0][2], outs[1][2]):
-        assert torch.equal(a, b)
+    for other in outs[1:]:
+        assert torch.equal(outs[0][0], other[0]) and torch.equal(outs[0][1], other[1])
+        for a, b in zip(outs[0][2], other[2]):
+            assert torch.equal(a, b)
 
 
 # ------------------------------------------------------- kernel 2 on tcgen05 (TF32 / 3xTF32)
