@@ -435,7 +435,8 @@ def run_b200(args):
         us_iter_alone = 1e3 * g0.elapsed_time(g1) / iters
         plan = ub.plan_for(c["B"], c["H"], c["W"])
         steps_ = [(n_, f_) for n_, f_ in zip(plan.names, plan.steps) if callable(f_)]
-        plan.loop_active = ub.fused_lookup_conv   # time encoder.convc1 as the loop runs it (with the lookup fused in, if enabled)
+        # time encoder.convc1 as the captured loop runs it (with the lookup fused in, if enabled)
+        plan.loop_active = bool(ub.fused_lookup_conv and ub.pipelined and plan.fused_c1 is not None)
         reps = 10
         tot = [0.0] * len(steps_)
         for _ in range(reps):
@@ -452,7 +453,7 @@ def run_b200(args):
         clocks.stop()
         # with the lookup fused into encoder.convc1 (csrc/lookconv.cu, the default loop) that launch is the HBM-bound gather
         # with a small GEMM under it: it is reported under hbm_kernels, not in the tensor-core roofline
-        fused_c1 = bool(ub.fused_lookup_conv and plan.fused_c1 is not None)
+        fused_c1 = bool(ub.fused_lookup_conv and ub.pipelined and plan.fused_c1 is not None)
         is_conv = lambda n_, f_: hasattr(f_, "flops") and not (fused_c1 and n_ == "encoder.convc1")
         conv_ms = sum(t for (n_, f_), t in zip(steps_, tot) if is_conv(n_, f_))
         other_ms = sum(t for (n_, f_), t in zip(steps_, tot) if not is_conv(n_, f_))

@@ -98,7 +98,8 @@ class _Convc1Step:
         self.args = conv.args
 
     def __call__(self) -> None:
-        # only inside refine()'s loop: the drop-in forward() is handed ITS caller's lookup tensor
+        # only inside the captured, pipelined loop of refine(): the drop-in forward() is handed ITS caller's lookup tensor,
+        # and the iteration-by-iteration order (run_steps) runs lookup + convc1 as two launches
         fused = self.plan.fused_c1 if self.plan.loop_active else None
         (fused or self.conv)()
 
@@ -138,7 +139,9 @@ class SelectiveUpdateBlock:
         # 92.4 vs 91.6 pairs/s in the loop.  Same 16-bit operand values; the GEMM's K order differs (split by level), so
         # results agree to fp32 accumulation order (max |d disparity| 2.6e-5 px after 6 iterations in the test).
         # FSB_FUSED_LOOKUP_CONV=0 restores the two launches; radius != 4, more than two levels, Cg % 4 != 0 or a banded
-        # correlation pyramid use them anyway.
+        # correlation pyramid use them anyway, and so does the iteration-by-iteration order of `run_steps`: the fused launch
+        # exists only in the pipelined loop, on the main lane (with it on the side lane of the iteration-by-iteration order a
+        # full-size one-pair run stalled twice in nine test-suite runs).
         self.fused_lookup_conv = _os.environ.get("FSB_FUSED_LOOKUP_CONV", "1") != "0"
         # refine(): coarse GRU levels of iteration i+1 under the disparity head of iteration i (run_loop_pipelined).
         # Bit-identical results; B200, 8 pairs: 93.0 -> 93.9 pairs/s (2640 -> 2614 us per iteration) -- the step runs at
@@ -655,6 +658,14 @@ class SelectiveUpdateBlock:
         assert self.n_layers >= 2
         main = torch.cuda.current_stream()
         plan.accum = self.dot_head4
+        fused = plan.fused_c1 is not None
+        plan.loop_active = fused     # encoder.convc1 = the lookup fused into it (csrc/lookconv.cu); no lookup launch
+        try:
+            self._emit_pipelined(plan, iters, main, fused)
+        finally:
+            plan.loop_active = False
+
+    def _emit_pipelined(self, plan: _Plan, iters: int, main, fused: bool) -> None:
         lib = _lib.lib()
         fence = [False, False]
 
@@ -698,13 +709,15 @@ class SelectiveUpdateBlock:
                     plan.side.wait_event(ev)
                     fence[1] = True
                 group("enc", 1, only=_ENC_D)
-                plan.lookup()
+                if not fused:
+                    plan.lookup()
                 group("enc", 0, skip=_ENC_D + ("encoder.conv",))
                 main.wait_stream(plan.side)      # join
                 fence[0] = True
                 group("enc", 0, only=("encoder.conv",))
             else:
-                plan.lookup()
+                if not fused:
+                    plan.lookup()
                 group("enc", 0)
                 main.wait_stream(plan.side)      # join
                 fence[0] = True
@@ -814,7 +827,10 @@ class SelectiveUpdateBlock:
                     _, w1, b1 = self._w1_levels
                     plan.fused_c1 = lambda: ops.lookup_convc1(levels[0], levels[1], plan.disp, plan.coords, levels[2], w1,
                                                               b1, plan.c1)
-                    plan.lookup = lambda: None
+                    # only `run_loop_pipelined` (where the launch sits on the MAIN lane) uses it; the iteration-by-iteration
+                    # order of `run_steps` (FSB_PIPELINE=0, mask_every_iter) keeps lookup + convc1
+                    plan.lookup = lambda: ops.geo_lookup_nhwc16(levels[0], levels[1], plan.disp, plan.coords, levels[2],
+                                                                plan.corr16)
                 elif band is not None:
                     plan.lookup = lambda: ops.geo_lookup_band(levels[0], levels[1], plan.disp, plan.coords, levels[2], band,
                                                               plan.corr16)
@@ -825,11 +841,7 @@ class SelectiveUpdateBlock:
                 plan.iter_graph = None
                 plan.loop_graphs = {}
                 plan.iter_calls = 0
-            plan.loop_active = True
-            try:
-                self._refine_loop(plan, iters, mask_every_iter)
-            finally:
-                plan.loop_active = False
+            self._refine_loop(plan, iters, mask_every_iter)
             if not mask_every_iter:
                 self.run_steps(plan, only_mask=True)
             return plan.disp.clone(), plan.mask, [plan.h32[l].permute(0, 3, 1, 2) for l in range(self.n_layers)]
@@ -840,12 +852,18 @@ class SelectiveUpdateBlock:
             tp = self.tail_pools
             if tp:
                 self.run_steps(plan, only_tag="pool_head")
-            if self.use_graph and self.loop_graph and plan.iter_calls > 0:
+            pipe = self.pipelined and self.two_lanes and self.n_layers >= 2 and not mask_every_iter and not tp
+            if pipe and not (self.use_graph and self.loop_graph and plan.iter_calls > 0):
+                # first call on a plan (or no graphs at all): the SAME pipelined launch order, issued eagerly -- every call
+                # then runs the same kernels in the same order (bit-identical results from call to call), and the fused
+                # lookup -> convc1 launch only ever runs on the main lane
+                self.run_loop_pipelined(plan, iters)
+                plan.iter_calls += iters
+            elif self.use_graph and self.loop_graph and plan.iter_calls > 0:
                 # the WHOLE loop as one graph (iters x 30-odd kernel nodes): programmatic dependent launch keeps
                 # overlapping kernel tails across iteration boundaries and the host launches once per pair batch
                 g = plan.loop_graphs.get(iters)
                 if g is None:
-                    pipe = self.pipelined and self.two_lanes and self.n_layers >= 2 and not mask_every_iter and not tp
                     g = plan.loop_graphs[iters] = self._capture(plan, True, mask_every_iter, iters, tail_pools=tp,
                                                                 pipelined=pipe)
                 self._replay(g)

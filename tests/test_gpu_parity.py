@@ -494,6 +494,7 @@ def test_pipelined_loop_is_bit_identical(fsb, layers):
     for pipe in (False, True, "encd_side"):
         ub = fsb.SelectiveUpdateBlock(p, "cuda", use_graph=True)
         ub.pipelined = bool(pipe)
+        ub.fused_lookup_conv = False         # like with like: the fused lookup -> convc1 exists in the pipelined order only
         ub.encd_side = pipe == "encd_side"   # convd1 / convd2 on the side lane as well
         for _ in range(3):  # eager + per-iteration graph, then the captured loop graph, then its replay
             got, mask, net = ub.refine(geo, [c(t) for t in x["net"]][:layers], inp, att, c(x["disp"]), iters)
@@ -598,6 +599,9 @@ def test_refine_mask_once_equals_mask_every_iteration(fsb):
     res = []
     for every in (False, True):
         ub = fsb.SelectiveUpdateBlock(p, "cuda")
+        # like with like: mask_every_iter runs the iteration-by-iteration order, which keeps lookup and convc1 as two
+        # launches; the fused launch of the pipelined order accumulates in another K order (equal to fp32 rounding only)
+        ub.fused_lookup_conv = False
         ws = fsb.Combined_Geo_Encoding_Volume.make_workspace(1, 28, D, H, W, W, 2, "cuda")
         geo = fsb.Combined_Geo_Encoding_Volume(c(x["fl"]), c(x["fr"]), c(x["volume"]), num_levels=2, dx=dx, workspace=ws)
         for _ in range(3):  # eager first call, per-iteration graph, whole-loop graph
