@@ -792,8 +792,9 @@ class SelectiveUpdateBlock:
     # ---- the whole refinement loop (core/foundation_stereo.py:236-242) -----------------------
     def refine(self, geo, net: Sequence[Tensor], inp: Sequence[Tensor], att: Sequence[Tensor], disp: Tensor,
                iters: int, mask_every_iter: bool = False) -> Tuple[Tensor, Tensor, List[Tensor]]:
-        """``iters`` x [geo lookup -> update block -> disp += delta] with every iteration ONE
-        CUDA-graph replay: the lookup writes the 16-bit NHWC tensor convc1 reads, the update
+        """``iters`` x [geo lookup -> update block -> disp += delta] as ONE CUDA-graph replay for the whole loop (the
+        first call on a plan issues the same launches eagerly): the lookup is gathered straight into convc1's
+        shared-memory operand (csrc/lookconv.cu; or written as the 16-bit NHWC tensor convc1 reads), the update
         runs on the plan's static buffers and the disparity is updated in place, so there is no
         host work or host sync between iterations.  ``geo`` is a Combined_Geo_Encoding_Volume
         (its level buffers should have stable addresses -- ``workspace=`` -- or the graph is
