@@ -16,6 +16,7 @@ from .hotpath import (  # noqa: F401
     l2_normalize,
     gwc_volume,
     concat_volume,
+    volume_stem,
     row_correlation,
     halve_last,
     corr_pyramid,

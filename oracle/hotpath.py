@@ -66,6 +66,16 @@ def concat_volume(left: Tensor, right: Tensor, maxdisp: int) -> Tensor:
     return vol
 
 
+def volume_stem(left: Tensor, right: Tensor, proj_left: Tensor, proj_right: Tensor, weight: Tensor, bias: Tensor,
+                maxdisp: int, num_groups: int) -> Tensor:
+    """What the caller computes up to the first layer of corr_stem (core/foundation_stereo.py:207-213 with the 1x1x1
+    Conv3d(32 -> 28) of :164-165): corr_stem[0](cat([gwc volume, concat volume], 1)).  ``weight`` (Co, G + 2 Cp[,1,1,1]),
+    ``bias`` (Co).  The checker of the opt-in fused kernel fsb_volume_stem."""
+    vol = torch.cat([gwc_volume(left, right, maxdisp, num_groups), concat_volume(proj_left, proj_right, maxdisp)], 1)
+    w = weight.reshape(weight.shape[0], -1)
+    return torch.einsum("oc,bcdhw->bodhw", w, vol) + bias.reshape(1, -1, 1, 1, 1)
+
+
 # --------------------------------------------------------------------------
 # geometry-encoding volume  (core/geometry.py:17-77, core/utils/utils.py:44-55)
 # --------------------------------------------------------------------------

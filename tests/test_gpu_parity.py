@@ -311,8 +311,7 @@ def test_volume_fused_with_corr_stem(fsb, cfg):
     bst = torch.randn(Co, generator=g) * 0.1
     fl, fr, pl, pr = (x[k].to(dtype) for k in ("fl", "fr", "pl", "pr"))
     with torch.no_grad():
-        vol = torch.cat([oracle.gwc_volume(fl.float(), fr.float(), D, G), oracle.concat_volume(pl.float(), pr.float(), D)], 1)
-        want = F.conv3d(vol, wst.reshape(Co, -1, 1, 1, 1), bst)
+        want = oracle.volume_stem(fl.float(), fr.float(), pl.float(), pr.float(), wst, bst, D, G)
     got = ops.volume_stem(dev(fl), dev(fr), dev(pl), dev(pr), wst.reshape(Co, -1, 1, 1, 1).cuda(), bst.cuda(), D, G)
     assert got.shape == want.shape and got.dtype == dtype and got.is_contiguous()
     tol = 1e-4 if dtype == torch.float32 else (2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7)

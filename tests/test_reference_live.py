@@ -23,6 +23,21 @@ def test_volumes_and_geo_match_reference_live():
         assert rel_err(mine(x["disp"], x["coords"]), ref(x["disp"], x["coords"])) <= 1e-5
 
 
+def test_volume_stem_matches_reference_live():
+    """oracle.volume_stem (the checker of the opt-in fused kernel fsb_volume_stem) against the reference's own sequence:
+    build_gwc_volume, build_concat_volume, torch.cat and an nn.Conv3d(32, 28, kernel_size=1) as in corr_stem
+    (core/foundation_stereo.py:207-213, 164-165)."""
+    ns = rm.import_reference()
+    x = oracle.make_inputs(B=2, C=32, H=5, W=21, D=11, Cg=28, seed=23)
+    torch.manual_seed(5)
+    conv0 = torch.nn.Conv3d(8 + 2 * x["pl"].shape[1], 28, kernel_size=1)
+    with torch.no_grad():
+        want = conv0(torch.cat([ns.build_gwc_volume(x["fl"], x["fr"], 11, 8), ns.build_concat_volume(x["pl"], x["pr"], 11)], 1))
+        got = oracle.volume_stem(x["fl"], x["fr"], x["pl"], x["pr"], conv0.weight, conv0.bias, 11, 8)
+    assert got.shape == want.shape
+    assert rel_err(got, want) <= 1e-5
+
+
 @pytest.mark.parametrize("n_layers,levels", [(3, 2), (2, 2), (1, 2), (3, 4)])
 def test_update_block_matches_reference_live(n_layers, levels):
     """n_gru_layers 1..3 (core/update.py:128-132,142-153; with one layer the reference never calls gru04) and the
